@@ -1,0 +1,1475 @@
+// epde_b200.cu -- B200 (sm_100a) kernels + C ABI of the EPDE fitness-evaluation engine.
+//
+// Path (reference paths relative to the EPDE tree):
+//   token cache            epde/cache/cache.py:141-524              -> HBM-resident token table
+//   term assembly          structure/factor.py:218-269, evaluators.py:92-151,
+//                          structure/main_structures.py:207-235,588-641
+//                                                                    -> gram_cells_kernel (pass A)
+//   calculate_weights      epde/supplementary.py:394-471             -> segment Grams + lasso_solve_kernel
+//   PhysicsInformedLasso   operators/common/sparsity.py:20-150       -> lasso_solve_kernel
+//   L2LRFitness/L2Fitness  operators/common/fitness.py:27-183        -> residual_kernel (pass B)
+//
+// Data layout in HBM
+//   token t            double[N]   N = prod(inner_shape), C order, last axis contiguous
+//   cell Grams  C      per equation: [cellA][cellB][piece][NACC]   NACC = T(T+3)/2
+//                      (upper triangle of the T x T term Gram, then the T column sums)
+//   segment Grams S    per equation: [segment row][NE], NE = NACC + 1 (last = point count);
+//                      segment rows of all axes stacked; after prefix_kernel rows hold inclusive
+//                      prefix sums along each axis, so a sliding-window Gram is a difference of
+//                      two rows.
+//
+// No CPU fallback exists in this file: every entry point either runs the CUDA path or fails.
+#include "../../include/epde_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <set>
+#include <string>
+#include <vector>
+
+#define TMAX EPDE_MAX_TERMS
+#define FMAXF EPDE_MAX_FACTORS
+#define KS (TMAX + 1)          // stride of a sliding-window weight row
+#define RIDGE 1e-6             // supplementary.py:458
+#define LASSO_MAX_ITER 20      // sparsity.py:21
+#define LASSO_TOL 1e-4         // sparsity.py:21
+#define RED_CHUNK 16           // Gram entries reduced per shared-memory round in pass A
+
+static thread_local std::string g_err;
+
+static int fail(const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+
+#define CK(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t _e = (call);                                                              \
+        if (_e != cudaSuccess)                                                                \
+            return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------
+// device-side descriptors
+// ------------------------------------------------------------------------------------------
+struct FactorDesc {          // 32 bytes
+    const double* ptr;       // token vector
+    double param;            // freq for trig kinds
+    double power;
+    int kind;                // 0 pow, 1 sin, 2 cos, 3 inverse
+    int ipow;                // integer power if power is a small positive integer, else 0
+};
+
+struct EqDesc {
+    int T;
+    int fac_off[TMAX + 1];   // into the batch factor array
+    long long s_off;         // doubles, into the segment-Gram table
+};
+
+struct UnitDesc {            // one CTA work unit of pass A: a cell of the leading axes x a column chunk
+    int a_lo, a_hi;          // index range on leading slot A
+    int b_lo, b_hi;          // index range on leading slot B
+    int col_lo, ncols;       // columns (last axis) handled, ncols <= blockDim.x
+    int cell;                // (cellA * nB + cellB)
+    int piece_lo, npieces;   // pieces (sub-segments of the last axis) covered by the chunk
+    int pad0, pad1, pad2;
+};
+
+struct MargDesc {            // one output row of the segment-Gram table
+    int row;                 // row in S
+    int a_lo, a_hi, b_lo, b_hi, p_lo, p_hi;   // cell ranges to sum
+    int pad;
+    double count;            // number of grid points in the segment slab (local)
+};
+
+struct Geom {                // kernel-visible geometry (by value)
+    long long strideA, strideB;    // element strides of the leading slots
+    int nA, nB, npieces;           // cell-grid extents
+    int n_units;
+    int n_cells;                   // nA * nB * npieces
+    int n_rows;                    // segment rows over all axes
+    int n_windows;
+    int ndim;
+    int total_row;                 // prefix row holding the Gram of all points (last row of axis 0)
+    long long N;
+    const UnitDesc* units;
+    const int* piece_start;        // [npieces + 1] column bounds
+    const MargDesc* marg;          // [n_rows]
+    const int* axis_row_base;      // [ndim + 1]
+    const int* win_hi_row;         // [W]
+    const int* win_lo_row;         // [W] (-1: window starts at the axis origin)
+};
+
+__host__ __device__ __forceinline__ int nacc_of(int T) { return T * (T + 3) / 2; }
+
+// index of the (i, j) product inside a Gram row; column T is the ones column
+__host__ __device__ __forceinline__ int gidx(int i, int j, int T) {
+    if (i > j) { int t = i; i = j; j = t; }
+    if (j == T) return (i == T) ? nacc_of(T) : T * (T + 1) / 2 + i;
+    return i * T - i * (i - 1) / 2 + (j - i);
+}
+
+// ------------------------------------------------------------------------------------------
+// factor / term evaluation (factor.py:218-269, evaluators.py:92-151)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ double ld_stream(const double* p) {
+    return __ldg(p);
+}
+
+__device__ __forceinline__ double apply_factor(const FactorDesc& f, double x) {
+    if (f.kind != 0) {
+        if (f.kind == 1) x = sin(f.param * x);
+        else if (f.kind == 2) x = cos(f.param * x);
+        else return pow(x, -f.power);
+    }
+    if (f.ipow == 1) return x;
+    if (f.ipow == 2) return x * x;
+    if (f.ipow == 3) return x * x * x;
+    return pow(x, f.power);
+}
+
+template <int T>
+__device__ __forceinline__ void eval_terms(const FactorDesc* sf, const int* foff, long long idx,
+                                           double (&c)[T]) {
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+        const int f0 = foff[t], f1 = foff[t + 1];
+        double v = apply_factor(sf[f0], ld_stream(sf[f0].ptr + idx));
+        for (int f = f0 + 1; f < f1; ++f) v *= apply_factor(sf[f], ld_stream(sf[f].ptr + idx));
+        c[t] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// pass A: fused term assembly + cell Gram.  One CTA = (unit, equation); thread <-> column of the
+// last axis, looping over the rows of the leading-axes cell, so every thread only ever sees points
+// of one last-axis piece and the accumulators stay in registers.  Equation index is the fastest
+// grid dimension so CTAs sweeping the same token tile for different equations are co-resident
+// (L2 reuse).
+// ------------------------------------------------------------------------------------------
+struct GramParams {
+    Geom g;
+    const EqDesc* eqs;
+    const FactorDesc* factors;
+    const int* eq_list;      // equations of this launch (all with the same T)
+    int n_eq;
+    double* cells;           // cell-Gram scratch
+};
+
+template <int T>
+__global__ void __launch_bounds__(256) gram_cells_kernel(GramParams p) {
+    constexpr int NACC = T * (T + 3) / 2;
+    __shared__ FactorDesc sf[T * FMAXF];
+    __shared__ int foff[T + 1];
+    extern __shared__ double red[];            // RED_CHUNK x (blockDim.x + 1)
+
+    const int tid = threadIdx.x;
+    const int BX = blockDim.x;
+    const int le = blockIdx.x % p.n_eq;        // position inside the launch group
+    const int e = p.eq_list[le];
+    const UnitDesc u = p.g.units[blockIdx.x / p.n_eq];
+    const EqDesc& eq = p.eqs[e];
+    const int fbase = eq.fac_off[0];
+    if (tid <= T) foff[tid] = eq.fac_off[tid] - fbase;
+    const int nfac = eq.fac_off[T] - fbase;
+    if (tid < nfac) sf[tid] = p.factors[fbase + tid];
+    __syncthreads();
+
+    double acc[NACC];
+#pragma unroll
+    for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
+
+    if (tid < u.ncols) {
+        const int wb = u.b_hi - u.b_lo;
+        const int nrows = (u.a_hi - u.a_lo) * wb;
+        const long long col = u.col_lo + tid;
+        int ia = u.a_lo, ib = u.b_lo;
+        for (int r = 0; r < nrows; ++r) {
+            const long long idx = ia * p.g.strideA + ib * p.g.strideB + col;
+            double c[T];
+            eval_terms<T>(sf, foff, idx, c);
+            int k = 0;
+#pragma unroll
+            for (int i = 0; i < T; ++i)
+#pragma unroll
+                for (int j = i; j < T; ++j) { acc[k] = fma(c[i], c[j], acc[k]); ++k; }
+#pragma unroll
+            for (int i = 0; i < T; ++i) { acc[k] += c[i]; ++k; }
+            if (++ib == u.b_hi) { ib = u.b_lo; ++ia; }
+        }
+    }
+
+    // epilogue: reduce the columns of every piece, RED_CHUNK Gram entries per round
+    const int RS = BX + 1;
+    double* out = p.cells + ((long long)le * p.g.n_cells + (long long)u.cell * p.g.npieces + u.piece_lo) * NACC;
+#pragma unroll
+    for (int base = 0; base < NACC; base += RED_CHUNK) {
+        const int cnt = (NACC - base) < RED_CHUNK ? (NACC - base) : RED_CHUNK;
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < RED_CHUNK; ++k)
+            if (base + k < NACC) red[k * RS + tid] = acc[base + k];
+        __syncthreads();
+        const int nout = u.npieces * cnt;
+        for (int o = tid; o < nout; o += BX) {
+            const int pp = o / cnt, k = o - pp * cnt;
+            const int lo = p.g.piece_start[u.piece_lo + pp] - u.col_lo;
+            const int hi = p.g.piece_start[u.piece_lo + pp + 1] - u.col_lo;
+            double s = 0.0;
+            for (int cidx = lo; cidx < hi; ++cidx) s += red[k * RS + cidx];
+            out[(long long)pp * NACC + base + k] = s;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// marginals: segment Gram row = sum of the cell Grams of the slab, in a fixed order (deterministic)
+// grid = (n_rows, n_eq_group); block = 256 = 8 cell lanes x 32 entry lanes
+// ------------------------------------------------------------------------------------------
+struct MargParams {
+    Geom g;
+    const EqDesc* eqs;
+    const int* eq_list;
+    const double* cells;
+    double* seg;
+};
+
+__global__ void __launch_bounds__(256) marginal_kernel(MargParams p) {
+    __shared__ double part[8][64];
+    const int e = p.eq_list[blockIdx.y];
+    const EqDesc& eq = p.eqs[e];
+    const int NACC = nacc_of(eq.T);
+    const int NE = NACC + 1;
+    const MargDesc m = p.g.marg[blockIdx.x];
+    const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
+    const int na = m.a_hi - m.a_lo, nb = m.b_hi - m.b_lo, np = m.p_hi - m.p_lo;
+    const int ncell = na * nb * np;
+    const double* C = p.cells + (long long)blockIdx.y * p.g.n_cells * NACC;
+    double s0 = 0.0, s1 = 0.0;
+    for (int q = grp; q < ncell; q += 8) {
+        const int ip = q % np;
+        const int r = q / np;
+        const int ibb = r % nb, iaa = r / nb;
+        const long long cell = ((long long)(m.a_lo + iaa) * p.g.nB + (m.b_lo + ibb)) * p.g.npieces + (m.p_lo + ip);
+        const double* src = C + cell * NACC;
+        if (lane < NACC) s0 += src[lane];
+        if (lane + 32 < NACC) s1 += src[lane + 32];
+    }
+    part[grp][lane] = s0;
+    part[grp][lane + 32] = s1;
+    __syncthreads();
+    if (threadIdx.x < 64 && threadIdx.x < NACC) {
+        double s = 0.0;
+#pragma unroll
+        for (int gI = 0; gI < 8; ++gI) s += part[gI][threadIdx.x];
+        p.seg[eq.s_off + (long long)m.row * NE + threadIdx.x] = s;
+    }
+    if (threadIdx.x == 64) p.seg[eq.s_off + (long long)m.row * NE + NACC] = m.count;
+}
+
+// inclusive prefix along the segments of each axis, in place.  grid = (ndim, n_eq), block = 64
+struct PrefixParams {
+    Geom g;
+    const EqDesc* eqs;
+    int n_eq;
+    double* seg;
+};
+
+__global__ void prefix_kernel(PrefixParams p) {
+    const int e = blockIdx.y, d = blockIdx.x;
+    const EqDesc& eq = p.eqs[e];
+    const int NE = nacc_of(eq.T) + 1;
+    const int r0 = p.g.axis_row_base[d], r1 = p.g.axis_row_base[d + 1];
+    double* S = p.seg + eq.s_off;
+    for (int a = threadIdx.x; a < NE; a += blockDim.x) {
+        double run = 0.0;
+        for (int r = r0; r < r1; ++r) {
+            run += S[(long long)r * NE + a];
+            S[(long long)r * NE + a] = run;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// solve: one CTA per eval.  calculate_weights (supplementary.py:455-469) = every window's ridge
+// system solved by a GS-lane group (Gaussian elimination with partial pivoting, as LAPACK gesv);
+// PhysicsInformedLasso.fit (sparsity.py:42-150) on the total Gram by thread 0 with the reference's
+// exact control flow.
+// ------------------------------------------------------------------------------------------
+struct SolveParams {
+    Geom g;
+    const EqDesc* eqs;
+    const int* eval_list;
+    const int* eval_eq;
+    const int* eval_tgt;
+    const double* seg;       // prefix-summed segment Grams
+    const int* mode;         // per eval: 0 LASSO, 1 given weights + window solves, 2 given weights only (may be null)
+    const double* given_wterm;   // [n_eval][TMAX] coefficient per term index (modes 1, 2)
+    const double* given_b;       // [n_eval]
+    // outputs (per eval)
+    double* coef;            // [n_eval][TMAX]   feature order
+    double* intercept;       // [n_eval]
+    double* stability;       // [n_eval]
+    double* sw;              // [n_eval][W][KS]
+    double* wterm;           // [n_eval][TMAX]   coefficient per TERM index (0 for target / inactive)
+    int* n_active;
+    int* all_zero;
+    int* iters;
+};
+
+#define SOLVE_THREADS 128
+
+__device__ __forceinline__ double nan_to_num(double x) {
+    if (isnan(x)) return 0.0;
+    if (isinf(x)) return x > 0 ? 1.7976931348623157e308 : -1.7976931348623157e308;
+    return x;
+}
+
+template <int GS>
+__global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams p) {
+    constexpr int NG = SOLVE_THREADS / GS;
+    __shared__ double Gt[KS * KS];             // total Gram of all points, symmetric K x K
+    __shared__ double M[NG][GS][GS + 1];       // augmented systems
+    __shared__ int cols[KS];                   // columns of the current system: active terms, then T (ones)
+    __shared__ double s_coef[TMAX], s_cv[TMAX], s_mu[KS], s_cvraw[KS];
+    __shared__ int s_n, s_state, s_iter, s_sweeps;
+    __shared__ double s_b;
+    extern __shared__ double s_sw[];           // [W][KS]
+
+    const int tid = threadIdx.x;
+    const int ev = p.eval_list[blockIdx.x];
+    const int e = p.eval_eq[ev];
+    const int tgt = p.eval_tgt[ev];
+    const EqDesc& eq = p.eqs[e];
+    const int T = eq.T, F = T - 1;
+    const int NE = nacc_of(T) + 1;
+    const int W = p.g.n_windows;
+    const double* P = p.seg + eq.s_off;
+
+    // total Gram
+    for (int q = tid; q < (T + 1) * (T + 1); q += SOLVE_THREADS) {
+        const int i = q / (T + 1), j = q % (T + 1);
+        Gt[i * KS + j] = P[(long long)p.g.total_row * NE + gidx(i, j, T)];
+    }
+    if (tid == 0) {
+        int n = 0;
+        for (int t = 0; t < T; ++t)
+            if (t != tgt) cols[n++] = t;
+        cols[n] = T;
+        s_n = n + 1;
+        s_state = 0;      // 0: first fit, 1: refit after a zeroed coefficient, 2: done
+        s_iter = 0;
+        s_sweeps = 0;
+        for (int j = 0; j < TMAX; ++j) { s_coef[j] = 0.0; s_cv[j] = 0.0; }
+    }
+    __syncthreads();
+
+    const int grp = tid / GS, lr = tid % GS;
+    // feature j (0..F-1) <-> term index
+    auto feat_term = [&](int j) { return j < tgt ? j : j + 1; };
+    const int mode = p.mode ? p.mode[ev] : 0;
+
+    while (mode != 2) {
+        const int n = s_n;                     // system size (active features + ones)
+        // ---------------- calculate_weights on the active set ----------------
+        const int rounds = (W + NG - 1) / NG;
+        for (int it = 0; it < rounds; ++it) {
+            int w = it * NG + grp;
+            const bool valid = w < W;
+            if (!valid) w = W - 1;
+            const double* Phi = P + (long long)p.g.win_hi_row[w] * NE;
+            const int lo_row = p.g.win_lo_row[w];
+            const double* Plo = P + (long long)(lo_row < 0 ? 0 : lo_row) * NE;
+            const double lo_on = lo_row < 0 ? 0.0 : 1.0;
+            double (*Mg)[GS + 1] = M[grp];
+            if (lr < n) {
+                const int i = cols[lr];
+                for (int c = 0; c < n; ++c) {
+                    const int gi = gidx(i, cols[c], T);
+                    double v = Phi[gi] - lo_on * Plo[gi];
+                    if (c == lr) v += RIDGE;
+                    Mg[lr][c] = v;
+                }
+                const int gi = gidx(i, tgt, T);
+                Mg[lr][n] = Phi[gi] - lo_on * Plo[gi];
+            }
+            __syncwarp();
+            for (int k = 0; k < n; ++k) {
+                // partial pivoting: first row of maximal |a_rk|, r >= k
+                double val = (lr >= k && lr < n) ? fabs(Mg[lr][k]) : -1.0;
+                int idx = lr;
+#pragma unroll
+                for (int off = GS / 2; off > 0; off >>= 1) {
+                    const double ov = __shfl_xor_sync(0xffffffffu, val, off, GS);
+                    const int oi = __shfl_xor_sync(0xffffffffu, idx, off, GS);
+                    if (ov > val || (ov == val && oi < idx)) { val = ov; idx = oi; }
+                }
+                if (idx != k && lr >= k && lr <= n) {
+                    const double t0 = Mg[k][lr];
+                    Mg[k][lr] = Mg[idx][lr];
+                    Mg[idx][lr] = t0;
+                }
+                __syncwarp();
+                if (lr > k && lr < n) {
+                    const double f = Mg[lr][k] / Mg[k][k];
+                    for (int c = k + 1; c <= n; ++c) Mg[lr][c] = fma(-f, Mg[k][c], Mg[lr][c]);
+                }
+                __syncwarp();
+            }
+            for (int k = n - 1; k >= 0; --k) {
+                const double xk = Mg[k][n] / Mg[k][k];
+                __syncwarp();
+                if (lr < k) Mg[lr][n] = fma(-Mg[lr][k], xk, Mg[lr][n]);
+                if (lr == k && valid) s_sw[w * KS + k] = xk;
+                __syncwarp();
+            }
+        }
+        __syncthreads();
+        // ---------------- column statistics: mean, var(ddof=1), CV (sparsity.py:29-40) ----------
+        if (tid < n) {
+            double s = 0.0;
+            for (int w = 0; w < W; ++w) s += s_sw[w * KS + tid];
+            const double mu = s / W;
+            double q = 0.0;
+            for (int w = 0; w < W; ++w) { const double dlt = s_sw[w * KS + tid] - mu; q = fma(dlt, dlt, q); }
+            const double var = q / (W - 1);     // std(ddof=1)**2 ; W == 1 -> nan like numpy
+            double cv = var / (mu * mu);
+            if (mu == 0.0) cv = 0.0;
+            s_mu[tid] = mu;
+            s_cvraw[tid] = cv;
+        }
+        __syncthreads();
+        // ---------------- coordinate descent (thread 0) ----------------
+        if (tid == 0 && mode == 1) s_state = 2;   // in-place fitness: window weights only (fitness.py:155-159)
+        if (tid == 0 && mode == 0) {
+            // scatter the refit into full-length feature vectors (sparsity.py:49-52, 87-96)
+            {
+                int a = 0;
+                for (int j = 0; j < F; ++j) {
+                    const bool act = (a < n - 1) && (cols[a] == feat_term(j));
+                    if (act) { s_coef[j] = s_mu[a]; s_cv[j] = nan_to_num(s_cvraw[a]); ++a; }
+                    else { s_coef[j] = 0.0; s_cv[j] = 0.0; }
+                }
+                s_b = s_mu[n - 1];
+            }
+            const double yy = Gt[tgt * KS + tgt], sy = Gt[tgt * KS + T], Npts = Gt[T * KS + T];
+            int iteration = s_iter;
+            bool refit = false;
+            bool first_pass_after_refit = (s_state == 1);
+            // after a refit the reference finishes the interrupted sweep's bookkeeping:
+            // max_change = inf fails criterion 1, then iteration += 1  (sparsity.py:96-150)
+            if (first_pass_after_refit) iteration = 1;
+            auto all_zero = [&]() { for (int j = 0; j < F; ++j) if (s_coef[j] != 0.0) return false; return true; };
+            auto xt_res = [&](int j) {
+                const int tj = feat_term(j);
+                double s = Gt[tj * KS + tgt];
+                for (int k2 = 0; k2 < F; ++k2) s = fma(-Gt[tj * KS + feat_term(k2)], s_coef[k2], s);
+                return fma(-s_b, Gt[tj * KS + T], s);
+            };
+            while (iteration < LASSO_MAX_ITER && !all_zero()) {
+                ++s_sweeps;
+                double max_change = 0.0;
+                // order = argsort(cv)[::-1]: descending CV, ties -> higher index first
+                int order[TMAX];
+                for (int j = 0; j < F; ++j) order[j] = j;
+                for (int a = 1; a < F; ++a) {
+                    const int oj = order[a];
+                    int b2 = a - 1;
+                    while (b2 >= 0 && (s_cv[order[b2]] < s_cv[oj] || (s_cv[order[b2]] == s_cv[oj] && order[b2] < oj))) {
+                        order[b2 + 1] = order[b2];
+                        --b2;
+                    }
+                    order[b2 + 1] = oj;
+                }
+                for (int q = 0; q < F; ++q) {
+                    const int j = order[q];
+                    const double old_coef = s_coef[j];
+                    if (old_coef == 0.0) continue;
+                    const int tj = feat_term(j);
+                    const double norm_sq = Gt[tj * KS + tj];
+                    const double y_sq_sum = yy - 2.0 * s_b * sy + Npts * s_b * s_b;
+                    const double rho = xt_res(j) + old_coef * norm_sq;
+                    const double thr = s_cv[j] * y_sq_sum;
+                    const double mag = fmax(fabs(rho) - thr, 0.0);
+                    const double sgn = (rho > 0.0) ? 1.0 : ((rho < 0.0) ? -1.0 : 0.0);
+                    const double new_coef = (sgn * mag) / norm_sq;
+                    s_coef[j] = new_coef;
+                    if (new_coef == 0.0) { refit = true; break; }
+                    const double change = fabs(new_coef - old_coef);
+                    if (change > max_change) max_change = change;
+                }
+                if (refit) break;
+                double max_abs = 0.0;
+                for (int j = 0; j < F; ++j) max_abs = fmax(max_abs, fabs(s_coef[j]));
+                if (max_change <= LASSO_TOL * max_abs) {
+                    const double y_sq_sum = yy - 2.0 * s_b * sy + Npts * s_b * s_b;
+                    double dual_norm = 0.0;
+                    for (int j = 0; j < F; ++j)
+                        if (s_cv[j] * y_sq_sum > 0.0)
+                            dual_norm = fmax(dual_norm, fabs(xt_res(j)) / s_cv[j] * y_sq_sum);
+                    double cGc = 0.0, cXy = 0.0, cXs = 0.0, pen = 0.0;
+                    for (int j = 0; j < F; ++j) {
+                        const int tj = feat_term(j);
+                        double row = 0.0;
+                        for (int k2 = 0; k2 < F; ++k2) row = fma(Gt[tj * KS + feat_term(k2)], s_coef[k2], row);
+                        cGc = fma(s_coef[j], row, cGc);
+                        cXy = fma(s_coef[j], Gt[tj * KS + tgt], cXy);
+                        cXs = fma(s_coef[j], Gt[tj * KS + T], cXs);
+                        pen += s_cv[j] * y_sq_sum * fabs(s_coef[j]);
+                    }
+                    const double b = s_b;
+                    const double rr = yy - 2.0 * cXy - 2.0 * b * sy + cGc + 2.0 * b * cXs + Npts * b * b;
+                    const double sum_r = sy - cXs - Npts * b;
+                    const double y_r = yy - cXy - b * sy;
+                    const double yb_r = y_r - b * sum_r;
+                    const double alpha = dual_norm > 1.0 ? 1.0 / dual_norm : 1.0;
+                    const double primal = 0.5 * rr + pen;
+                    const double dual = 0.5 * y_sq_sum - 0.5 * (y_sq_sum - 2.0 * alpha * yb_r + alpha * alpha * rr);
+                    if (primal - dual <= LASSO_TOL * (y_sq_sum / Npts)) break;
+                }
+                ++iteration;
+            }
+            if (refit) {
+                int nn = 0;
+                for (int j = 0; j < F; ++j)
+                    if (s_coef[j] != 0.0) cols[nn++] = feat_term(j);
+                cols[nn] = T;
+                s_n = nn + 1;
+                s_state = 1;
+                s_iter = 0;
+            } else {
+                s_state = 2;
+            }
+        }
+        __syncthreads();
+        if (s_state == 2) break;
+    }
+
+    // ---------------- outputs ----------------
+    if (tid == 0 && mode != 0) {
+        for (int j = 0; j < F; ++j) s_coef[j] = p.given_wterm[(long long)ev * TMAX + feat_term(j)];
+        s_b = p.given_b[ev];
+    }
+    __syncthreads();
+    const int n = (mode == 2) ? 0 : s_n;
+    for (int q = tid; q < W * KS; q += SOLVE_THREADS) {
+        const int c = q % KS;
+        p.sw[(long long)ev * W * KS + q] = (c < n) ? s_sw[q] : 0.0;
+    }
+    if (tid == 0) {
+        int nact = 0;
+        for (int j = 0; j < TMAX; ++j) {
+            const double cj = (j < F) ? s_coef[j] : 0.0;
+            p.coef[(long long)ev * TMAX + j] = cj;
+            if (cj != 0.0) ++nact;
+        }
+        for (int t = 0; t < TMAX; ++t) p.wterm[(long long)ev * TMAX + t] = 0.0;
+        for (int j = 0; j < F; ++j) p.wterm[(long long)ev * TMAX + feat_term(j)] = s_coef[j];
+        p.intercept[ev] = s_b;
+        p.n_active[ev] = nact;
+        p.all_zero[ev] = (nact == 0);
+        p.iters[ev] = s_sweeps;
+        // stability = sum(cv[:-1]) / ndim over the columns of the cached weights (fitness.py:160-169)
+        double st = 0.0;
+        for (int a = 0; a < n - 1; ++a) st += s_cvraw[a];
+        p.stability[ev] = (mode == 2) ? nan("") : st / p.g.ndim;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// pass B: residual sums per eval: sum|r|, sum|t|, sum r^2 with r = t - (F w + b)
+// (fitness.py:135-142 and 70-83).  One CTA handles a strip of points of ONE equation and all of
+// its evals (slot d = target term d), so the term columns are assembled once for all targets.
+// grid = (blocks_per_eq, n_eq_launch); partial sums per block, reduced in fixed order afterwards.
+// ------------------------------------------------------------------------------------------
+struct ResidParams {
+    Geom g;
+    const EqDesc* eqs;
+    const FactorDesc* factors;
+    const int* eq_list;
+    const int* slot_eval;    // [n_eq][TMAX] eval id of (equation, target term) or -1
+    const double* wterm;     // [n_eval][TMAX]
+    const double* intercept; // [n_eval]
+    double* partial;         // [n_eq_launch][gridDim.x][TMAX][3]
+    int points_per_block;
+};
+
+template <int T>
+__global__ void __launch_bounds__(256) residual_kernel(ResidParams p) {
+    __shared__ FactorDesc sf[T * FMAXF];
+    __shared__ int foff[T + 1];
+    __shared__ double sw_[T][T];
+    __shared__ double sb_[T];
+    __shared__ int s_slot[T];
+    __shared__ unsigned long long s_nz;
+    __shared__ unsigned int s_used, s_valid;
+    __shared__ double sred[8][T][3];
+
+    const int tid = threadIdx.x;
+    const int e = p.eq_list[blockIdx.y];
+    const EqDesc& eq = p.eqs[e];
+    const int fbase = eq.fac_off[0];
+    if (tid <= T) foff[tid] = eq.fac_off[tid] - fbase;
+    const int nfac = eq.fac_off[T] - fbase;
+    if (tid < nfac) sf[tid] = p.factors[fbase + tid];
+    if (tid < T) s_slot[tid] = p.slot_eval[e * TMAX + tid];
+    __syncthreads();
+    if (tid < T * T) {
+        const int d = tid / T, j = tid % T;
+        const int evd = s_slot[d];
+        sw_[d][j] = evd >= 0 ? p.wterm[(long long)evd * TMAX + j] : 0.0;
+        if (j == 0) sb_[d] = evd >= 0 ? p.intercept[evd] : 0.0;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        unsigned long long nz = 0ull;
+        unsigned int used = 0u, valid = 0u;
+        for (int d = 0; d < T; ++d) {
+            if (s_slot[d] < 0) continue;
+            valid |= 1u << d;
+            used |= 1u << d;
+            for (int j = 0; j < T; ++j)
+                if (sw_[d][j] != 0.0) { nz |= 1ull << (d * 8 + j); used |= 1u << j; }
+        }
+        s_nz = nz; s_used = used; s_valid = valid;
+    }
+    __syncthreads();
+    const unsigned long long nz = s_nz;
+    const unsigned int used = s_used, valid = s_valid;
+
+    double a1[T], a2[T], a3[T];
+#pragma unroll
+    for (int d = 0; d < T; ++d) { a1[d] = 0.0; a2[d] = 0.0; a3[d] = 0.0; }
+
+    const long long start = (long long)blockIdx.x * p.points_per_block;
+    long long stop = start + p.points_per_block;
+    if (stop > p.g.N) stop = p.g.N;
+    for (long long idx = start + tid; idx < stop; idx += 256) {
+        double c[T];
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            double v = 0.0;
+            if (used >> t & 1u) {
+                const int f0 = foff[t], f1 = foff[t + 1];
+                v = apply_factor(sf[f0], ld_stream(sf[f0].ptr + idx));
+                for (int f = f0 + 1; f < f1; ++f) v *= apply_factor(sf[f], ld_stream(sf[f].ptr + idx));
+            }
+            c[t] = v;
+        }
+#pragma unroll
+        for (int d = 0; d < T; ++d) {
+            if (valid >> d & 1u) {
+                // np.dot(features, w) + b, then target - that  (fitness.py:137-140)
+                double pred = 0.0;
+#pragma unroll
+                for (int j = 0; j < T; ++j)
+                    if (nz >> (d * 8 + j) & 1ull) pred = fma(sw_[d][j], c[j], pred);
+                const double r = c[d] - (pred + sb_[d]);
+                a1[d] += fabs(r);
+                a2[d] += fabs(c[d]);
+                a3[d] = fma(r, r, a3[d]);
+            }
+        }
+    }
+    // block reduction: warp shuffle then fixed-order sum over the 8 warps
+    const int lane = tid & 31, wp = tid >> 5;
+#pragma unroll
+    for (int d = 0; d < T; ++d) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            a1[d] += __shfl_down_sync(0xffffffffu, a1[d], off);
+            a2[d] += __shfl_down_sync(0xffffffffu, a2[d], off);
+            a3[d] += __shfl_down_sync(0xffffffffu, a3[d], off);
+        }
+        if (lane == 0) { sred[wp][d][0] = a1[d]; sred[wp][d][1] = a2[d]; sred[wp][d][2] = a3[d]; }
+    }
+    __syncthreads();
+    if (tid < T * 3) {
+        const int d = tid / 3, q = tid % 3;
+        double s = 0.0;
+#pragma unroll
+        for (int w8 = 0; w8 < 8; ++w8) s += sred[w8][d][q];
+        p.partial[(((long long)blockIdx.y * gridDim.x + blockIdx.x) * TMAX + d) * 3 + q] = s;
+    }
+}
+
+// fixed-order reduction of the per-block partial sums -> sums[eval][3]
+struct ResidFinalParams {
+    const int* eq_list;
+    const int* slot_eval;
+    const double* partial;
+    double* sums;
+    int blocks_per_eq;
+};
+
+__global__ void residual_final_kernel(ResidFinalParams p) {
+    const int le = blockIdx.x;
+    const int e = p.eq_list[le];
+    const int tid = threadIdx.x;          // TMAX*3 threads
+    if (tid >= TMAX * 3) return;
+    const int d = tid / 3, q = tid % 3;
+    const int ev = p.slot_eval[e * TMAX + d];
+    if (ev < 0) return;
+    double s = 0.0;
+    for (int b = 0; b < p.blocks_per_eq; ++b)
+        s += p.partial[(((long long)le * p.blocks_per_eq + b) * TMAX + d) * 3 + q];
+    p.sums[(long long)ev * 3 + q] = s;
+}
+
+// ------------------------------------------------------------------------------------------
+// host side: window plan (supplementary.py:411-425), contexts, batches
+// ------------------------------------------------------------------------------------------
+struct AxisPlan {
+    long long n_global = 0, offset = 0, n_local = 0;
+    long long window = 0, step = 1;
+    std::vector<long long> starts, bounds;     // global coordinates
+    std::vector<int> seg_lo, seg_hi;           // per window: segment range [lo, hi)
+    int nseg = 0;
+    // local cells: segments intersecting [offset, offset + n_local)
+    struct Cell { int seg; int lo, hi; };       // local index range
+    std::vector<Cell> cells;
+
+    void build(long long ng, long long off, long long nl) {
+        n_global = ng; offset = off; n_local = nl;
+        window = ng / 2;
+        const long long horizons = window + 1;
+        step = std::max<long long>(1, horizons / 30);
+        starts.clear();
+        for (long long s = 0; s < horizons; s += step) starts.push_back(s);
+        std::set<long long> edges;
+        edges.insert(0); edges.insert(ng);
+        for (long long s : starts) { edges.insert(s); edges.insert(s + window); }
+        bounds.assign(edges.begin(), edges.end());
+        nseg = (int)bounds.size() - 1;
+        std::map<long long, int> pos;
+        for (int i = 0; i < (int)bounds.size(); ++i) pos[bounds[i]] = i;
+        seg_lo.clear(); seg_hi.clear();
+        for (long long s : starts) { seg_lo.push_back(pos[s]); seg_hi.push_back(pos[s + window]); }
+        cells.clear();
+        for (int s = 0; s < nseg; ++s) {
+            const long long lo = std::max(bounds[s], off), hi = std::min(bounds[s + 1], off + nl);
+            if (hi > lo) cells.push_back({s, (int)(lo - off), (int)(hi - off)});
+        }
+    }
+};
+
+struct DevBuf {
+    void* ptr = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes) {
+        if (bytes <= cap) return 0;
+        if (ptr) { cudaFree(ptr); ptr = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&ptr, want);
+        if (e != cudaSuccess) {
+            ptr = nullptr;
+            return fail("cudaMalloc(%zu bytes) failed: %s", want, cudaGetErrorString(e));
+        }
+        cap = want;
+        return 0;
+    }
+    void release() { if (ptr) cudaFree(ptr); ptr = nullptr; cap = 0; }
+};
+
+struct epde_ctx {
+    int device = 0;
+    int ndim = 0;
+    long long shape[EPDE_MAX_NDIM] = {0, 0, 0};
+    long long N = 0;
+    cudaStream_t stream = 0;
+    std::map<int, double*> tokens;
+    AxisPlan axes[EPDE_MAX_NDIM];
+    bool geom_ready = false;
+    int BX = 256;
+    Geom geom;
+    int n_cells = 0;             // nA * nB * npieces
+    DevBuf d_geom;               // packed geometry tables
+    DevBuf d_cells, d_seg, d_enc, d_out, d_partial, d_given;
+    void* h_pinned = nullptr; size_t h_pinned_cap = 0;
+    epde_batch* live = nullptr;
+    long long launches = 0;
+    size_t cell_budget_bytes = (size_t)8 << 30;   // scratch cap for the cell Grams of one group
+    int sm_count = 148;
+};
+
+static int ensure_pinned(epde_ctx* c, size_t bytes) {
+    if (bytes <= c->h_pinned_cap) return 0;
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    c->h_pinned = nullptr; c->h_pinned_cap = 0;
+    CK(cudaMallocHost(&c->h_pinned, bytes + 4096));
+    c->h_pinned_cap = bytes + 4096;
+    return 0;
+}
+
+static int build_geometry(epde_ctx* c) {
+    const int nd = c->ndim;
+    // slot A / slot B = leading axes (dummy when absent), last axis = columns
+    const int last = nd - 1;
+    std::vector<AxisPlan::Cell> cellsA, cellsB;
+    long long strideA = 0, strideB = 0;
+    if (nd == 3) {
+        cellsA = c->axes[0].cells; cellsB = c->axes[1].cells;
+        strideA = c->shape[1] * c->shape[2]; strideB = c->shape[2];
+    } else if (nd == 2) {
+        cellsA = {{0, 0, 1}}; cellsB = c->axes[0].cells;
+        strideA = 0; strideB = c->shape[1];
+    } else {
+        cellsA = {{0, 0, 1}}; cellsB = {{0, 0, 1}};
+    }
+    const AxisPlan& lastp = c->axes[last];
+    const long long nl = c->shape[last];
+    c->BX = nl <= 64 ? 64 : (nl <= 128 ? 128 : 256);
+    const int BX = c->BX;
+    // pieces: sub-segments of the last axis no wider than BX
+    std::vector<int> piece_start, piece_seg;
+    for (auto& cl : lastp.cells) {
+        for (int lo = cl.lo; lo < cl.hi; lo += BX) { piece_start.push_back(lo); piece_seg.push_back(cl.seg); }
+    }
+    piece_start.push_back((int)nl);
+    const int npieces = (int)piece_seg.size();
+    // chunks: runs of pieces with total width <= BX
+    struct Chunk { int p_lo, np, col_lo, ncols; };
+    std::vector<Chunk> chunks;
+    for (int pI = 0; pI < npieces;) {
+        int q = pI;
+        while (q < npieces && piece_start[q + 1] - piece_start[pI] <= BX) ++q;
+        chunks.push_back({pI, q - pI, piece_start[pI], piece_start[q] - piece_start[pI]});
+        pI = q;
+    }
+    const int nA = (int)cellsA.size(), nB = (int)cellsB.size();
+    std::vector<UnitDesc> units;
+    units.reserve((size_t)nA * nB * chunks.size());
+    for (int a = 0; a < nA; ++a)
+        for (int b = 0; b < nB; ++b)
+            for (auto& ch : chunks) {
+                UnitDesc u;
+                memset(&u, 0, sizeof u);
+                u.a_lo = cellsA[a].lo; u.a_hi = cellsA[a].hi;
+                u.b_lo = cellsB[b].lo; u.b_hi = cellsB[b].hi;
+                u.col_lo = ch.col_lo; u.ncols = ch.ncols;
+                u.cell = a * nB + b;
+                u.piece_lo = ch.p_lo; u.npieces = ch.np;
+                units.push_back(u);
+            }
+    // segment rows: axes stacked; marginal descriptors
+    std::vector<int> axis_row_base(nd + 1, 0);
+    for (int d = 0; d < nd; ++d) axis_row_base[d + 1] = axis_row_base[d] + c->axes[d].nseg;
+    const int n_rows = axis_row_base[nd];
+    std::vector<MargDesc> marg(n_rows);
+    const long long Nloc = c->N;
+    for (int d = 0; d < nd; ++d) {
+        for (int s = 0; s < c->axes[d].nseg; ++s) {
+            MargDesc m;
+            memset(&m, 0, sizeof m);
+            m.row = axis_row_base[d] + s;
+            m.a_lo = 0; m.a_hi = nA; m.b_lo = 0; m.b_hi = nB; m.p_lo = 0; m.p_hi = npieces;
+            long long width = 0;
+            if (d == last) {
+                int lo = -1, hi = -1;
+                for (int q = 0; q < npieces; ++q)
+                    if (piece_seg[q] == s) { if (lo < 0) lo = q; hi = q + 1; width += piece_start[q + 1] - piece_start[q]; }
+                if (lo < 0) { m.p_lo = 0; m.p_hi = 0; } else { m.p_lo = lo; m.p_hi = hi; }
+            } else {
+                const bool isA = (nd == 3 && d == 0);
+                const std::vector<AxisPlan::Cell>& cl = isA ? cellsA : cellsB;
+                int lo = -1, hi = -1;
+                for (int q = 0; q < (int)cl.size(); ++q)
+                    if (cl[q].seg == s) { lo = q; hi = q + 1; width = cl[q].hi - cl[q].lo; }
+                if (lo < 0) { lo = 0; hi = 0; }
+                if (isA) { m.a_lo = lo; m.a_hi = hi; } else { m.b_lo = lo; m.b_hi = hi; }
+            }
+            m.count = (double)(width * (Nloc / c->shape[d]));
+            marg[m.row] = m;
+        }
+    }
+    // windows
+    std::vector<int> win_hi, win_lo;
+    for (int d = 0; d < nd; ++d)
+        for (size_t w = 0; w < c->axes[d].starts.size(); ++w) {
+            win_hi.push_back(axis_row_base[d] + c->axes[d].seg_hi[w] - 1);
+            win_lo.push_back(c->axes[d].seg_lo[w] > 0 ? axis_row_base[d] + c->axes[d].seg_lo[w] - 1 : -1);
+        }
+    // pack and upload
+    auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    size_t o_units = 0;
+    size_t o_piece = align(o_units + units.size() * sizeof(UnitDesc));
+    size_t o_marg = align(o_piece + piece_start.size() * sizeof(int));
+    size_t o_base = align(o_marg + marg.size() * sizeof(MargDesc));
+    size_t o_whi = align(o_base + axis_row_base.size() * sizeof(int));
+    size_t o_wlo = align(o_whi + win_hi.size() * sizeof(int));
+    size_t total = align(o_wlo + win_lo.size() * sizeof(int));
+    std::vector<char> host(total, 0);
+    memcpy(host.data() + o_units, units.data(), units.size() * sizeof(UnitDesc));
+    memcpy(host.data() + o_piece, piece_start.data(), piece_start.size() * sizeof(int));
+    memcpy(host.data() + o_marg, marg.data(), marg.size() * sizeof(MargDesc));
+    memcpy(host.data() + o_base, axis_row_base.data(), axis_row_base.size() * sizeof(int));
+    memcpy(host.data() + o_whi, win_hi.data(), win_hi.size() * sizeof(int));
+    memcpy(host.data() + o_wlo, win_lo.data(), win_lo.size() * sizeof(int));
+    if (c->d_geom.ensure(total)) return 1;
+    CK(cudaMemcpy(c->d_geom.ptr, host.data(), total, cudaMemcpyHostToDevice));
+    char* base = (char*)c->d_geom.ptr;
+    Geom& g = c->geom;
+    g.strideA = strideA; g.strideB = strideB;
+    g.nA = nA; g.nB = nB; g.npieces = npieces;
+    g.n_units = (int)units.size();
+    g.n_cells = nA * nB * npieces;
+    g.n_rows = n_rows;
+    g.n_windows = (int)win_hi.size();
+    g.ndim = nd;
+    g.total_row = axis_row_base[1] - 1;
+    g.N = c->N;
+    g.units = (const UnitDesc*)(base + o_units);
+    g.piece_start = (const int*)(base + o_piece);
+    g.marg = (const MargDesc*)(base + o_marg);
+    g.axis_row_base = (const int*)(base + o_base);
+    g.win_hi_row = (const int*)(base + o_whi);
+    g.win_lo_row = (const int*)(base + o_wlo);
+    c->n_cells = nA * nB * npieces;
+    c->geom_ready = true;
+    return 0;
+}
+
+struct epde_batch {
+    epde_ctx* ctx = nullptr;
+    int n_eq = 0, n_eval = 0, n_fac = 0;
+    std::vector<EqDesc> eqs;
+    std::vector<std::vector<int>> eq_by_T;      // index T -> equation ids
+    std::vector<int> evals_gs8, evals_gs16;
+    // device pointers into ctx->d_enc
+    EqDesc* d_eqs = nullptr;
+    FactorDesc* d_factors = nullptr;
+    int* d_eval_eq = nullptr; int* d_eval_tgt = nullptr; int* d_slot_eval = nullptr;
+    int* d_lists = nullptr;                      // eq lists by T, eval lists by GS
+    std::vector<int> list_off_T;                 // offsets into d_lists
+    int off_gs8 = 0, off_gs16 = 0;
+    // outputs in ctx->d_out
+    double* d_coef = nullptr; double* d_intercept = nullptr; double* d_stab = nullptr;
+    double* d_sw = nullptr; double* d_wterm = nullptr; double* d_sums = nullptr;
+    int* d_nact = nullptr; int* d_allzero = nullptr; int* d_iters = nullptr;
+    size_t out_bytes = 0;
+    long long seg_doubles = 0;
+    int* d_mode = nullptr; double* d_given_w = nullptr; double* d_given_b = nullptr;
+    bool solved = false;
+};
+
+template <int T>
+static int launch_gram(epde_ctx* c, epde_batch* b, const int* d_list, int n_eq, double* cells) {
+    GramParams p;
+    p.g = c->geom; p.eqs = b->d_eqs; p.factors = b->d_factors; p.eq_list = d_list; p.n_eq = n_eq; p.cells = cells;
+    const size_t smem = sizeof(double) * RED_CHUNK * (c->BX + 1);
+    const long long grid = (long long)c->geom.n_units * n_eq;
+    if (grid > 2147483647LL) return fail("pass A grid too large (%lld CTAs)", grid);
+    gram_cells_kernel<T><<<(unsigned)grid, c->BX, smem, c->stream>>>(p);
+    c->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+static int dispatch_gram(int T, epde_ctx* c, epde_batch* b, const int* d_list, int n_eq, double* cells) {
+    switch (T) {
+        case 1: return launch_gram<1>(c, b, d_list, n_eq, cells);
+        case 2: return launch_gram<2>(c, b, d_list, n_eq, cells);
+        case 3: return launch_gram<3>(c, b, d_list, n_eq, cells);
+        case 4: return launch_gram<4>(c, b, d_list, n_eq, cells);
+        case 5: return launch_gram<5>(c, b, d_list, n_eq, cells);
+        case 6: return launch_gram<6>(c, b, d_list, n_eq, cells);
+        case 7: return launch_gram<7>(c, b, d_list, n_eq, cells);
+        case 8: return launch_gram<8>(c, b, d_list, n_eq, cells);
+    }
+    return fail("unsupported term count %d", T);
+}
+
+template <int T>
+static int launch_resid(epde_ctx* c, epde_batch* b, const int* d_list, int n_eq, double* sums) {
+    // enough CTAs to fill the machine a few times over, at least 64K points each on big grids
+    long long bpe = (c->N + 65535) / 65536;
+    const long long want = std::max<long long>(1, (long long)c->sm_count * 8 / std::max(1, n_eq));
+    bpe = std::max<long long>(1, std::min<long long>(bpe, std::max<long long>(want, 1)));
+    if (bpe > 65535) bpe = 65535;
+    long long ppb = (c->N + bpe - 1) / bpe;
+    ppb = (ppb + 255) / 256 * 256;
+    bpe = (c->N + ppb - 1) / ppb;
+    if (c->d_partial.ensure(sizeof(double) * (size_t)n_eq * bpe * TMAX * 3)) return 1;
+    ResidParams p;
+    p.g = c->geom; p.eqs = b->d_eqs; p.factors = b->d_factors; p.eq_list = d_list; p.slot_eval = b->d_slot_eval;
+    p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.partial = (double*)c->d_partial.ptr;
+    p.points_per_block = (int)ppb;
+    residual_kernel<T><<<dim3((unsigned)bpe, n_eq), 256, 0, c->stream>>>(p);
+    c->launches++;
+    CK(cudaGetLastError());
+    ResidFinalParams fp;
+    fp.eq_list = d_list; fp.slot_eval = b->d_slot_eval; fp.partial = (const double*)c->d_partial.ptr; fp.sums = sums;
+    fp.blocks_per_eq = (int)bpe;
+    residual_final_kernel<<<n_eq, 32, 0, c->stream>>>(fp);
+    c->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* epde_last_error(void) { return g_err.c_str(); }
+const char* epde_version(void) { return "epde_b200 0.1.0 sm_100a"; }
+
+int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx** out) {
+    if (!out || !inner_shape) return fail("epde_ctx_create: null argument");
+    if (ndim < 1 || ndim > EPDE_MAX_NDIM) return fail("epde_ctx_create: ndim %d not in [1, %d]", ndim, EPDE_MAX_NDIM);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail("epde_ctx_create: no CUDA device available (%s); this engine has no CPU fallback",
+                    cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail("epde_ctx_create: device %d out of range (%d devices)", device, ndev);
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    epde_ctx* c = new epde_ctx();
+    c->device = device;
+    c->ndim = ndim;
+    c->sm_count = prop.multiProcessorCount;
+    c->N = 1;
+    for (int d = 0; d < ndim; ++d) {
+        if (inner_shape[d] < 2) { delete c; return fail("epde_ctx_create: axis %d has %lld points (< 2)", d, (long long)inner_shape[d]); }
+        c->shape[d] = inner_shape[d];
+        c->N *= inner_shape[d];
+    }
+    for (int d = 0; d < ndim; ++d) c->axes[d].build(c->shape[d], 0, c->shape[d]);
+    if (build_geometry(c)) { delete c; return 1; }
+    *out = c;
+    return 0;
+}
+
+int epde_ctx_destroy(epde_ctx* c) {
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    for (auto& kv : c->tokens) cudaFree(kv.second);
+    c->d_geom.release(); c->d_cells.release(); c->d_seg.release(); c->d_enc.release();
+    c->d_out.release(); c->d_partial.release(); c->d_given.release();
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    if (c->live) { c->live->ctx = nullptr; }
+    delete c;
+    return 0;
+}
+
+int epde_ctx_set_stream(epde_ctx* c, void* s) {
+    if (!c) return fail("null context");
+    c->stream = (cudaStream_t)s;
+    return 0;
+}
+
+int epde_ctx_set_shard(epde_ctx* c, int64_t off, int64_t glob) {
+    if (!c) return fail("null context");
+    if (c->ndim < 2) return fail("epde_ctx_set_shard: grid sharding needs ndim >= 2");
+    if (off < 0 || off + c->shape[0] > glob) return fail("epde_ctx_set_shard: rows [%lld, %lld) outside global axis of %lld",
+                                                        (long long)off, (long long)(off + c->shape[0]), (long long)glob);
+    CK(cudaSetDevice(c->device));
+    c->axes[0].build(glob, off, c->shape[0]);
+    return build_geometry(c);
+}
+
+int epde_cache_upload(epde_ctx* c, int id, const double* host, int64_t n) {
+    if (!c || !host) return fail("epde_cache_upload: null argument");
+    if (n != c->N) return fail("epde_cache_upload: token %d has %lld values, context expects %lld", id, (long long)n, c->N);
+    if (id < 0 || id >= EPDE_MAX_TOKENS) return fail("epde_cache_upload: token id %d out of range", id);
+    CK(cudaSetDevice(c->device));
+    double*& p = c->tokens[id];
+    if (!p) {
+        cudaError_t e = cudaMalloc((void**)&p, sizeof(double) * (size_t)n);
+        if (e != cudaSuccess) { c->tokens.erase(id); return fail("epde_cache_upload: out of device memory (%s)", cudaGetErrorString(e)); }
+    }
+    CK(cudaMemcpyAsync(p, host, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int epde_cache_upload_device(epde_ctx* c, int id, const double* dev, int64_t n) {
+    if (!c || !dev) return fail("epde_cache_upload_device: null argument");
+    if (n != c->N) return fail("epde_cache_upload_device: token %d has %lld values, context expects %lld", id, (long long)n, c->N);
+    if (id < 0 || id >= EPDE_MAX_TOKENS) return fail("epde_cache_upload_device: token id %d out of range", id);
+    CK(cudaSetDevice(c->device));
+    double*& p = c->tokens[id];
+    if (!p) {
+        cudaError_t e = cudaMalloc((void**)&p, sizeof(double) * (size_t)n);
+        if (e != cudaSuccess) { c->tokens.erase(id); return fail("epde_cache_upload_device: out of device memory (%s)", cudaGetErrorString(e)); }
+    }
+    CK(cudaMemcpyAsync(p, dev, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, c->stream));
+    return 0;
+}
+
+int epde_cache_download(epde_ctx* c, int id, double* host, int64_t n) {
+    if (!c || !host) return fail("epde_cache_download: null argument");
+    auto it = c->tokens.find(id);
+    if (it == c->tokens.end()) return fail("epde_cache_download: token %d not in cache", id);
+    if (n != c->N) return fail("epde_cache_download: size mismatch");
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(host, it->second, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int epde_cache_contains(epde_ctx* c, int id, int* present) {
+    if (!c || !present) return fail("null argument");
+    *present = c->tokens.count(id) ? 1 : 0;
+    return 0;
+}
+
+int epde_cache_delete(epde_ctx* c, int id) {
+    if (!c) return fail("null context");
+    auto it = c->tokens.find(id);
+    if (it == c->tokens.end()) return fail("epde_cache_delete: token %d not in cache", id);
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    cudaFree(it->second);
+    c->tokens.erase(it);
+    return 0;
+}
+
+int epde_cache_bytes(epde_ctx* c, int64_t* bytes) {
+    if (!c || !bytes) return fail("null argument");
+    *bytes = (int64_t)c->tokens.size() * c->N * (int64_t)sizeof(double);
+    return 0;
+}
+
+int epde_ctx_set_sample_weights(epde_ctx* c, const double* host, int64_t n) {
+    if (!c || !host) return fail("null argument");
+    if (n != c->N) return fail("epde_ctx_set_sample_weights: size mismatch");
+    for (int64_t i = 0; i < n; ++i)
+        if (host[i] != 1.0)
+            return fail("epde_ctx_set_sample_weights: only the default all-ones g_func mask is supported "
+                        "(value %g at %lld); non-trivial sample weights are not implemented", host[i], (long long)i);
+    return 0;
+}
+
+int epde_ctx_num_windows(epde_ctx* c, int* w) {
+    if (!c || !w) return fail("null argument");
+    *w = c->geom.n_windows;
+    return 0;
+}
+
+int epde_ctx_num_segments(epde_ctx* c, int* s) {
+    if (!c || !s) return fail("null argument");
+    *s = c->geom.n_rows;
+    return 0;
+}
+
+int epde_ctx_launch_count(epde_ctx* c, int64_t* l) {
+    if (!c || !l) return fail("null argument");
+    *l = c->launches;
+    return 0;
+}
+
+int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int32_t* fac_off,
+                      const int32_t* fac_token, const double* fac_power, const int32_t* fac_kind,
+                      const double* fac_param, int n_eval, const int32_t* eval_eq,
+                      const int32_t* eval_target, epde_batch** out) {
+    if (!c || !term_off || !fac_off || !fac_token || !fac_power || !out) return fail("epde_batch_create: null argument");
+    if (n_eq <= 0) return fail("epde_batch_create: empty batch");
+    if (n_eval < 0 || (n_eval > 0 && (!eval_eq || !eval_target))) return fail("epde_batch_create: bad eval list");
+    if (c->live) return fail("epde_batch_create: another batch is live on this context");
+    CK(cudaSetDevice(c->device));
+    epde_batch* b = new epde_batch();
+    b->ctx = c; b->n_eq = n_eq; b->n_eval = n_eval;
+    const int n_terms = term_off[n_eq];
+    b->n_fac = fac_off[n_terms];
+    std::vector<FactorDesc> factors(b->n_fac);
+    b->eqs.resize(n_eq);
+    b->eq_by_T.assign(TMAX + 1, {});
+    long long s_off = 0;
+    for (int e = 0; e < n_eq; ++e) {
+        const int T = term_off[e + 1] - term_off[e];
+        if (T < 1 || T > TMAX) { delete b; return fail("equation %d has %d terms; supported: 1..%d", e, T, TMAX); }
+        EqDesc& q = b->eqs[e];
+        memset(&q, 0, sizeof q);
+        q.T = T;
+        for (int t = 0; t <= T; ++t) q.fac_off[t] = fac_off[term_off[e] + t];
+        for (int t = 0; t < T; ++t) {
+            const int nf = q.fac_off[t + 1] - q.fac_off[t];
+            if (nf < 1 || nf > FMAXF) { delete b; return fail("equation %d term %d has %d factors; supported: 1..%d", e, t, nf, FMAXF); }
+        }
+        q.s_off = s_off;
+        s_off += (long long)c->geom.n_rows * (nacc_of(T) + 1);
+        b->eq_by_T[T].push_back(e);
+    }
+    b->seg_doubles = s_off;
+    for (int f = 0; f < b->n_fac; ++f) {
+        auto it = c->tokens.find(fac_token[f]);
+        if (it == c->tokens.end()) { delete b; return fail("factor %d references token %d which is not in the cache", f, fac_token[f]); }
+        FactorDesc& d = factors[f];
+        d.ptr = it->second;
+        d.power = fac_power[f];
+        d.kind = fac_kind ? fac_kind[f] : 0;
+        d.param = fac_param ? fac_param[f] : 0.0;
+        if (d.kind < 0 || d.kind > 3) { delete b; return fail("factor %d has unknown kind %d", f, d.kind); }
+        d.ipow = (d.power == 1.0) ? 1 : (d.power == 2.0) ? 2 : (d.power == 3.0) ? 3 : 0;
+    }
+    std::vector<int> slot_eval((size_t)n_eq * TMAX, -1);
+    for (int v = 0; v < n_eval; ++v) {
+        const int e = eval_eq[v], t = eval_target[v];
+        if (e < 0 || e >= n_eq) { delete b; return fail("eval %d references equation %d", v, e); }
+        if (t < 0 || t >= b->eqs[e].T) { delete b; return fail("eval %d: target %d outside equation %d (%d terms)", v, t, e, b->eqs[e].T); }
+        if (slot_eval[(size_t)e * TMAX + t] >= 0) { delete b; return fail("eval %d duplicates (equation %d, target %d)", v, e, t); }
+        slot_eval[(size_t)e * TMAX + t] = v;
+        if (b->eqs[e].T + 1 <= 8) b->evals_gs8.push_back(v); else b->evals_gs16.push_back(v);
+    }
+    // lists: equations by T, evals by group size
+    std::vector<int> lists;
+    b->list_off_T.assign(TMAX + 2, 0);
+    for (int T = 1; T <= TMAX; ++T) {
+        b->list_off_T[T] = (int)lists.size();
+        lists.insert(lists.end(), b->eq_by_T[T].begin(), b->eq_by_T[T].end());
+    }
+    b->off_gs8 = (int)lists.size();
+    lists.insert(lists.end(), b->evals_gs8.begin(), b->evals_gs8.end());
+    b->off_gs16 = (int)lists.size();
+    lists.insert(lists.end(), b->evals_gs16.begin(), b->evals_gs16.end());
+    if (lists.empty()) lists.push_back(0);
+    // pack the encoding into one pinned staging buffer -> one H2D copy
+    auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    const size_t o_eqs = 0;
+    const size_t o_fac = align(o_eqs + sizeof(EqDesc) * n_eq);
+    const size_t o_eveq = align(o_fac + sizeof(FactorDesc) * std::max(1, b->n_fac));
+    const size_t o_evtg = align(o_eveq + sizeof(int) * std::max(1, n_eval));
+    const size_t o_slot = align(o_evtg + sizeof(int) * std::max(1, n_eval));
+    const size_t o_list = align(o_slot + sizeof(int) * slot_eval.size());
+    const size_t total = align(o_list + sizeof(int) * lists.size());
+    if (ensure_pinned(c, total) || c->d_enc.ensure(total)) { delete b; return 1; }
+    char* h = (char*)c->h_pinned;
+    memcpy(h + o_eqs, b->eqs.data(), sizeof(EqDesc) * n_eq);
+    memcpy(h + o_fac, factors.data(), sizeof(FactorDesc) * b->n_fac);
+    if (n_eval) { memcpy(h + o_eveq, eval_eq, sizeof(int) * n_eval); memcpy(h + o_evtg, eval_target, sizeof(int) * n_eval); }
+    memcpy(h + o_slot, slot_eval.data(), sizeof(int) * slot_eval.size());
+    memcpy(h + o_list, lists.data(), sizeof(int) * lists.size());
+    cudaError_t ce = cudaMemcpyAsync(c->d_enc.ptr, h, total, cudaMemcpyHostToDevice, c->stream);
+    if (ce != cudaSuccess) { delete b; return fail("encoding upload failed: %s", cudaGetErrorString(ce)); }
+    char* d = (char*)c->d_enc.ptr;
+    b->d_eqs = (EqDesc*)(d + o_eqs);
+    b->d_factors = (FactorDesc*)(d + o_fac);
+    b->d_eval_eq = (int*)(d + o_eveq);
+    b->d_eval_tgt = (int*)(d + o_evtg);
+    b->d_slot_eval = (int*)(d + o_slot);
+    b->d_lists = (int*)(d + o_list);
+    // outputs
+    const int W = c->geom.n_windows;
+    const size_t ne = (size_t)std::max(1, n_eval);
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o = align(o + bytes); return r; };
+    const size_t oc = take(ne * TMAX * 8), oi = take(ne * 8), ost = take(ne * 8), osw = take(ne * W * KS * 8),
+                 owt = take(ne * TMAX * 8), osu = take(ne * 3 * 8), ona = take(ne * 4), oaz = take(ne * 4), oit = take(ne * 4);
+    b->out_bytes = o;
+    if (c->d_out.ensure(o)) { delete b; return 1; }
+    char* od = (char*)c->d_out.ptr;
+    b->d_coef = (double*)(od + oc); b->d_intercept = (double*)(od + oi); b->d_stab = (double*)(od + ost);
+    b->d_sw = (double*)(od + osw); b->d_wterm = (double*)(od + owt); b->d_sums = (double*)(od + osu);
+    b->d_nact = (int*)(od + ona); b->d_allzero = (int*)(od + oaz); b->d_iters = (int*)(od + oit);
+    c->live = b;
+    *out = b;
+    return 0;
+}
+
+int epde_batch_destroy(epde_batch* b) {
+    if (!b) return 0;
+    if (b->ctx) {
+        cudaSetDevice(b->ctx->device);
+        cudaStreamSynchronize(b->ctx->stream);
+        if (b->ctx->live == b) b->ctx->live = nullptr;
+    }
+    delete b;
+    return 0;
+}
+
+int epde_batch_set_given(epde_batch* b, const int32_t* mode, const double* wterm, const double* intercept) {
+    if (!b || !b->ctx || !mode || !wterm || !intercept) return fail("epde_batch_set_given: null argument");
+    epde_ctx* c = b->ctx;
+    CK(cudaSetDevice(c->device));
+    const size_t ne = (size_t)std::max(1, b->n_eval);
+    auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    const size_t o_w = align(ne * sizeof(int)), o_b = align(o_w + ne * TMAX * 8), total = align(o_b + ne * 8);
+    for (int v = 0; v < b->n_eval; ++v)
+        if (mode[v] < 0 || mode[v] > 2) return fail("epde_batch_set_given: eval %d has mode %d", v, mode[v]);
+    if (c->d_given.ensure(total)) return 1;
+    char* d = (char*)c->d_given.ptr;
+    // pageable sources: the runtime stages them before returning, so the caller may reuse them
+    CK(cudaMemcpyAsync(d, mode, sizeof(int) * b->n_eval, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(d + o_w, wterm, sizeof(double) * b->n_eval * TMAX, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(d + o_b, intercept, sizeof(double) * b->n_eval, cudaMemcpyHostToDevice, c->stream));
+    b->d_mode = (int*)d; b->d_given_w = (double*)(d + o_w); b->d_given_b = (double*)(d + o_b);
+    return 0;
+}
+
+int epde_batch_gram_size(epde_batch* b, int64_t* n) {
+    if (!b || !n) return fail("null argument");
+    *n = b->seg_doubles;
+    return 0;
+}
+
+int epde_batch_residual_size(epde_batch* b, int64_t* n) {
+    if (!b || !n) return fail("null argument");
+    *n = (int64_t)std::max(1, b->n_eval) * 3;
+    return 0;
+}
+
+int epde_batch_gram(epde_batch* b, double* dev_seg) {
+    if (!b || !b->ctx) return fail("null batch");
+    epde_ctx* c = b->ctx;
+    CK(cudaSetDevice(c->device));
+    if (!dev_seg) {
+        if (c->d_seg.ensure(sizeof(double) * (size_t)b->seg_doubles)) return 1;
+        dev_seg = (double*)c->d_seg.ptr;
+    }
+    // equations are processed in groups (same T) whose cell Grams fit the scratch budget
+    for (int T = 1; T <= TMAX; ++T) {
+        const std::vector<int>& lst = b->eq_by_T[T];
+        if (lst.empty()) continue;
+        const size_t per_eq = sizeof(double) * (size_t)c->n_cells * nacc_of(T);
+        int group = (int)std::max<size_t>(1, c->cell_budget_bytes / per_eq);
+        group = std::min<int>(group, (int)lst.size());
+        if (c->d_cells.ensure(per_eq * group)) return 1;
+        for (int g0 = 0; g0 < (int)lst.size(); g0 += group) {
+            const int ng = std::min<int>(group, (int)lst.size() - g0);
+            // cell Grams of the group's i-th equation start at i * n_cells * NACC
+            const int* d_list = b->d_lists + b->list_off_T[T] + g0;
+            if (dispatch_gram(T, c, b, d_list, ng, (double*)c->d_cells.ptr)) return 1;
+            MargParams mp;
+            mp.g = c->geom; mp.eqs = b->d_eqs; mp.eq_list = d_list; mp.cells = (const double*)c->d_cells.ptr; mp.seg = dev_seg;
+            dim3 grid(c->geom.n_rows, ng);
+            marginal_kernel<<<grid, 256, 0, c->stream>>>(mp);
+            c->launches++;
+            CK(cudaGetLastError());
+        }
+    }
+    return 0;
+}
+
+int epde_batch_solve(epde_batch* b, const double* dev_seg) {
+    if (!b || !b->ctx) return fail("null batch");
+    epde_ctx* c = b->ctx;
+    CK(cudaSetDevice(c->device));
+    double* seg = dev_seg ? (double*)dev_seg : (double*)c->d_seg.ptr;
+    if (!seg) return fail("epde_batch_solve: no segment Grams (call epde_batch_gram first)");
+    PrefixParams pp;
+    pp.g = c->geom; pp.eqs = b->d_eqs; pp.n_eq = b->n_eq; pp.seg = seg;
+    prefix_kernel<<<dim3(c->ndim, b->n_eq), 64, 0, c->stream>>>(pp);
+    c->launches++;
+    CK(cudaGetLastError());
+    if (b->n_eval > 0) {
+        SolveParams sp;
+        sp.g = c->geom; sp.eqs = b->d_eqs; sp.eval_eq = b->d_eval_eq; sp.eval_tgt = b->d_eval_tgt; sp.seg = seg;
+        sp.mode = b->d_mode; sp.given_wterm = b->d_given_w; sp.given_b = b->d_given_b;
+        sp.coef = b->d_coef; sp.intercept = b->d_intercept; sp.stability = b->d_stab; sp.sw = b->d_sw;
+        sp.wterm = b->d_wterm; sp.n_active = b->d_nact; sp.all_zero = b->d_allzero; sp.iters = b->d_iters;
+        const size_t smem = sizeof(double) * (size_t)c->geom.n_windows * KS;
+        if (!b->evals_gs8.empty()) {
+            sp.eval_list = b->d_lists + b->off_gs8;
+            lasso_solve_kernel<8><<<(unsigned)b->evals_gs8.size(), SOLVE_THREADS, smem, c->stream>>>(sp);
+            c->launches++;
+            CK(cudaGetLastError());
+        }
+        if (!b->evals_gs16.empty()) {
+            sp.eval_list = b->d_lists + b->off_gs16;
+            lasso_solve_kernel<16><<<(unsigned)b->evals_gs16.size(), SOLVE_THREADS, smem, c->stream>>>(sp);
+            c->launches++;
+            CK(cudaGetLastError());
+        }
+    }
+    b->solved = true;
+    return 0;
+}
+
+int epde_batch_residual(epde_batch* b, double* dev_sums) {
+    if (!b || !b->ctx) return fail("null batch");
+    if (!b->solved) return fail("epde_batch_residual: call epde_batch_solve first");
+    epde_ctx* c = b->ctx;
+    CK(cudaSetDevice(c->device));
+    double* sums = dev_sums ? dev_sums : b->d_sums;
+    if (b->n_eval == 0) return 0;
+    for (int T = 1; T <= TMAX; ++T) {
+        const std::vector<int>& lst = b->eq_by_T[T];
+        if (lst.empty()) continue;
+        const int* d_list = b->d_lists + b->list_off_T[T];
+        int rc = 0;
+        switch (T) {
+            case 1: rc = launch_resid<1>(c, b, d_list, (int)lst.size(), sums); break;
+            case 2: rc = launch_resid<2>(c, b, d_list, (int)lst.size(), sums); break;
+            case 3: rc = launch_resid<3>(c, b, d_list, (int)lst.size(), sums); break;
+            case 4: rc = launch_resid<4>(c, b, d_list, (int)lst.size(), sums); break;
+            case 5: rc = launch_resid<5>(c, b, d_list, (int)lst.size(), sums); break;
+            case 6: rc = launch_resid<6>(c, b, d_list, (int)lst.size(), sums); break;
+            case 7: rc = launch_resid<7>(c, b, d_list, (int)lst.size(), sums); break;
+            case 8: rc = launch_resid<8>(c, b, d_list, (int)lst.size(), sums); break;
+        }
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int epde_batch_fetch(epde_batch* b, const double* dev_sums, double* coef, double* intercept,
+                     double* fitness_l1, double* fitness_l2, double* stability, double* sw_weights,
+                     int32_t* n_active, int32_t* all_zero, int32_t* iters) {
+    if (!b || !b->ctx) return fail("null batch");
+    epde_ctx* c = b->ctx;
+    CK(cudaSetDevice(c->device));
+    const int ne = b->n_eval;
+    if (ne == 0) { CK(cudaStreamSynchronize(c->stream)); return 0; }
+    if (dev_sums && dev_sums != b->d_sums)
+        CK(cudaMemcpyAsync(b->d_sums, dev_sums, sizeof(double) * 3 * ne, cudaMemcpyDeviceToDevice, c->stream));
+    // the pinned buffer doubles as the encoding staging area; the encoding copy is complete once
+    // the stream reaches this point, so synchronise before reallocating / overwriting it
+    CK(cudaStreamSynchronize(c->stream));
+    if (ensure_pinned(c, std::max(b->out_bytes, (size_t)1))) return 1;
+    CK(cudaMemcpyAsync(c->h_pinned, c->d_out.ptr, b->out_bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    const char* h = (const char*)c->h_pinned;
+    const char* d0 = (const char*)c->d_out.ptr;
+    auto hp = [&](const void* dptr) { return h + ((const char*)dptr - d0); };
+    const int W = c->geom.n_windows;
+    if (coef) memcpy(coef, hp(b->d_coef), sizeof(double) * ne * TMAX);
+    if (intercept) memcpy(intercept, hp(b->d_intercept), sizeof(double) * ne);
+    if (stability) memcpy(stability, hp(b->d_stab), sizeof(double) * ne);
+    if (sw_weights) memcpy(sw_weights, hp(b->d_sw), sizeof(double) * (size_t)ne * W * KS);
+    if (n_active) memcpy(n_active, hp(b->d_nact), sizeof(int) * ne);
+    if (all_zero) memcpy(all_zero, hp(b->d_allzero), sizeof(int) * ne);
+    if (iters) memcpy(iters, hp(b->d_iters), sizeof(int) * ne);
+    const double* sums = (const double*)hp(b->d_sums);
+    for (int v = 0; v < ne; ++v) {
+        if (fitness_l1) fitness_l1[v] = sums[3 * v] / sums[3 * v + 1];
+        if (fitness_l2) fitness_l2[v] = std::sqrt(sums[3 * v + 2]);
+    }
+    return 0;
+}
+
+int epde_evaluate_batch(epde_ctx* c, int n_eq, const int32_t* term_off, const int32_t* fac_off,
+                        const int32_t* fac_token, const double* fac_power, const int32_t* fac_kind,
+                        const double* fac_param, int n_eval, const int32_t* eval_eq,
+                        const int32_t* eval_target, double* coef, double* intercept,
+                        double* fitness_l1, double* fitness_l2, double* stability, double* sw_weights,
+                        int32_t* n_active, int32_t* all_zero, int32_t* iters) {
+    epde_batch* b = nullptr;
+    if (epde_batch_create(c, n_eq, term_off, fac_off, fac_token, fac_power, fac_kind, fac_param,
+                          n_eval, eval_eq, eval_target, &b)) return 1;
+    int rc = epde_batch_gram(b, nullptr);
+    if (!rc) rc = epde_batch_solve(b, nullptr);
+    if (!rc) rc = epde_batch_residual(b, nullptr);
+    if (!rc) rc = epde_batch_fetch(b, nullptr, coef, intercept, fitness_l1, fitness_l2, stability,
+                                   sw_weights, n_active, all_zero, iters);
+    std::string keep = g_err;
+    epde_batch_destroy(b);
+    if (rc) g_err = keep;
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,162 @@
+/* epde_b200.h -- C ABI of the B200-native EPDE fitness-evaluation engine.
+ *
+ * The reference (ITMO-NSS-team/EPDE, pure Python) has no FFI; its boundary for this path is the
+ * Python operator / cache API.  Each entry point below names the reference
+ * interface it replaces (paths relative to the reference root).  The Python shims in
+ * epde_b200/ (ctypes) are the only callers.
+ *
+ * Conventions: every function returns 0 on success, non-zero on failure (never throws, never
+ * aborts); epde_last_error() gives the message of the last failure on the calling thread.
+ * Caller owns all host buffers; the library owns device memory unless a parameter is named
+ * dev_*.  One CUDA stream per context (epde_ctx_set_stream), every call that returns data to host
+ * buffers is synchronous at the call boundary; the staged epde_batch_* calls are asynchronous on
+ * the context stream.  One context per process per device (the reference is single threaded with
+ * module-global caches: epde/globals.py:26-42).  All arithmetic is IEEE float64.
+ *
+ * Equation encoding (CSR):  equation e owns terms [term_off[e], term_off[e+1]);  term t owns
+ * factors [fac_off[t], fac_off[t+1]);  factor f = (fac_token[f], fac_power[f], fac_kind[f],
+ * fac_param[f]):
+ *     kind 0: token ** power               epde/evaluators.py:92-135  simple_function_evaluator
+ *     kind 1: sin(param * token) ** power  epde/evaluators.py:141-142 trig_eval_fun_np['sin']
+ *     kind 2: cos(param * token) ** power  epde/evaluators.py:141     trig_eval_fun_np['cos']
+ *     kind 3: token ** (-power)            epde/evaluators.py:147     inverse_eval_fun_np
+ * A term is the product of its factors (epde/structure/structure_template.py:49-58,
+ * epde/structure/main_structures.py:207-235 with structural=False).
+ * An "eval" is one (equation, target term) pair = one LASSOSparsity.apply + L2LRFitness.apply
+ * (force_out_of_place=True) of the reference (operators/common/sparsity.py:178-211,
+ * operators/common/fitness.py:105-150).
+ */
+#ifndef EPDE_B200_H
+#define EPDE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EPDE_MAX_NDIM 3
+#define EPDE_MAX_TERMS 8      /* terms per equation handled by the register-resident Gram kernels */
+#define EPDE_MAX_FACTORS 4    /* factors per term */
+#define EPDE_MAX_TOKENS 4096
+
+typedef struct epde_ctx epde_ctx;
+typedef struct epde_batch epde_batch;
+
+/* message of the last failing call on this thread ("" if none). */
+const char* epde_last_error(void);
+/* library / build identification: "epde_b200 <version> sm_100a". */
+const char* epde_version(void);
+
+/* ---- token cache ---------------------------------------------------------------------------
+ * Replaces epde/cache/cache.py:141-524 (class Cache) for the tensors the evaluator reads, and
+ * Cache.set_boundaries / inner_shape (cache.py:250-270): the context is created for one inner
+ * grid shape (C order, time axis first), N = prod(inner_shape) points per token vector. */
+int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx** out);
+int epde_ctx_destroy(epde_ctx* ctx);
+/* cudaStream_t to run on (0 = legacy default stream).  torch callers pass
+ * torch.cuda.current_stream().cuda_stream so kernels order with NCCL collectives. */
+int epde_ctx_set_stream(epde_ctx* ctx, void* cuda_stream);
+/* Grid-point sharding: this context holds rows [axis0_offset,
+ * axis0_offset + inner_shape[0]) of a global time axis of length axis0_global.  The sliding
+ * windows of supplementary.py:411-425 are laid out on the GLOBAL axis.  Default: offset 0,
+ * global = inner_shape[0]. */
+int epde_ctx_set_shard(epde_ctx* ctx, int64_t axis0_offset, int64_t axis0_global);
+/* Cache.add (cache.py:333-395): store / overwrite token `token_id` from a host vector of n = N
+ * doubles.  Unlike the reference there is no tensor-count budget: the call fails with an
+ * out-of-memory status instead of silently refusing. */
+int epde_cache_upload(epde_ctx* ctx, int token_id, const double* host, int64_t n);
+/* same, from a device vector (device-to-device copy on the context stream). */
+int epde_cache_upload_device(epde_ctx* ctx, int token_id, const double* dev, int64_t n);
+/* Cache.get (cache.py:397-452): copy the token back to a host vector. */
+int epde_cache_download(epde_ctx* ctx, int token_id, double* host, int64_t n);
+/* Cache.__contains__ (cache.py:454-470): *present = 1/0. */
+int epde_cache_contains(epde_ctx* ctx, int token_id, int* present);
+/* Cache.delete_entry (cache.py:472-490). */
+int epde_cache_delete(epde_ctx* ctx, int token_id);
+/* Cache.consumed_memory (cache.py:305-330): bytes of HBM held by token vectors. */
+int epde_cache_bytes(epde_ctx* ctx, int64_t* bytes);
+/* sample weights of the window regressions = g_func[g_func_mask] (cache.py:219-244,
+ * sparsity.py:202).  Only the default all-ones mask (interface.py:540-545) is supported by the
+ * kernels in this version: any other vector fails loudly. */
+int epde_ctx_set_sample_weights(epde_ctx* ctx, const double* host, int64_t n);
+
+/* ---- geometry of the sliding windows (supplementary.py:411-425) ----------------------------- */
+/* total number of windows W over all axes (rows of calculate_weights' result). */
+int epde_ctx_num_windows(epde_ctx* ctx, int* n_windows);
+/* total number of segments over all axes (rows of the per-equation segment-Gram table). */
+int epde_ctx_num_segments(epde_ctx* ctx, int* n_segments);
+
+/* ---- evaluation -----------------------------------------------------------------------------
+ * epde_evaluate_batch = the whole path for a batch of evals, host buffers in and out:
+ *   Equation.evaluate (main_structures.py:588-641) -> calculate_weights (supplementary.py:394-471)
+ *   -> PhysicsInformedLasso.fit (sparsity.py:42-150) -> LASSOSparsity.apply outputs
+ *   (sparsity.py:205-211) -> L2LRFitness.apply (fitness.py:105-174) and L2Fitness.apply
+ *   (fitness.py:54-96) values.
+ * Outputs, one row per eval, strides in doubles given by the constants above:
+ *   coef      [n_eval * EPDE_MAX_TERMS]  weights_internal: feature j of the eval = j-th term of
+ *                                         the equation skipping the target (zero padded)
+ *   intercept [n_eval]                    PhysicsInformedLasso.intercept_
+ *   fitness_l1[n_eval]                    sum|t - Fw - b| / sum|t|   (fitness.py:142); computed
+ *                                         also when all coefficients vanish (the reference
+ *                                         returns None there: see all_zero)
+ *   fitness_l2[n_eval]                    ||Fw + b - t||_2           (fitness.py:78-83, g == 1)
+ *   stability [n_eval]                    sum_j CV_j / ndim of the cached window weights
+ *                                         (fitness.py:160-169)
+ *   sw_weights[n_eval * W * (EPDE_MAX_TERMS+1)] cached_weights_: row w holds n_active[e]+1 values
+ *                                         (active features in order, then the intercept), rest 0
+ *   n_active  [n_eval]                    number of non-zero coefficients
+ *   all_zero  [n_eval]                    1 when every coefficient is zero (fitness.py:123 -> None)
+ *   iters     [n_eval]                    (diagnostic) coordinate-descent sweeps executed
+ * Any output pointer may be NULL.                                                              */
+int epde_evaluate_batch(epde_ctx* ctx,
+                        int n_eq, const int32_t* term_off, const int32_t* fac_off,
+                        const int32_t* fac_token, const double* fac_power,
+                        const int32_t* fac_kind, const double* fac_param,
+                        int n_eval, const int32_t* eval_eq, const int32_t* eval_target,
+                        double* coef, double* intercept, double* fitness_l1, double* fitness_l2,
+                        double* stability, double* sw_weights, int32_t* n_active,
+                        int32_t* all_zero, int32_t* iters);
+
+/* Staged form of the same path, for grid-sharded multi-GPU runs: the
+ * caller all-reduces (sum, float64) the two device buffers between the stages.
+ *   epde_batch_create      upload the encoding
+ *   epde_batch_gram        pass A: fused term assembly + per-segment Gram -> dev_seg (device,
+ *                          epde_batch_gram_size doubles).  dev_seg == NULL: internal buffer.
+ *   epde_batch_solve       window solves + LASSO from (all-reduced) segment Grams
+ *   epde_batch_residual    pass B: residual sums -> dev_sums (device, epde_batch_residual_size
+ *                          doubles; 3 per eval: sum|r|, sum|t|, sum r^2).  NULL: internal buffer.
+ *   epde_batch_fetch       synchronise and copy results to host (same layout as above); reads
+ *                          the residual sums from dev_sums (or the internal buffer if NULL).  */
+int epde_batch_create(epde_ctx* ctx,
+                      int n_eq, const int32_t* term_off, const int32_t* fac_off,
+                      const int32_t* fac_token, const double* fac_power,
+                      const int32_t* fac_kind, const double* fac_param,
+                      int n_eval, const int32_t* eval_eq, const int32_t* eval_target,
+                      epde_batch** out);
+int epde_batch_destroy(epde_batch* b);
+/* In-place fitness of equations whose weights are already known (L2LRFitness.apply /
+ * L2Fitness.apply with force_out_of_place=False, fitness.py:70-96,130-174).  Call between
+ * epde_batch_create and epde_batch_solve.  Per eval: mode 0 = LASSO (default); 1 = use the given
+ * coefficients, still solve the sliding windows on ALL features for the stability objective
+ * (fitness.py:155-169 without cached weights); 2 = given coefficients only (stability = NaN).
+ * wterm[n_eval * EPDE_MAX_TERMS]: coefficient per TERM index of the equation (target and absent
+ * terms 0); intercept[n_eval]. */
+int epde_batch_set_given(epde_batch* b, const int32_t* mode, const double* wterm,
+                         const double* intercept);
+int epde_batch_gram_size(epde_batch* b, int64_t* n_doubles);
+int epde_batch_residual_size(epde_batch* b, int64_t* n_doubles);
+int epde_batch_gram(epde_batch* b, double* dev_seg);
+int epde_batch_solve(epde_batch* b, const double* dev_seg);
+int epde_batch_residual(epde_batch* b, double* dev_sums);
+int epde_batch_fetch(epde_batch* b, const double* dev_sums,
+                     double* coef, double* intercept, double* fitness_l1, double* fitness_l2,
+                     double* stability, double* sw_weights, int32_t* n_active,
+                     int32_t* all_zero, int32_t* iters);
+/* number of kernel launches issued by the library on this context since creation. */
+int epde_ctx_launch_count(epde_ctx* ctx, int64_t* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EPDE_B200_H */
