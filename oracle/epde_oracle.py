@@ -269,6 +269,18 @@ def calc_weights_gram(win_grams, feat_idx, y_idx):
     return np.linalg.solve(A, b[..., None])[..., 0]
 
 
+def window_condition(win_grams, feat_idx):
+    """max over windows of cond(D A D), A = ridge system of the columns ``feat_idx``,
+    D = diag(A)^-1/2.  Tests use it to tell well-posed evals (result determined by the data) from
+    windows that are singular up to the 1e-6 ridge, where the reference's own answer is rounding
+    noise of its BLAS summation order (e.g. burgers_b50 eval 5: last x-window, scaled cond 8e15,
+    reference and any restatement are both 100 % off the extended-precision solution)."""
+    idx = np.asarray(feat_idx, dtype=np.int64)
+    A = win_grams[:, idx[:, None], idx[None, :]] + RIDGE * np.eye(len(idx))
+    d = 1.0 / np.sqrt(np.abs(np.diagonal(A, axis1=1, axis2=2)))
+    return float(np.max(np.linalg.cond(A * d[:, :, None] * d[:, None, :])))
+
+
 def lasso_fit_gram(win_grams, total_gram, feat_cols, y_col, max_iter=MAX_ITER, tol=TOL):
     """PhysicsInformedLasso.fit (sparsity.py:42-150) driven only by Gram quantities.
 
@@ -397,7 +409,7 @@ class EvalResult:
     """What the reference leaves on the Equation after LASSOSparsity + L2LRFitness
     (sparsity.py:205-211, fitness.py:142-174)."""
     __slots__ = ('target', 'coef', 'intercept', 'sw_weights', 'fitness', 'fitness_l2',
-                 'stability', 'all_zero')
+                 'stability', 'all_zero', 'cond')
 
     def as_dict(self):
         return {k: getattr(self, k) for k in self.__slots__}
@@ -432,6 +444,7 @@ def evaluate_equation(tokens, grid_shape, equation, targets=None, sample_weights
         else:
             coef, b, cached = lasso_fit_direct(cols[:, feat], cols[:, tgt], g, plan.shape)
         r = EvalResult()
+        r.cond = window_condition(win, feat + [T], ) if method == 'gram' else float('nan')
         r.target = tgt
         r.coef = coef
         r.intercept = float(b)
