@@ -43,6 +43,8 @@ SIGNATURES = {
     'epde_batch_residual': (C.c_int, [vp, vp]),
     'epde_batch_fetch': (C.c_int, [vp, vp] + _OUT),
     'epde_ctx_launch_count': (C.c_int, [vp, c_i64p]),
+    'epde_ctx_set_timing': (C.c_int, [vp, C.c_int]),
+    'epde_ctx_kernel_time': (C.c_int, [vp, C.c_int, c_f64p, c_i64p]),
 }
 
 _lib = None

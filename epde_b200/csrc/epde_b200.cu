@@ -320,6 +320,8 @@ struct SolveParams {
     // outputs (per eval)
     double* coef;            // [n_eval][TMAX]   feature order
     double* intercept;       // [n_eval]
+    double* intercept_l1;    // [n_eval] offset used by the L1 fitness: intercept, or mean(target) when no
+                             //          feature survives (fitness.py:135-136 'features is None')
     double* stability;       // [n_eval]
     double* sw;              // [n_eval][W][KS]
     double* wterm;           // [n_eval][TMAX]   coefficient per TERM index (0 for target / inactive)
@@ -577,6 +579,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
         for (int t = 0; t < TMAX; ++t) p.wterm[(long long)ev * TMAX + t] = 0.0;
         for (int j = 0; j < F; ++j) p.wterm[(long long)ev * TMAX + feat_term(j)] = s_coef[j];
         p.intercept[ev] = s_b;
+        p.intercept_l1[ev] = (nact == 0) ? Gt[tgt * KS + T] / Gt[T * KS + T] : s_b;
         p.n_active[ev] = nact;
         p.all_zero[ev] = (nact == 0);
         p.iters[ev] = s_sweeps;
@@ -601,6 +604,7 @@ struct ResidParams {
     const int* slot_eval;    // [n_eq][TMAX] eval id of (equation, target term) or -1
     const double* wterm;     // [n_eval][TMAX]
     const double* intercept; // [n_eval]
+    const double* intercept_l1;  // [n_eval]
     double* partial;         // [n_eq_launch][gridDim.x][TMAX][3]
     int points_per_block;
 };
@@ -610,7 +614,7 @@ __global__ void __launch_bounds__(256) residual_kernel(ResidParams p) {
     __shared__ FactorDesc sf[T * FMAXF];
     __shared__ int foff[T + 1];
     __shared__ double sw_[T][T];
-    __shared__ double sb_[T];
+    __shared__ double sb_[T], sdb_[T];
     __shared__ int s_slot[T];
     __shared__ unsigned long long s_nz;
     __shared__ unsigned int s_used, s_valid;
@@ -629,7 +633,10 @@ __global__ void __launch_bounds__(256) residual_kernel(ResidParams p) {
         const int d = tid / T, j = tid % T;
         const int evd = s_slot[d];
         sw_[d][j] = evd >= 0 ? p.wterm[(long long)evd * TMAX + j] : 0.0;
-        if (j == 0) sb_[d] = evd >= 0 ? p.intercept[evd] : 0.0;
+        if (j == 0) {
+            sb_[d] = evd >= 0 ? p.intercept_l1[evd] : 0.0;
+            sdb_[d] = evd >= 0 ? p.intercept_l1[evd] - p.intercept[evd] : 0.0;
+        }
     }
     __syncthreads();
     if (tid == 0) {
@@ -676,9 +683,10 @@ __global__ void __launch_bounds__(256) residual_kernel(ResidParams p) {
                 for (int j = 0; j < T; ++j)
                     if (nz >> (d * 8 + j) & 1ull) pred = fma(sw_[d][j], c[j], pred);
                 const double r = c[d] - (pred + sb_[d]);
+                const double r2 = r + sdb_[d];       // L2Fitness keeps the LASSO intercept (fitness.py:80)
                 a1[d] += fabs(r);
                 a2[d] += fabs(c[d]);
-                a3[d] = fma(r, r, a3[d]);
+                a3[d] = fma(r2, r2, a3[d]);
             }
         }
     }
@@ -801,7 +809,48 @@ struct epde_ctx {
     long long launches = 0;
     size_t cell_budget_bytes = (size_t)8 << 30;   // scratch cap for the cell Grams of one group
     int sm_count = 148;
+    // optional per-kernel-class device timing (epde_ctx_set_timing)
+    bool timing = false;
+    struct Span { int cls; cudaEvent_t a, b; };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> free_events;
+    double class_ms[EPDE_N_KERNEL_CLASSES] = {0, 0, 0, 0};
+    long long class_launches[EPDE_N_KERNEL_CLASSES] = {0, 0, 0, 0};
 };
+
+static cudaEvent_t take_event(epde_ctx* c) {
+    cudaEvent_t e = nullptr;
+    if (!c->free_events.empty()) { e = c->free_events.back(); c->free_events.pop_back(); }
+    else cudaEventCreate(&e);
+    return e;
+}
+
+// RAII bracket of one kernel launch: two event records on the context stream when timing is on
+struct KernelSpan {
+    epde_ctx* c; int cls; cudaEvent_t a = nullptr;
+    KernelSpan(epde_ctx* c_, int cls_) : c(c_), cls(cls_) {
+        c->launches++;
+        if (c->timing) { a = take_event(c); cudaEventRecord(a, c->stream); }
+    }
+    ~KernelSpan() {
+        if (a) { cudaEvent_t b = take_event(c); cudaEventRecord(b, c->stream); c->spans.push_back({cls, a, b}); }
+    }
+};
+
+static int drain_spans(epde_ctx* c) {
+    if (c->spans.empty()) return 0;
+    CK(cudaStreamSynchronize(c->stream));
+    for (auto& sp : c->spans) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, sp.a, sp.b));
+        c->class_ms[sp.cls] += ms;
+        c->class_launches[sp.cls]++;
+        c->free_events.push_back(sp.a);
+        c->free_events.push_back(sp.b);
+    }
+    c->spans.clear();
+    return 0;
+}
 
 static int ensure_pinned(epde_ctx* c, size_t bytes) {
     if (bytes <= c->h_pinned_cap) return 0;
@@ -955,7 +1004,7 @@ struct epde_batch {
     int off_gs8 = 0, off_gs16 = 0;
     // outputs in ctx->d_out
     double* d_coef = nullptr; double* d_intercept = nullptr; double* d_stab = nullptr;
-    double* d_sw = nullptr; double* d_wterm = nullptr; double* d_sums = nullptr;
+    double* d_sw = nullptr; double* d_wterm = nullptr; double* d_sums = nullptr; double* d_b1 = nullptr;
     int* d_nact = nullptr; int* d_allzero = nullptr; int* d_iters = nullptr;
     size_t out_bytes = 0;
     long long seg_doubles = 0;
@@ -970,8 +1019,7 @@ static int launch_gram(epde_ctx* c, epde_batch* b, const int* d_list, int n_eq, 
     const size_t smem = sizeof(double) * RED_CHUNK * (c->BX + 1);
     const long long grid = (long long)c->geom.n_units * n_eq;
     if (grid > 2147483647LL) return fail("pass A grid too large (%lld CTAs)", grid);
-    gram_cells_kernel<T><<<(unsigned)grid, c->BX, smem, c->stream>>>(p);
-    c->launches++;
+    { KernelSpan ks(c, EPDE_KERNEL_GRAM); gram_cells_kernel<T><<<(unsigned)grid, c->BX, smem, c->stream>>>(p); }
     CK(cudaGetLastError());
     return 0;
 }
@@ -1003,16 +1051,14 @@ static int launch_resid(epde_ctx* c, epde_batch* b, const int* d_list, int n_eq,
     if (c->d_partial.ensure(sizeof(double) * (size_t)n_eq * bpe * TMAX * 3)) return 1;
     ResidParams p;
     p.g = c->geom; p.eqs = b->d_eqs; p.factors = b->d_factors; p.eq_list = d_list; p.slot_eval = b->d_slot_eval;
-    p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.partial = (double*)c->d_partial.ptr;
+    p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.intercept_l1 = b->d_b1; p.partial = (double*)c->d_partial.ptr;
     p.points_per_block = (int)ppb;
-    residual_kernel<T><<<dim3((unsigned)bpe, n_eq), 256, 0, c->stream>>>(p);
-    c->launches++;
+    { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_kernel<T><<<dim3((unsigned)bpe, n_eq), 256, 0, c->stream>>>(p); }
     CK(cudaGetLastError());
     ResidFinalParams fp;
     fp.eq_list = d_list; fp.slot_eval = b->d_slot_eval; fp.partial = (const double*)c->d_partial.ptr; fp.sums = sums;
     fp.blocks_per_eq = (int)bpe;
-    residual_final_kernel<<<n_eq, 32, 0, c->stream>>>(fp);
-    c->launches++;
+    { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_final_kernel<<<n_eq, 32, 0, c->stream>>>(fp); }
     CK(cudaGetLastError());
     return 0;
 }
@@ -1061,6 +1107,8 @@ int epde_ctx_destroy(epde_ctx* c) {
     c->d_geom.release(); c->d_cells.release(); c->d_seg.release(); c->d_enc.release();
     c->d_out.release(); c->d_partial.release(); c->d_given.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    for (auto& sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+    for (auto& ev : c->free_events) cudaEventDestroy(ev);
     if (c->live) { c->live->ctx = nullptr; }
     delete c;
     return 0;
@@ -1173,6 +1221,25 @@ int epde_ctx_launch_count(epde_ctx* c, int64_t* l) {
     return 0;
 }
 
+int epde_ctx_set_timing(epde_ctx* c, int enabled) {
+    if (!c) return fail("null context");
+    CK(cudaSetDevice(c->device));
+    if (drain_spans(c)) return 1;
+    c->timing = enabled != 0;
+    for (int k = 0; k < EPDE_N_KERNEL_CLASSES; ++k) { c->class_ms[k] = 0.0; c->class_launches[k] = 0; }
+    return 0;
+}
+
+int epde_ctx_kernel_time(epde_ctx* c, int cls, double* ms, int64_t* launches) {
+    if (!c) return fail("null context");
+    if (cls < 0 || cls >= EPDE_N_KERNEL_CLASSES) return fail("epde_ctx_kernel_time: unknown kernel class %d", cls);
+    CK(cudaSetDevice(c->device));
+    if (drain_spans(c)) return 1;
+    if (ms) *ms = c->class_ms[cls];
+    if (launches) *launches = c->class_launches[cls];
+    return 0;
+}
+
 int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int32_t* fac_off,
                       const int32_t* fac_token, const double* fac_power, const int32_t* fac_kind,
                       const double* fac_param, int n_eval, const int32_t* eval_eq,
@@ -1269,12 +1336,12 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align(o + bytes); return r; };
     const size_t oc = take(ne * TMAX * 8), oi = take(ne * 8), ost = take(ne * 8), osw = take(ne * W * KS * 8),
-                 owt = take(ne * TMAX * 8), osu = take(ne * 3 * 8), ona = take(ne * 4), oaz = take(ne * 4), oit = take(ne * 4);
+                 owt = take(ne * TMAX * 8), osu = take(ne * 3 * 8), ob1 = take(ne * 8), ona = take(ne * 4), oaz = take(ne * 4), oit = take(ne * 4);
     b->out_bytes = o;
     if (c->d_out.ensure(o)) { delete b; return 1; }
     char* od = (char*)c->d_out.ptr;
     b->d_coef = (double*)(od + oc); b->d_intercept = (double*)(od + oi); b->d_stab = (double*)(od + ost);
-    b->d_sw = (double*)(od + osw); b->d_wterm = (double*)(od + owt); b->d_sums = (double*)(od + osu);
+    b->d_sw = (double*)(od + osw); b->d_wterm = (double*)(od + owt); b->d_sums = (double*)(od + osu); b->d_b1 = (double*)(od + ob1);
     b->d_nact = (int*)(od + ona); b->d_allzero = (int*)(od + oaz); b->d_iters = (int*)(od + oit);
     c->live = b;
     *out = b;
@@ -1347,8 +1414,7 @@ int epde_batch_gram(epde_batch* b, double* dev_seg) {
             MargParams mp;
             mp.g = c->geom; mp.eqs = b->d_eqs; mp.eq_list = d_list; mp.cells = (const double*)c->d_cells.ptr; mp.seg = dev_seg;
             dim3 grid(c->geom.n_rows, ng);
-            marginal_kernel<<<grid, 256, 0, c->stream>>>(mp);
-            c->launches++;
+            { KernelSpan ks(c, EPDE_KERNEL_MARGINAL); marginal_kernel<<<grid, 256, 0, c->stream>>>(mp); }
             CK(cudaGetLastError());
         }
     }
@@ -1363,26 +1429,23 @@ int epde_batch_solve(epde_batch* b, const double* dev_seg) {
     if (!seg) return fail("epde_batch_solve: no segment Grams (call epde_batch_gram first)");
     PrefixParams pp;
     pp.g = c->geom; pp.eqs = b->d_eqs; pp.n_eq = b->n_eq; pp.seg = seg;
-    prefix_kernel<<<dim3(c->ndim, b->n_eq), 64, 0, c->stream>>>(pp);
-    c->launches++;
+    { KernelSpan ks(c, EPDE_KERNEL_MARGINAL); prefix_kernel<<<dim3(c->ndim, b->n_eq), 64, 0, c->stream>>>(pp); }
     CK(cudaGetLastError());
     if (b->n_eval > 0) {
         SolveParams sp;
         sp.g = c->geom; sp.eqs = b->d_eqs; sp.eval_eq = b->d_eval_eq; sp.eval_tgt = b->d_eval_tgt; sp.seg = seg;
         sp.mode = b->d_mode; sp.given_wterm = b->d_given_w; sp.given_b = b->d_given_b;
-        sp.coef = b->d_coef; sp.intercept = b->d_intercept; sp.stability = b->d_stab; sp.sw = b->d_sw;
+        sp.coef = b->d_coef; sp.intercept = b->d_intercept; sp.intercept_l1 = b->d_b1; sp.stability = b->d_stab; sp.sw = b->d_sw;
         sp.wterm = b->d_wterm; sp.n_active = b->d_nact; sp.all_zero = b->d_allzero; sp.iters = b->d_iters;
         const size_t smem = sizeof(double) * (size_t)c->geom.n_windows * KS;
         if (!b->evals_gs8.empty()) {
             sp.eval_list = b->d_lists + b->off_gs8;
-            lasso_solve_kernel<8><<<(unsigned)b->evals_gs8.size(), SOLVE_THREADS, smem, c->stream>>>(sp);
-            c->launches++;
+            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<8><<<(unsigned)b->evals_gs8.size(), SOLVE_THREADS, smem, c->stream>>>(sp); }
             CK(cudaGetLastError());
         }
         if (!b->evals_gs16.empty()) {
             sp.eval_list = b->d_lists + b->off_gs16;
-            lasso_solve_kernel<16><<<(unsigned)b->evals_gs16.size(), SOLVE_THREADS, smem, c->stream>>>(sp);
-            c->launches++;
+            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<16><<<(unsigned)b->evals_gs16.size(), SOLVE_THREADS, smem, c->stream>>>(sp); }
             CK(cudaGetLastError());
         }
     }

@@ -212,6 +212,21 @@ class Engine:
         _lib.check(self._lib.epde_ctx_launch_count(self._h, C.byref(r)))
         return int(r.value)
 
+    # ---- measurement aid (include/epde_b200.h epde_ctx_set_timing)
+    KERNEL_CLASSES = ('gram', 'marginal', 'solve', 'residual')
+
+    def set_timing(self, enabled=True):
+        _lib.check(self._lib.epde_ctx_set_timing(self._h, int(bool(enabled))))
+
+    def kernel_times(self):
+        """{class: (summed device ms, launches)} since timing was enabled (synchronises)."""
+        out = {}
+        for k, name in enumerate(self.KERNEL_CLASSES):
+            ms, n = C.c_double(0), C.c_int64(0)
+            _lib.check(self._lib.epde_ctx_kernel_time(self._h, k, C.byref(ms), C.byref(n)))
+            out[name] = (ms.value, int(n.value))
+        return out
+
     # ---- evaluation
     def evaluate(self, enc: Encoding, want_sw=True) -> BatchResult:
         """Whole path, host buffers in/out, synchronous."""

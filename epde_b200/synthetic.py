@@ -1,0 +1,150 @@
+"""Seeded synthetic workloads of BASELINE.json's configs.
+
+Fields are analytic solutions on uniform grids (boundary 0, so inner shape == grid shape); the
+tokens are u and its analytic derivatives up to order 2 per axis, as the reference would hold them
+in its tensor cache after ``create_pool(..., derivs=...)`` (interface/interface.py:133-155), plus
+Gaussian noise.  Populations follow the reference scripts: 1-2 factors per term with probabilities
+(0.8, 0.2) (examples/wave_equation_multiobjective.py:114), powers <= 3, every equation holding at
+least one derivative term, a mix of fresh (T = 5..8) and pruned (T = 2..4) equations as observed in
+a MOEADD run (SURVEY.md section 8d 'observed workload shape').
+
+Works on numpy arrays (CPU, tests / CPU baseline) or torch tensors (GPU, bench) through the tiny
+``xp`` shim; nothing here is on the evaluator's hot path.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+CONFIGS = {
+    # name: (shape, population, kind)
+    'wave61': ((61, 61), 8, 'wave'),            # stand-in of config 1's size (real data lives in tests/golden)
+    'burgers156': ((156, 156), 16, 'wave'),     # config 2's inner size
+    'wave1024': ((1024, 1024), 64, 'wave'),     # config 3
+    'heat256': ((256, 256, 256), 256, 'heat'),  # config 4
+    'heat512': ((512, 512, 512), 128, 'heat'),  # config 5
+    'heat64': ((64, 64, 64), 32, 'heat'),       # small stand-ins for tests / CPU baselines
+    'heat128': ((128, 128, 128), 32, 'heat'),
+}
+
+
+def token_labels(kind):
+    if kind == 'wave':
+        return ['u', 'du/dx0', 'd^2u/dx0^2', 'du/dx1', 'd^2u/dx1^2']
+    return ['u', 'du/dx0', 'd^2u/dx0^2', 'du/dx1', 'd^2u/dx1^2', 'du/dx2', 'd^2u/dx2^2']
+
+
+def _axes(xp, shape, kind, lo_hi, dev):
+    axes = []
+    for n, (lo, hi) in zip(shape, lo_hi):
+        if xp is np:
+            axes.append(np.linspace(lo, hi, n))
+        else:
+            axes.append(xp.linspace(lo, hi, n, dtype=xp.float64, device=dev))
+    return axes
+
+
+def make_tokens(shape, kind, xp=np, device=None, noise=1e-3, seed=0, axis0_range=None):
+    """list of flat float64 token vectors (C order) in token_labels(kind) order.
+
+    axis0_range=(lo, hi): only rows [lo, hi) of the time axis (grid-point sharding); the noise
+    stream is keyed by (seed, token, global row) so shards reproduce the unsharded field."""
+    shape = tuple(shape)
+    lo0, hi0 = (0, shape[0]) if axis0_range is None else axis0_range
+    pi = float(np.pi)
+    if kind == 'wave':
+        c = 0.2
+        t, x = _axes(xp, shape, kind, [(0.0, 1.0), (0.0, 1.0)], device)
+        t = t[lo0:hi0]
+        T, X = t[:, None], x[None, :]
+        s1, c1 = xp.sin(pi * X), xp.cos(pi * X)
+        s2, c2 = xp.sin(2 * pi * X), xp.cos(2 * pi * X)
+        a1, b1 = xp.cos(c * pi * T), xp.sin(c * pi * T)
+        a2, b2 = xp.cos(2 * c * pi * T), xp.sin(2 * c * pi * T)
+        toks = [s1 * a1 + 0.5 * s2 * a2,
+                -c * pi * s1 * b1 - c * pi * s2 * b2,
+                -(c * pi) ** 2 * s1 * a1 - 2 * (c * pi) ** 2 * s2 * a2,
+                pi * c1 * a1 + pi * c2 * a2,
+                -pi ** 2 * s1 * a1 - 2 * pi ** 2 * s2 * a2]
+    elif kind == 'heat':
+        k = 0.5
+        t, x, y = _axes(xp, shape, kind, [(0.0, 1.0), (0.0, pi), (0.0, pi)], device)
+        t = t[lo0:hi0]
+        T, X, Y = t[:, None, None], x[None, :, None], y[None, None, :]
+        e1, e2 = xp.exp(-2 * k * T), 0.3 * xp.exp(-5 * k * T)
+        sx, cx, s2x, c2x = xp.sin(X), xp.cos(X), xp.sin(2 * X), xp.cos(2 * X)
+        sy, cy = xp.sin(Y), xp.cos(Y)
+        toks = [e1 * sx * sy + e2 * s2x * sy,
+                -2 * k * e1 * sx * sy - 5 * k * e2 * s2x * sy,
+                4 * k * k * e1 * sx * sy + 25 * k * k * e2 * s2x * sy,
+                e1 * cx * sy + 2 * e2 * c2x * sy,
+                -e1 * sx * sy - 4 * e2 * s2x * sy,
+                e1 * sx * cy + e2 * s2x * cy,
+                -e1 * sx * sy - e2 * s2x * sy]
+    else:
+        raise ValueError(kind)
+    out = []
+    row = int(np.prod(shape[1:]))
+    if noise:
+        # noise amplitude from a coarse copy of the GLOBAL field, so every shard uses the same one
+        coarse = make_tokens(tuple(min(n, 33) for n in shape), kind, noise=0.0)
+    for i, tk in enumerate(toks):
+        tk = tk.reshape(-1)
+        if noise:
+            scale = noise * float(coarse[i].std())
+            if xp is np:
+                nz = np.empty(tk.shape[0])
+                for r in range(lo0, hi0):
+                    nz[(r - lo0) * row:(r - lo0 + 1) * row] = \
+                        np.random.default_rng([seed, i, r]).standard_normal(row)
+                tk = tk + scale * nz
+            else:
+                g = xp.Generator(device=device)
+                g.manual_seed(seed * 1000003 + i * 7919 + lo0)
+                tk = tk + scale * xp.randn(tk.shape[0], dtype=xp.float64, device=device, generator=g)
+        out.append(tk.contiguous() if xp is not np else np.ascontiguousarray(tk))
+    return out
+
+
+def make_population(n_tokens, pop, seed=0, t_fresh=(5, 8), t_pruned=(2, 4), pruned_fraction=0.45,
+                    max_power=3):
+    """pop equations as nested lists [[(token, power, 0, 0.0), ...] per term].  Token 0 is u, the
+    others derivatives; an admissible target is a term with exactly one derivative factor
+    (right_part_selection.py:60-63 'contains a derivative of the main variable')."""
+    rng = np.random.default_rng(seed)
+    eqs = []
+    while len(eqs) < pop:
+        lo, hi = t_pruned if rng.random() < pruned_fraction else t_fresh
+        T = int(rng.integers(lo, hi + 1))
+        terms, seen = [], set()
+        tries = 0
+        while len(terms) < T and tries < 500:
+            tries += 1
+            nf = 1 if rng.random() < 0.8 else 2
+            chosen = rng.choice(n_tokens, size=nf, replace=False)
+            term = []
+            for c in chosen:
+                pmax = max_power if c == 0 else 2
+                p = int(rng.integers(1, pmax + 1)) if rng.random() < 0.3 else 1
+                term.append((int(c), float(p), 0, 0.0))
+            key = frozenset(term)
+            if key in seen:
+                continue
+            seen.add(key)
+            terms.append(term)
+        if len(terms) == T and admissible_targets(terms):
+            eqs.append(terms)
+    return eqs
+
+
+def admissible_targets(eq):
+    return [i for i, term in enumerate(eq) if sum(1 for f in term if f[0] != 0) == 1]
+
+
+def make_evals(eqs):
+    """every admissible (equation, target) pair: the D evals EqRightPartSelector runs per equation
+    (right_part_selection.py:60-74)."""
+    return [(e, t) for e, eq in enumerate(eqs) for t in admissible_targets(eq)]
+
+
+def distinct_tokens(eq):
+    return len({f[0] for term in eq for f in term})

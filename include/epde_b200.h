@@ -97,9 +97,10 @@ int epde_ctx_num_segments(epde_ctx* ctx, int* n_segments);
  *   coef      [n_eval * EPDE_MAX_TERMS]  weights_internal: feature j of the eval = j-th term of
  *                                         the equation skipping the target (zero padded)
  *   intercept [n_eval]                    PhysicsInformedLasso.intercept_
- *   fitness_l1[n_eval]                    sum|t - Fw - b| / sum|t|   (fitness.py:142); computed
- *                                         also when all coefficients vanish (the reference
- *                                         returns None there: see all_zero)
+ *   fitness_l1[n_eval]                    sum|t - Fw - b| / sum|t|   (fitness.py:142); when all
+ *                                         coefficients vanish: sum|t - mean(t)| / sum|t|
+ *                                         (fitness.py:135-136, 'features is None'; the
+ *                                         out-of-place call returns None there: see all_zero)
  *   fitness_l2[n_eval]                    ||Fw + b - t||_2           (fitness.py:78-83, g == 1)
  *   stability [n_eval]                    sum_j CV_j / ndim of the cached window weights
  *                                         (fitness.py:160-169)
@@ -155,6 +156,18 @@ int epde_batch_fetch(epde_batch* b, const double* dev_sums,
                      int32_t* all_zero, int32_t* iters);
 /* number of kernel launches issued by the library on this context since creation. */
 int epde_ctx_launch_count(epde_ctx* ctx, int64_t* launches);
+
+/* Measurement aid (no reference counterpart): with timing enabled every kernel launch is bracketed
+ * by two CUDA events recorded on the context stream; epde_ctx_kernel_time synchronises the stream
+ * and returns the summed device time (ms) and launch count of one kernel class since timing was
+ * last enabled.  Enabling / disabling resets the sums. */
+#define EPDE_KERNEL_GRAM 0       /* pass A: fused term assembly + Gram */
+#define EPDE_KERNEL_MARGINAL 1   /* segment / window Gram reductions */
+#define EPDE_KERNEL_SOLVE 2      /* window solves + LASSO */
+#define EPDE_KERNEL_RESIDUAL 3   /* pass B: residual sums */
+#define EPDE_N_KERNEL_CLASSES 4
+int epde_ctx_set_timing(epde_ctx* ctx, int enabled);
+int epde_ctx_kernel_time(epde_ctx* ctx, int kernel_class, double* ms, int64_t* launches);
 
 #ifdef __cplusplus
 }

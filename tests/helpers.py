@@ -23,11 +23,24 @@ def assert_rel(a, b, what, rtol=RTOL, atol=0.0):
     assert not bad.any(), f'{what}: max rel err {err[bad].max():.3e} (rtol {rtol}) at {np.argwhere(bad)[:4].tolist()}'
 
 
-def assert_sw(sw, ref, what, rtol=RTOL):
-    """sliding-window weight matrices: per column, absolute floor 1e-9 x the column's largest
-    magnitude (entries that are ~0 by cancellation carry no relative information)."""
+def natural_scales(columns, target):
+    """Natural magnitude of each regression coefficient: mean|target| / rms(column), and
+    mean|target| for the intercept.  A coefficient (or a whole window-weight column) that is ~0 by
+    cancellation carries no relative information below 1e-9 of this."""
+    columns = np.asarray(columns, dtype=np.float64)
+    ts = float(np.abs(target).mean())
+    rms = np.sqrt((columns ** 2).mean(axis=0)) if columns.size else np.zeros(0)
+    return np.append(ts / np.maximum(rms, 1e-300), ts)
+
+
+def assert_sw(sw, ref, what, rtol=RTOL, col_scales=None):
+    """sliding-window weight matrices, compared per column with an absolute floor of
+    1e-9 x max(largest |entry| of the column, natural scale of that coefficient)."""
     sw = np.asarray(sw, dtype=np.float64)
     ref = np.asarray(ref, dtype=np.float64)
     assert sw.shape == ref.shape, f'{what}: shape {sw.shape} vs {ref.shape}'
     for c in range(ref.shape[1]):
-        assert_rel(sw[:, c], ref[:, c], f'{what} col {c}', rtol=rtol, atol=1e-9 * np.abs(ref[:, c]).max())
+        scale = np.abs(ref[:, c]).max()
+        if col_scales is not None:
+            scale = max(scale, float(col_scales[c]))
+        assert_rel(sw[:, c], ref[:, c], f'{what} col {c}', rtol=rtol, atol=1e-9 * scale)

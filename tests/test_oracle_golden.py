@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 
 from conftest import EQ_FIXTURES, fixture_equations, load_fixture
-from helpers import assert_rel, assert_sw
+from helpers import assert_rel, assert_sw, natural_scales
 from oracle import epde_oracle as orc
 
 
@@ -94,7 +94,10 @@ def test_equation_evals(name):
             assert_rel(r.intercept, fx['ev_b'][v], f'{name} eval {v} intercept', atol=1e-12)
             nact = int(fx['ev_nact'][v])
             assert r.sw_weights.shape[1] == nact + 1
-            assert_sw(r.sw_weights, fx['ev_sw'][v, :, :nact + 1], f'{name} eval {v} sw')
+            cols = orc.term_columns(tokens, eq)
+            sc = natural_scales(np.delete(cols, r.target, axis=1), cols[:, r.target])
+            assert_sw(r.sw_weights, fx['ev_sw'][v, :, :nact + 1], f'{name} eval {v} sw',
+                      col_scales=sc[np.append(ref_coef != 0, True)])
             if np.isnan(fx['ev_fit'][v]):
                 assert r.all_zero
             else:
