@@ -1,0 +1,410 @@
+#!/usr/bin/env python
+"""bench.py -- candidate-equation fitness evaluations per second on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload heat512] [--impl reference]
+
+One "step" = one pass of the evaluator hot path over the whole synthetic population: every
+admissible (equation, target) pair through fused term assembly + Gram (pass A), sliding-window
+solves + LASSO, and the residual norms (pass B).  An "eval" is one such pair.
+
+Workloads (BASELINE.json configs; --workload):
+    heat512   config 5: 512^3 (t,x,y), population 128.  N > 1: grid-point sharding along t, NCCL
+              all-reduce of the segment Grams and of the residual sums (strong scaling).  DEFAULT.
+    heat256   config 4: 256^3, population 256.  N > 1: population sharding, no collective.
+    wave1024  config 3: 1024^2, population 64.   N > 1: population sharding.
+The JSON line follows the driver contract; `value` is device-resident throughput, `e2e` goes
+through the public host API (host encodings in, host results out, copies inside the timed region).
+`--impl reference` times the CPU port of the reference's algorithm (oracle/, numpy, all host
+cores) on a bounded sample of the same workload: the Python reference itself cannot travel to the
+GPU box and cannot allocate its window copies at these sizes.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = 'fitness_evals_per_sec'
+UNIT = 'evals/s'
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--workload', default='heat512')
+    ap.add_argument('--pop', type=int, default=0, help='override the population size')
+    ap.add_argument('--seed', type=int, default=5)
+    ap.add_argument('--cpu-seconds', type=float, default=20.0, help='budget of the cpu_baseline sample')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+def peaks():
+    """(hbm GB/s, source) -- measured copy bandwidth of this pool's B200s."""
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        with open(path) as f:
+            return float(json.load(f)['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    except Exception:       # noqa: BLE001
+        return 6650.0, 'fallback (B200_PROFILING.md 6.65 TB/s)'
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits',
+                 '-lms', '100'], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:       # noqa: BLE001
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:       # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            parts = [p.strip() for p in r.split(',')]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'samples': len(sm), 'reasons': sorted(reasons)}
+
+
+def build_workload(name, pop_override, seed):
+    from epde_b200 import synthetic as syn
+    shape, pop, kind = syn.CONFIGS[name]
+    if pop_override:
+        pop = pop_override
+    n_tokens = len(syn.token_labels(kind))
+    eqs = syn.make_population(n_tokens, pop, seed=seed)
+    evals = syn.make_evals(eqs)
+    return shape, kind, eqs, evals
+
+
+def algorithmic_bytes(eqs, n_points):
+    """pass A reads each distinct token tensor an equation references once:
+    8 * N * U_A per equation."""
+    from epde_b200 import synthetic as syn
+    return sum(8 * n_points * syn.distinct_tokens(eq) for eq in eqs)
+
+
+# ------------------------------------------------------------------------------------------
+# CPU side: the oracle port (numpy, all host cores through BLAS) -- ONLY the cpu_baseline leg and
+# the --impl reference arm may execute oracle/.
+# ------------------------------------------------------------------------------------------
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_eval_equations(tokens, shape, eqs, eq_ids, budget_s, min_eqs=1):
+    """Evaluate equations eq_ids (all admissible targets each) with the oracle until the time
+    budget is exhausted.  Returns (evals done, seconds, equations done)."""
+    from oracle import epde_oracle as orc
+    from epde_b200 import synthetic as syn
+    big = int(np.prod(shape)) > (1 << 22)
+    done_ev, done_eq = 0, 0
+    t0 = time.perf_counter()
+    for e in eq_ids:
+        eq = eqs[e]
+        targets = syn.admissible_targets(eq)
+        if big:
+            orc.evaluate_equation_streamed(tokens, shape, eq, targets=targets)
+        else:
+            orc.evaluate_equation(tokens, shape, eq, targets=targets)
+        done_ev += len(targets)
+        done_eq += 1
+        if done_eq >= min_eqs and time.perf_counter() - t0 >= budget_s:
+            break
+    return done_ev, time.perf_counter() - t0, done_eq
+
+
+def cpu_baseline(tokens, shape, eqs, budget_s, workload):
+    n_ev, dt, n_eq = cpu_eval_equations(tokens, shape, eqs, range(len(eqs)), budget_s)
+    return {'value': n_ev / dt, 'unit': UNIT, 'cores': host_cores(), 'kind': 'port',
+            'sample': f'first {n_eq} of {len(eqs)} equations of {workload} ({n_ev} evals, full grid '
+                      f'{"x".join(map(str, shape))}) in {dt:.1f} s; numpy Gram restatement oracle/epde_oracle.py, '
+                      f'BLAS threads unset'}
+
+
+def run_reference(args):
+    """--impl reference: CPU port of the reference's algorithm on the host cores.  Under torchrun
+    only rank 0 works."""
+    if int(os.environ.get('RANK', '0')) != 0:
+        return
+    from epde_b200 import synthetic as syn
+    shape, kind, eqs, evals = build_workload(args.workload, args.pop, args.seed)
+    # tokens needed by the sampled equations only (generation of all 7 at 512^3 takes minutes)
+    total_budget = max(30.0, 8.0 * args.cpu_seconds)
+    per_step = total_budget / max(1, args.steps + args.warmup)
+    order = list(range(len(eqs)))
+    tokens = syn.make_tokens(shape, kind, seed=args.seed)
+    # warm-up steps also calibrate how many equations fit one step
+    pos = 0
+
+    def step(budget):
+        nonlocal pos
+        ids = [order[(pos + i) % len(order)] for i in range(len(order))]
+        n_ev, dt, n_eq = cpu_eval_equations(tokens, shape, eqs, ids, budget)
+        pos = (pos + n_eq) % len(order)
+        return n_ev, dt, n_eq
+
+    for _ in range(args.warmup):
+        step(min(per_step, 5.0))
+    tot_ev, tot_dt, tot_eq = 0, 0.0, 0
+    for _ in range(args.steps):
+        n_ev, dt, n_eq = step(per_step)
+        tot_ev += n_ev; tot_dt += dt; tot_eq += n_eq
+    value = tot_ev / tot_dt
+    sample = (f'{tot_eq} equations ({tot_ev} evals) of the {len(eqs)}-equation population over {args.steps} steps, '
+              f'full grid {"x".join(map(str, shape))}; numpy Gram restatement (oracle/epde_oracle.py): the Python '
+              f'reference cannot travel to the GPU box nor allocate its window copies at this size')
+    line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * tot_dt / max(1, args.steps),
+            'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64',
+            'data': 'synthetic', 'config': workload_config(args, shape, eqs, evals, 1),
+            'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': host_cores(), 'kind': 'port', 'sample': sample},
+            'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, shape, eqs, evals, world):
+    from epde_b200 import synthetic as syn
+    T = [len(e) for e in eqs]
+    grid_sharded = args.workload == 'heat512' and world > 1
+    return {'workload': args.workload, 'grid': 'x'.join(map(str, shape)), 'population': len(eqs),
+            'evals_per_step': len(evals), 'terms_per_equation': f'{min(T)}..{max(T)} (mean {np.mean(T):.2f})',
+            'distinct_tokens_mean': float(np.mean([syn.distinct_tokens(e) for e in eqs])),
+            'sharding': ('grid-points along t + NCCL all-reduce' if grid_sharded else
+                         ('population round-robin, no collective' if world > 1 else 'single GPU')),
+            'l2_policy': 'token set larger than L2' if int(np.prod(shape)) * 8 * 3 > 126e6 else
+                         'L2 flushed (256 MB write) between timed steps',
+            'seed': args.seed}
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import epde_b200
+    from epde_b200 import synthetic as syn
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if world != args.gpus and rank == 0:
+        print(f'[bench] note: --gpus {args.gpus} but WORLD_SIZE={world}; using WORLD_SIZE', file=sys.stderr)
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    shape, kind, eqs, evals = build_workload(args.workload, args.pop, args.seed)
+    grid_sharded = args.workload == 'heat512' and world > 1
+    if grid_sharded:
+        lo, hi = rank * shape[0] // world, (rank + 1) * shape[0] // world
+        local_shape, shard = (hi - lo,) + tuple(shape[1:]), (lo, shape[0])
+        my_eqs, my_evals = eqs, evals
+    else:
+        lo, hi, local_shape, shard = 0, shape[0], tuple(shape), None
+        my_eqs = eqs[rank::world]
+        my_evals = syn.make_evals(my_eqs)
+    n_local = int(np.prod(local_shape))
+
+    stream = torch.cuda.current_stream()
+    eng = epde_b200.Engine(local_shape, device=local_rank, shard=shard, stream=stream.cuda_stream)
+    t_up0 = time.perf_counter()
+    n_tok = len(syn.token_labels(kind))
+    for i in range(n_tok):
+        tk = syn.make_tokens(shape, kind, xp=torch, device=dev, seed=args.seed, axis0_range=(lo, hi), only=[i])[i]
+        eng.upload_device(i, tk.data_ptr(), tk.numel())
+        torch.cuda.synchronize()
+        del tk
+    torch.cuda.empty_cache()
+    t_gen = time.perf_counter() - t_up0
+
+    enc = epde_b200.encode(my_eqs, my_evals)
+    flush = None
+    if n_local * 8 * 3 <= 126e6:
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident step: encoding already on the device, results stay on the device
+    batch = eng.batch(enc)
+    seg = torch.zeros(batch.gram_size, dtype=torch.float64, device=dev)
+    sums = torch.zeros(batch.residual_size, dtype=torch.float64, device=dev)
+
+    def device_step():
+        batch.gram(seg.data_ptr())
+        if grid_sharded:
+            dist.all_reduce(seg)
+        batch.solve(seg.data_ptr())
+        batch.residual(sums.data_ptr())
+        if grid_sharded:
+            dist.all_reduce(sums)
+
+    def timed(step_fn, k):
+        """sum of per-step device times (CUDA events on the launching stream), L2 flushed between
+        steps when the token set fits L2; barrier + synchronize on both sides."""
+        pairs = []
+        barrier()
+        for _ in range(k):
+            if flush is not None:
+                flush.fill_(1)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            step_fn()
+            b.record(stream)
+            pairs.append((a, b))
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in pairs)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(args.warmup):
+        device_step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    eng.set_timing(True)
+    l0 = eng.launch_count
+    ms_total = timed(device_step, args.steps)
+    launches = eng.launch_count - l0
+    ktimes = eng.kernel_times()
+    eng.set_timing(False)
+    batch.fetch(sums.data_ptr(), want_sw=False)
+    batch.close()
+    total_evals = len(evals)
+    value = total_evals * args.steps / (ms_total * 1e-3)
+
+    # ---- end to end through the host API: host encodings in, host results out, every step
+    def e2e_step():
+        if grid_sharded:
+            with eng.batch(enc) as b:
+                b.gram(seg.data_ptr())
+                dist.all_reduce(seg)
+                b.solve(seg.data_ptr())
+                b.residual(sums.data_ptr())
+                dist.all_reduce(sums)
+                return b.fetch(sums.data_ptr(), want_sw=False)
+        return eng.evaluate(enc, want_sw=False)
+
+    def timed_wall(step_fn, k):
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(k):
+            if flush is not None:
+                flush.fill_(1)
+            res = step_fn()
+        barrier()
+        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), res
+
+    e2e_step()
+    e2e_s, last = timed_wall(e2e_step, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    h2d = sum(a.nbytes for a in (enc.term_off, enc.fac_off, enc.fac_token, enc.fac_power, enc.fac_kind,
+                                 enc.fac_param, enc.eval_eq, enc.eval_target))
+    d2h = sum(getattr(last, k).nbytes for k in ('coef', 'intercept', 'fitness_l1', 'fitness_l2', 'stability',
+                                                'n_active', 'all_zero', 'iters'))
+    e2e_value = total_evals * args.steps / e2e_s
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        alg = algorithmic_bytes(my_eqs, n_local) * args.steps
+        gram_ms, gram_n = ktimes['gram']
+        achieved = alg / (gram_ms * 1e-3) / 1e9 if gram_ms > 0 else 0.0
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': ms_total / args.steps, 'higher_is_better': True,
+            'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+            'config': workload_config(args, shape, eqs, evals, world),
+            'clocks': clocks,
+            'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
+                    'note': 'Engine.evaluate (C ABI epde_evaluate_batch): host CSR encodings in, host results out; '
+                            'token tensors are cache-resident in HBM as in the reference (filled once per dataset)',
+                    'token_cache_fill_s': t_gen},
+            'gpu_launches': int(launches),
+            'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                         'frac': achieved / peak, 'traffic': None, 'kernel': 'gram_cells_kernel (pass A)',
+                         'peak_source': peak_src, 'launches': int(gram_n), 'kernel_ms_per_step': gram_ms / args.steps,
+                         'algorithmic_bytes_per_step': alg // args.steps,
+                         'note': 'algorithmic bytes = 8*N*U_A per equation (each equation streams its distinct tokens '
+                                 'once); equations co-scheduled on the same token tile share it in L2, so frac > 1 '
+                                 'means DRAM traffic below the algorithmic figure'},
+            'kernel_ms_per_step': {k: v[0] / args.steps for k, v in ktimes.items()},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            host_tokens = [eng.download(i) for i in range(n_tok)]
+            line['cpu_baseline'] = cpu_baseline(host_tokens, shape, eqs, args.cpu_seconds, args.workload)
+            del host_tokens
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -43,11 +43,12 @@ def _axes(xp, shape, kind, lo_hi, dev):
     return axes
 
 
-def make_tokens(shape, kind, xp=np, device=None, noise=1e-3, seed=0, axis0_range=None):
+def make_tokens(shape, kind, xp=np, device=None, noise=1e-3, seed=0, axis0_range=None, only=None):
     """list of flat float64 token vectors (C order) in token_labels(kind) order.
 
     axis0_range=(lo, hi): only rows [lo, hi) of the time axis (grid-point sharding); the noise
-    stream is keyed by (seed, token, global row) so shards reproduce the unsharded field."""
+    stream is keyed by (seed, token, global row) so shards reproduce the unsharded field.
+    only: iterable of token indices to build (others are returned as None)."""
     shape = tuple(shape)
     lo0, hi0 = (0, shape[0]) if axis0_range is None else axis0_range
     pi = float(np.pi)
@@ -60,11 +61,11 @@ def make_tokens(shape, kind, xp=np, device=None, noise=1e-3, seed=0, axis0_range
         s2, c2 = xp.sin(2 * pi * X), xp.cos(2 * pi * X)
         a1, b1 = xp.cos(c * pi * T), xp.sin(c * pi * T)
         a2, b2 = xp.cos(2 * c * pi * T), xp.sin(2 * c * pi * T)
-        toks = [s1 * a1 + 0.5 * s2 * a2,
-                -c * pi * s1 * b1 - c * pi * s2 * b2,
-                -(c * pi) ** 2 * s1 * a1 - 2 * (c * pi) ** 2 * s2 * a2,
-                pi * c1 * a1 + pi * c2 * a2,
-                -pi ** 2 * s1 * a1 - 2 * pi ** 2 * s2 * a2]
+        toks = [lambda: s1 * a1 + 0.5 * s2 * a2,
+                lambda: -c * pi * s1 * b1 - c * pi * s2 * b2,
+                lambda: -(c * pi) ** 2 * s1 * a1 - 2 * (c * pi) ** 2 * s2 * a2,
+                lambda: pi * c1 * a1 + pi * c2 * a2,
+                lambda: -pi ** 2 * s1 * a1 - 2 * pi ** 2 * s2 * a2]
     elif kind == 'heat':
         k = 0.5
         t, x, y = _axes(xp, shape, kind, [(0.0, 1.0), (0.0, pi), (0.0, pi)], device)
@@ -73,13 +74,13 @@ def make_tokens(shape, kind, xp=np, device=None, noise=1e-3, seed=0, axis0_range
         e1, e2 = xp.exp(-2 * k * T), 0.3 * xp.exp(-5 * k * T)
         sx, cx, s2x, c2x = xp.sin(X), xp.cos(X), xp.sin(2 * X), xp.cos(2 * X)
         sy, cy = xp.sin(Y), xp.cos(Y)
-        toks = [e1 * sx * sy + e2 * s2x * sy,
-                -2 * k * e1 * sx * sy - 5 * k * e2 * s2x * sy,
-                4 * k * k * e1 * sx * sy + 25 * k * k * e2 * s2x * sy,
-                e1 * cx * sy + 2 * e2 * c2x * sy,
-                -e1 * sx * sy - 4 * e2 * s2x * sy,
-                e1 * sx * cy + e2 * s2x * cy,
-                -e1 * sx * sy - e2 * s2x * sy]
+        toks = [lambda: e1 * sx * sy + e2 * s2x * sy,
+                lambda: -2 * k * e1 * sx * sy - 5 * k * e2 * s2x * sy,
+                lambda: 4 * k * k * e1 * sx * sy + 25 * k * k * e2 * s2x * sy,
+                lambda: e1 * cx * sy + 2 * e2 * c2x * sy,
+                lambda: -e1 * sx * sy - 4 * e2 * s2x * sy,
+                lambda: e1 * sx * cy + e2 * s2x * cy,
+                lambda: -e1 * sx * sy - e2 * s2x * sy]
     else:
         raise ValueError(kind)
     out = []
@@ -87,8 +88,12 @@ def make_tokens(shape, kind, xp=np, device=None, noise=1e-3, seed=0, axis0_range
     if noise:
         # noise amplitude from a coarse copy of the GLOBAL field, so every shard uses the same one
         coarse = make_tokens(tuple(min(n, 33) for n in shape), kind, noise=0.0)
-    for i, tk in enumerate(toks):
-        tk = tk.reshape(-1)
+    only = None if only is None else set(int(i) for i in only)
+    for i, make in enumerate(toks):
+        if only is not None and i not in only:
+            out.append(None)
+            continue
+        tk = make().reshape(-1)
         if noise:
             scale = noise * float(coarse[i].std())
             if xp is np:

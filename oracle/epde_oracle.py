@@ -471,3 +471,94 @@ def select_right_part(results):
         if r.fitness < best_fit:
             best, best_fit = i, r.fitness
     return best
+
+
+# ----------------------------------------------------------------------------------------
+# streamed variant for large grids (256^3 / 512^3): same Gram formulation, axis-0 chunks so that
+# host memory stays bounded.  Used as the timed CPU port where the reference cannot allocate its
+# window copies and by the large-size spot checks.
+# ----------------------------------------------------------------------------------------
+def _chunk_rows(plan, T, budget_bytes=1 << 30):
+    row = int(np.prod(plan.shape[1:])) if len(plan.shape) > 1 else 1
+    return max(1, int(budget_bytes // (8 * row * (T + 2) * 2)))
+
+
+def segment_grams_streamed(tokens, equation, plan: WindowPlan, rows_per_chunk=None):
+    """segment_grams() without materialising the (N, K) matrix: loops over chunks of axis 0."""
+    T = len(equation)
+    K = T + 1
+    shape = plan.shape
+    nd = len(shape)
+    n0 = shape[0]
+    row = int(np.prod(shape[1:])) if nd > 1 else 1
+    if rows_per_chunk is None:
+        rows_per_chunk = _chunk_rows(plan, T)
+    slab0 = np.zeros((n0, K, K))
+    others = [np.zeros((shape[d], K, K)) for d in range(1, nd)]
+    for lo in range(0, n0, rows_per_chunk):
+        hi = min(n0, lo + rows_per_chunk)
+        sub = [np.asarray(t).reshape(-1)[lo * row:hi * row] for t in tokens] if not isinstance(tokens, dict) \
+            else {k: np.asarray(v).reshape(-1)[lo * row:hi * row] for k, v in tokens.items()}
+        aug = np.empty(((hi - lo) * row, K))
+        for t, term in enumerate(equation):
+            aug[:, t] = eval_term(sub, term)
+        aug[:, T] = 1.0
+        grid = aug.reshape((hi - lo,) + tuple(shape[1:]) + (K,))
+        X0 = grid.reshape(hi - lo, -1, K)
+        slab0[lo:hi] = np.matmul(X0.transpose(0, 2, 1), X0)
+        for d in range(1, nd):
+            Xd = np.moveaxis(grid, d, 0).reshape(shape[d], -1, K)
+            others[d - 1] += np.matmul(Xd.transpose(0, 2, 1), Xd)
+    slabs = [slab0] + others
+    return [np.add.reduceat(s, ax.bounds[:-1], axis=0) for s, ax in zip(slabs, plan.axes)]
+
+
+def residual_sums_streamed(tokens, equation, plan, jobs, rows_per_chunk=None):
+    """jobs: [(target, coef_per_term (T,), b_l1, b_l2)] -> [(sum|r|, sum|t|, sum r2^2)]."""
+    T = len(equation)
+    shape = plan.shape
+    row = int(np.prod(shape[1:])) if len(shape) > 1 else 1
+    if rows_per_chunk is None:
+        rows_per_chunk = _chunk_rows(plan, T)
+    acc = np.zeros((len(jobs), 3))
+    for lo in range(0, shape[0], rows_per_chunk):
+        hi = min(shape[0], lo + rows_per_chunk)
+        sub = [np.asarray(t).reshape(-1)[lo * row:hi * row] for t in tokens]
+        cols = np.stack([eval_term(sub, term) for term in equation], axis=1)
+        for i, (tgt, w, b1, b2) in enumerate(jobs):
+            pred = cols @ w
+            tcol = cols[:, tgt]
+            acc[i, 0] += np.abs(tcol - (pred + b1)).sum()
+            acc[i, 1] += np.abs(tcol).sum()
+            acc[i, 2] += ((pred + b2 - tcol) ** 2).sum()
+    return acc
+
+
+def evaluate_equation_streamed(tokens, grid_shape, equation, targets=None):
+    """evaluate_equation(method='gram') for grids too large for the in-memory version."""
+    plan = WindowPlan(grid_shape)
+    T = len(equation)
+    if targets is None:
+        targets = list(range(T))
+    seg = segment_grams_streamed(tokens, equation, plan)
+    win = window_grams(seg, plan)
+    total = seg[0].sum(axis=0)
+    results, jobs = [], []
+    for tgt in targets:
+        feat = [i for i in range(T) if i != tgt]
+        coef, b, cached = lasso_fit_gram(win, total, feat, tgt)
+        r = EvalResult()
+        r.cond = window_condition(win, feat + [T])
+        r.target, r.coef, r.intercept, r.sw_weights = tgt, coef, float(b), cached
+        r.all_zero = bool(np.all(coef == 0))
+        r.stability = stability_from_weights(cached, len(plan.shape))
+        w = np.zeros(T)
+        w[feat] = coef
+        b1 = total[tgt, T] / total[T, T] if r.all_zero else float(b)      # fitness.py:135-136
+        jobs.append((tgt, w, b1, float(b)))
+        results.append(r)
+    sums = residual_sums_streamed(tokens, equation, plan, jobs)
+    for r, s in zip(results, sums):
+        r.fitness = float(s[0] / s[1])
+        r.fitness_l2 = float(np.sqrt(s[2]))
+    return results

@@ -22,9 +22,16 @@ def make_engine(shape, tokens, **kw):
     return eng
 
 
+class Scales(np.ndarray):
+    """natural_scales() array carrying ||target||_2 for the L2 fitness floor."""
+    t_norm = 0.0
+
+
 def eval_scales(tokens, eq, tgt):
     cols = orc.term_columns(tokens, eq)
-    return natural_scales(np.delete(cols, tgt, axis=1), cols[:, tgt])
+    sc = natural_scales(np.delete(cols, tgt, axis=1), cols[:, tgt]).view(Scales)
+    sc.t_norm = float(np.linalg.norm(cols[:, tgt]))
+    return sc
 
 
 def compare_eval(res, v, ref, T, ndim, what, check_sw=True):
@@ -45,7 +52,7 @@ def compare_eval(res, v, ref, T, ndim, what, check_sw=True):
     if ref.get('fitness') is not None and not np.isnan(ref['fitness']):
         assert_rel(res.fitness_l1[v], ref['fitness'], f'{what} fitness', atol=1e-10)
     if ref.get('fitness_l2') is not None and not np.isnan(ref['fitness_l2']):
-        assert_rel(res.fitness_l2[v], ref['fitness_l2'], f'{what} fitness_l2')
+        assert_rel(res.fitness_l2[v], ref['fitness_l2'], f'{what} fitness_l2', atol=1e-9 * getattr(sc, 't_norm', 0.0))
     if ref.get('stability') is not None and not np.isnan(ref['stability']):
         assert_rel(res.stability[v], ref['stability'], f'{what} stability', rtol=1e-5, atol=1e-14)
 
