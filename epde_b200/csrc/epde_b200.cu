@@ -4,19 +4,27 @@
 //   token cache            epde/cache/cache.py:141-524              -> HBM-resident token table
 //   term assembly          structure/factor.py:218-269, evaluators.py:92-151,
 //                          structure/main_structures.py:207-235,588-641
-//                                                                    -> gram_cells_kernel (pass A)
-//   calculate_weights      epde/supplementary.py:394-471             -> segment Grams + lasso_solve_kernel
+//                                                                    -> gram_tile_kernel (pass A)
+//   calculate_weights      epde/supplementary.py:394-471             -> segment Grams, window_gram_kernel,
+//                                                                       lasso_solve_kernel
 //   PhysicsInformedLasso   operators/common/sparsity.py:20-150       -> lasso_solve_kernel
-//   L2LRFitness/L2Fitness  operators/common/fitness.py:27-183        -> residual_kernel (pass B)
+//   L2LRFitness/L2Fitness  operators/common/fitness.py:27-183        -> residual_tile_kernel (pass B)
 //
 // Data layout in HBM
 //   token t            double[N]   N = prod(inner_shape), C order, last axis contiguous
 //   cell Grams  C      per equation: [cellA][cellB][piece][NACC]   NACC = T(T+3)/2
 //                      (upper triangle of the T x T term Gram, then the T column sums)
 //   segment Grams S    per equation: [segment row][NE], NE = NACC + 1 (last = point count);
-//                      segment rows of all axes stacked; after prefix_kernel rows hold inclusive
-//                      prefix sums along each axis, so a sliding-window Gram is a difference of
-//                      two rows.
+//                      segment rows of all axes stacked.  This is the buffer that is all-reduced
+//                      under grid sharding.
+//   window Grams  Wg   per equation: [W + 1][NE]: row w = sum of the segment rows of sliding window w
+//                      (direct summation, no prefix differences: a window that holds small values
+//                      after a region of large ones keeps full relative accuracy); row W = all points.
+//
+// Execution model of the two streaming passes: a CTA stages one tile of every token the launch
+// group references in shared memory (cp.async), then each WARP evaluates a different equation on
+// that tile (lane <-> point column), so a token tile is read from L2/HBM once per group instead of
+// once per equation and all per-point operand fetches are shared-memory loads.
 //
 // No CPU fallback exists in this file: every entry point either runs the CUDA path or fails.
 #include "../../include/epde_b200.h"
@@ -27,6 +35,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <set>
@@ -39,7 +48,14 @@
 #define RIDGE 1e-6             // supplementary.py:458
 #define LASSO_MAX_ITER 20      // sparsity.py:21
 #define LASSO_TOL 1e-4         // sparsity.py:21
-#define RED_CHUNK 16           // Gram entries reduced per shared-memory round in pass A
+
+#define TILE_ROWS 64           // rows (leading-axes index pairs) of a pass-A tile
+#define TILE_COLS 32           // columns (last axis) of a pass-A tile = warp width
+#define GRAM_WARPS 8           // warps per pass-A CTA
+#define RED_CHUNK 8            // Gram entries reduced per shared-memory round of the cell flush
+#define MAXU 12                // distinct tokens per launch group (tile = MAXU x 64 x 32 doubles = 192 KB)
+#define RES_WARPS 16           // warps (= equations) per pass-B CTA
+#define RES_TILE 1024          // points of a pass-B tile
 
 static thread_local std::string g_err;
 
@@ -64,23 +80,29 @@ static int fail(const char* fmt, ...) {
 // device-side descriptors
 // ------------------------------------------------------------------------------------------
 struct FactorDesc {          // 32 bytes
-    const double* ptr;       // token vector
-    double param;            // freq for trig kinds
-    double power;
+    int slot;                // token slot inside the launch group's tile
+    int ipow;                // integer power if power is 1, 2 or 3, else 0
     int kind;                // 0 pow, 1 sin, 2 cos, 3 inverse
-    int ipow;                // integer power if power is a small positive integer, else 0
+    int pad;
+    double power;
+    double param;            // freq for trig kinds
 };
 
 struct EqDesc {
     int T;
+    int fast;                // 1: every term has <= 2 factors, all kind 0 with power in {1, 2, 3}
+    int group;               // launch group
     int fac_off[TMAX + 1];   // into the batch factor array
     long long s_off;         // doubles, into the segment-Gram table
+    long long c_off;         // doubles, into the cell-Gram scratch of its launch group
+    long long w_off;         // doubles, into the window-Gram table
+    int4 fastop[TMAX];       // fast terms: {slot0, ipow0, slot1 or -1, ipow1}
 };
 
-struct UnitDesc {            // one CTA work unit of pass A: a cell of the leading axes x a column chunk
+struct UnitDesc {            // one CTA work unit of pass A: a (sub-)cell of the leading axes x a column chunk
     int a_lo, a_hi;          // index range on leading slot A
     int b_lo, b_hi;          // index range on leading slot B
-    int col_lo, ncols;       // columns (last axis) handled, ncols <= blockDim.x
+    int col_lo, ncols;       // columns (last axis) handled, ncols <= TILE_COLS
     int cell;                // (cellA * nB + cellB)
     int piece_lo, npieces;   // pieces (sub-segments of the last axis) covered by the chunk
     int pad0, pad1, pad2;
@@ -101,14 +123,14 @@ struct Geom {                // kernel-visible geometry (by value)
     int n_rows;                    // segment rows over all axes
     int n_windows;
     int ndim;
-    int total_row;                 // prefix row holding the Gram of all points (last row of axis 0)
+    int max_rows;                  // largest row count of a unit (<= TILE_ROWS)
+    int aligned16;                 // 1: every tile row starts on a 16-byte boundary
     long long N;
     const UnitDesc* units;
     const int* piece_start;        // [npieces + 1] column bounds
     const MargDesc* marg;          // [n_rows]
-    const int* axis_row_base;      // [ndim + 1]
-    const int* win_hi_row;         // [W]
-    const int* win_lo_row;         // [W] (-1: window starts at the axis origin)
+    const int* win_lo_row;         // [W + 1] first segment row of window w (entry W: all of axis 0)
+    const int* win_hi_row;         // [W + 1] one past the last segment row
 };
 
 __host__ __device__ __forceinline__ int nacc_of(int T) { return T * (T + 3) / 2; }
@@ -121,12 +143,23 @@ __host__ __device__ __forceinline__ int gidx(int i, int j, int T) {
 }
 
 // ------------------------------------------------------------------------------------------
-// factor / term evaluation (factor.py:218-269, evaluators.py:92-151)
+// shared-memory staging helpers
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ double ld_stream(const double* p) {
-    return __ldg(p);
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gmem_src) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
 }
 
+// ------------------------------------------------------------------------------------------
+// factor / term evaluation (factor.py:218-269, evaluators.py:92-151)
+// ------------------------------------------------------------------------------------------
 __device__ __forceinline__ double apply_factor(const FactorDesc& f, double x) {
     if (f.kind != 0) {
         if (f.kind == 1) x = sin(f.param * x);
@@ -139,97 +172,252 @@ __device__ __forceinline__ double apply_factor(const FactorDesc& f, double x) {
     return pow(x, f.power);
 }
 
-template <int T>
-__device__ __forceinline__ void eval_terms(const FactorDesc* sf, const int* foff, long long idx,
-                                           double (&c)[T]) {
-#pragma unroll
-    for (int t = 0; t < T; ++t) {
-        const int f0 = foff[t], f1 = foff[t + 1];
-        double v = apply_factor(sf[f0], ld_stream(sf[f0].ptr + idx));
-        for (int f = f0 + 1; f < f1; ++f) v *= apply_factor(sf[f], ld_stream(sf[f].ptr + idx));
-        c[t] = v;
-    }
+__device__ __forceinline__ double ipow123(double x, int ip) {
+    if (ip >= 2) { const double s = x * x; x = (ip == 3) ? s * x : s; }
+    return x;
 }
 
+// generic term: product of its factors; `pt` = tile base + point offset, slot stride `tstride`
+__device__ __forceinline__ double eval_term_generic(const FactorDesc* fac, int f0, int f1, const double* pt,
+                                                    int tstride) {
+    double v = 1.0;
+    for (int f = f0; f < f1; ++f) {
+        const FactorDesc d = fac[f];
+        v *= apply_factor(d, pt[d.slot * tstride]);
+    }
+    return v;
+}
+
+// per-warp copy of the equation being processed (shared memory)
+struct WarpProg {
+    int4 op[TMAX];           // fast terms: {offset0, ipow0, offset1 or -1, ipow1} (offsets in doubles)
+    int foff[TMAX + 1];      // generic path: factor ranges
+    int T, fast, pad0, pad1;
+};
+
 // ------------------------------------------------------------------------------------------
-// pass A: fused term assembly + cell Gram.  One CTA = (unit, equation); thread <-> column of the
-// last axis, looping over the rows of the leading-axes cell, so every thread only ever sees points
-// of one last-axis piece and the accumulators stay in registers.  Equation index is the fastest
-// grid dimension so CTAs sweeping the same token tile for different equations are co-resident
-// (L2 reuse).
+// pass A: fused term assembly + cell Gram.
+// CTA <-> unit (a (sub-)cell of the leading axes x <= 32 columns of the last axis): the tile of
+// every token of the launch group is staged in shared memory once, then each warp takes equations
+// from the group's list (longest first, dynamic) and accumulates that equation's cell Gram in
+// registers, lane <-> column, looping over the tile rows.  The per-lane accumulators are reduced
+// over the columns of each last-axis piece through a small per-warp shared buffer and written to the
+// cell table (no atomics: fixed summation order).
 // ------------------------------------------------------------------------------------------
 struct GramParams {
     Geom g;
     const EqDesc* eqs;
     const FactorDesc* factors;
-    const int* eq_list;      // equations of this launch (all with the same T)
+    const int* eq_list;      // equations of this launch group, most terms first
     int n_eq;
-    double* cells;           // cell-Gram scratch
+    int U;                   // tokens of the group
+    const double* tok[MAXU];
+    double* cells;           // cell-Gram scratch of the group
 };
 
 template <int T>
-__global__ void __launch_bounds__(256) gram_cells_kernel(GramParams p) {
+__device__ __forceinline__ void gram_accumulate(double (&acc)[T * (T + 3) / 2], const double (&c)[T]) {
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < T; ++i)
+#pragma unroll
+        for (int j = i; j < T; ++j) { acc[k] = fma(c[i], c[j], acc[k]); ++k; }
+#pragma unroll
+    for (int i = 0; i < T; ++i) { acc[k] += c[i]; ++k; }
+}
+
+template <int T>
+__device__ __forceinline__ void fast_terms(const WarpProg* wp, const double* pr, double (&c)[T]) {
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+        const int4 d = wp->op[t];
+        double x = ipow123(pr[d.x], d.y);
+        if (d.z >= 0) x *= ipow123(pr[d.z], d.w);
+        c[t] = x;
+    }
+}
+
+template <int T>
+__device__ __forceinline__ void fast_terms2(const WarpProg* wp, const double* pr, double (&c0)[T], double (&c1)[T]) {
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+        const int4 d = wp->op[t];
+        double x0 = pr[d.x], x1 = pr[d.x + TILE_COLS];
+        if (d.y >= 2) {
+            const double s0 = x0 * x0, s1 = x1 * x1;
+            if (d.y == 3) { x0 *= s0; x1 *= s1; } else { x0 = s0; x1 = s1; }
+        }
+        if (d.z >= 0) {
+            double y0 = pr[d.z], y1 = pr[d.z + TILE_COLS];
+            if (d.w >= 2) {
+                const double s0 = y0 * y0, s1 = y1 * y1;
+                if (d.w == 3) { y0 *= s0; y1 *= s1; } else { y0 = s0; y1 = s1; }
+            }
+            x0 *= y0; x1 *= y1;
+        }
+        c0[t] = x0; c1[t] = x1;
+    }
+}
+
+// flush: sum the lanes (columns) of every piece, RED_CHUNK Gram entries per round
+template <int T>
+__device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2], int lane, double* red, double* out,
+                                            int piece_lo, int npieces, int col_lo, const int* __restrict__ piece_start) {
     constexpr int NACC = T * (T + 3) / 2;
-    __shared__ FactorDesc sf[T * FMAXF];
-    __shared__ int foff[T + 1];
-    extern __shared__ double red[];            // RED_CHUNK x (blockDim.x + 1)
+    constexpr int RS = TILE_COLS + 1;
+#pragma unroll
+    for (int b0 = 0; b0 < NACC; b0 += RED_CHUNK) {
+        const int cnt = (NACC - b0) < RED_CHUNK ? (NACC - b0) : RED_CHUNK;
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < RED_CHUNK; ++k)
+            if (b0 + k < NACC) red[k * RS + lane] = acc[b0 + k];
+        __syncwarp();
+        const int nout = npieces * cnt;
+        for (int o = lane; o < nout; o += 32) {
+            const int pp = o / cnt, k = o - pp * cnt;
+            const int lo = piece_start[piece_lo + pp] - col_lo;
+            const int hi = piece_start[piece_lo + pp + 1] - col_lo;
+            double s = 0.0;
+            for (int cidx = lo; cidx < hi; ++cidx) s += red[k * RS + cidx];
+            out[(long long)pp * NACC + b0 + k] = s;
+        }
+    }
+    __syncwarp();
+}
 
-    const int tid = threadIdx.x;
-    const int BX = blockDim.x;
-    const int le = blockIdx.x % p.n_eq;        // position inside the launch group
-    const int e = p.eq_list[le];
-    const UnitDesc u = p.g.units[blockIdx.x / p.n_eq];
-    const EqDesc& eq = p.eqs[e];
-    const int fbase = eq.fac_off[0];
-    if (tid <= T) foff[tid] = eq.fac_off[tid] - fbase;
-    const int nfac = eq.fac_off[T] - fbase;
-    if (tid < nfac) sf[tid] = p.factors[fbase + tid];
-    __syncthreads();
-
+// fast path: every term = x^p [* y^q], p, q in {1, 2, 3}; TWO = two tile rows per decode
+template <int T, bool TWO>
+__device__ __noinline__ void gram_warp_fast(const double* tile, const WarpProg* wp, int nrows, int lane, double* red,
+                                            double* out, int piece_lo, int npieces, int col_lo,
+                                            const int* __restrict__ piece_start) {
+    constexpr int NACC = T * (T + 3) / 2;
     double acc[NACC];
 #pragma unroll
     for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
-
-    if (tid < u.ncols) {
-        const int wb = u.b_hi - u.b_lo;
-        const int nrows = (u.a_hi - u.a_lo) * wb;
-        const long long col = u.col_lo + tid;
-        int ia = u.a_lo, ib = u.b_lo;
-        for (int r = 0; r < nrows; ++r) {
-            const long long idx = ia * p.g.strideA + ib * p.g.strideB + col;
-            double c[T];
-            eval_terms<T>(sf, foff, idx, c);
-            int k = 0;
-#pragma unroll
-            for (int i = 0; i < T; ++i)
-#pragma unroll
-                for (int j = i; j < T; ++j) { acc[k] = fma(c[i], c[j], acc[k]); ++k; }
-#pragma unroll
-            for (int i = 0; i < T; ++i) { acc[k] += c[i]; ++k; }
-            if (++ib == u.b_hi) { ib = u.b_lo; ++ia; }
+    const double* base = tile + lane;
+    int row = 0;
+    if (TWO) {
+        for (; row + 2 <= nrows; row += 2) {
+            double c0[T], c1[T];
+            fast_terms2<T>(wp, base + row * TILE_COLS, c0, c1);
+            gram_accumulate<T>(acc, c0);
+            gram_accumulate<T>(acc, c1);
         }
     }
+    for (; row < nrows; ++row) {
+        double c[T];
+        fast_terms<T>(wp, base + row * TILE_COLS, c);
+        gram_accumulate<T>(acc, c);
+    }
+    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start);
+}
 
-    // epilogue: reduce the columns of every piece, RED_CHUNK Gram entries per round
-    const int RS = BX + 1;
-    double* out = p.cells + ((long long)le * p.g.n_cells + (long long)u.cell * p.g.npieces + u.piece_lo) * NACC;
+// generic path: any factor kind / power / factor count
+template <int T>
+__device__ __noinline__ void gram_warp_generic(const double* tile, int tstride, const WarpProg* wp,
+                                               const FactorDesc* fac, int nrows, int lane, double* red, double* out,
+                                               int piece_lo, int npieces, int col_lo,
+                                               const int* __restrict__ piece_start) {
+    constexpr int NACC = T * (T + 3) / 2;
+    double acc[NACC];
 #pragma unroll
-    for (int base = 0; base < NACC; base += RED_CHUNK) {
-        const int cnt = (NACC - base) < RED_CHUNK ? (NACC - base) : RED_CHUNK;
-        __syncthreads();
+    for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
+    const double* base = tile + lane;
+    for (int row = 0; row < nrows; ++row) {
+        double c[T];
 #pragma unroll
-        for (int k = 0; k < RED_CHUNK; ++k)
-            if (base + k < NACC) red[k * RS + tid] = acc[base + k];
-        __syncthreads();
-        const int nout = u.npieces * cnt;
-        for (int o = tid; o < nout; o += BX) {
-            const int pp = o / cnt, k = o - pp * cnt;
-            const int lo = p.g.piece_start[u.piece_lo + pp] - u.col_lo;
-            const int hi = p.g.piece_start[u.piece_lo + pp + 1] - u.col_lo;
-            double s = 0.0;
-            for (int cidx = lo; cidx < hi; ++cidx) s += red[k * RS + cidx];
-            out[(long long)pp * NACC + base + k] = s;
+        for (int t = 0; t < T; ++t)
+            c[t] = eval_term_generic(fac, wp->foff[t], wp->foff[t + 1], base + row * TILE_COLS, tstride);
+        gram_accumulate<T>(acc, c);
+    }
+    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start);
+}
+
+template <int T, int NW>
+__device__ __forceinline__ void gram_warp(const double* tile, int tstride, const WarpProg* wp, const FactorDesc* fac,
+                                          int nrows, int lane, double* red, double* out, int piece_lo, int npieces,
+                                          int col_lo, const int* __restrict__ piece_start) {
+    // 8-warp CTAs may use 255 registers per thread: two rows per decode for every T
+    constexpr bool TWO = (NW <= 8) || (T <= 6);
+    if (wp->fast) gram_warp_fast<T, TWO>(tile, wp, nrows, lane, red, out, piece_lo, npieces, col_lo, piece_start);
+    else gram_warp_generic<T>(tile, tstride, wp, fac, nrows, lane, red, out, piece_lo, npieces, col_lo, piece_start);
+}
+
+template <int NW>
+__global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
+    extern __shared__ __align__(16) double smem[];
+    __shared__ int s_next;
+    __shared__ const double* s_tok[MAXU];
+    const int tid = threadIdx.x;
+    const int nwarps = blockDim.x >> 5;
+    const UnitDesc u = p.g.units[blockIdx.x];
+    const int wb = u.b_hi - u.b_lo;
+    const int nrows = (u.a_hi - u.a_lo) * wb;
+    const int tstride = p.g.max_rows * TILE_COLS;
+    double* tile = smem;                                              // [U][max_rows][32]
+    double* red_all = tile + (size_t)p.U * tstride;                   // [nwarps][RED_CHUNK][33]
+    WarpProg* progs = (WarpProg*)(red_all + nwarps * RED_CHUNK * (TILE_COLS + 1));
+    if (tid < MAXU) s_tok[tid] = p.tok[tid];
+    __syncthreads();
+
+    // ---- stage the tile: 16-byte cp.async where rows are aligned and full, 8-byte / zero fill otherwise
+    {
+        const bool vec = p.g.aligned16 && !(u.col_lo & 1);
+        const int total = p.U * nrows * (TILE_COLS / 2);
+        for (int q = tid; q < total; q += blockDim.x) {
+            const int part = q & (TILE_COLS / 2 - 1);
+            const int rr = q / (TILE_COLS / 2);
+            const int row = rr % nrows, us = rr / nrows;
+            const int ia = u.a_lo + row / wb, ib = u.b_lo + row % wb;
+            const int c0 = part * 2;
+            const double* src = s_tok[us] + ((long long)ia * p.g.strideA + (long long)ib * p.g.strideB + u.col_lo + c0);
+            double* dst = tile + (size_t)us * tstride + row * TILE_COLS + c0;
+            if (vec && c0 + 2 <= u.ncols) {
+                cp_async16(dst, src);
+            } else {
+                if (c0 < u.ncols) cp_async8(dst, src); else dst[0] = 0.0;
+                if (c0 + 1 < u.ncols) cp_async8(dst + 1, src + 1); else dst[1] = 0.0;
+            }
         }
+        cp_async_wait_all();
+        if (tid == 0) s_next = nwarps;
+        __syncthreads();
+    }
+
+    const int warp = tid >> 5, lane = tid & 31;
+    WarpProg* wp = progs + warp;
+    double* red = red_all + warp * RED_CHUNK * (TILE_COLS + 1);
+    int le = warp;
+    while (le < p.n_eq) {
+        const int e = p.eq_list[le];
+        const EqDesc* eq = p.eqs + e;
+        const int T = eq->T;
+        __syncwarp();
+        if (lane < TMAX) {
+            int4 d = eq->fastop[lane];
+            d.x *= tstride;
+            if (d.z >= 0) d.z *= tstride;
+            wp->op[lane] = d;
+        }
+        if (lane <= TMAX) wp->foff[lane] = eq->fac_off[lane];
+        if (lane == 0) { wp->T = T; wp->fast = eq->fast; }
+        __syncwarp();
+        double* out = p.cells + eq->c_off + ((long long)u.cell * p.g.npieces + u.piece_lo) * nacc_of(T);
+#define GW(TT) gram_warp<TT, NW>(tile, tstride, wp, p.factors, nrows, lane, red, out, u.piece_lo, u.npieces, u.col_lo, p.g.piece_start)
+        switch (T) {
+            case 1: GW(1); break;
+            case 2: GW(2); break;
+            case 3: GW(3); break;
+            case 4: GW(4); break;
+            case 5: GW(5); break;
+            case 6: GW(6); break;
+            case 7: GW(7); break;
+            default: GW(8); break;
+        }
+#undef GW
+        if (lane == 0) le = atomicAdd(&s_next, 1);
+        le = __shfl_sync(0xffffffffu, le, 0);
     }
 }
 
@@ -253,9 +441,9 @@ __global__ void __launch_bounds__(256) marginal_kernel(MargParams p) {
     const int NE = NACC + 1;
     const MargDesc m = p.g.marg[blockIdx.x];
     const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
-    const int na = m.a_hi - m.a_lo, nb = m.b_hi - m.b_lo, np = m.p_hi - m.p_lo;
-    const int ncell = na * nb * np;
-    const double* C = p.cells + (long long)blockIdx.y * p.g.n_cells * NACC;
+    const int nb = m.b_hi - m.b_lo, np = m.p_hi - m.p_lo;
+    const int ncell = (m.a_hi - m.a_lo) * nb * np;
+    const double* C = p.cells + eq.c_off;
     double s0 = 0.0, s1 = 0.0;
     for (int q = grp; q < ncell; q += 8) {
         const int ip = q % np;
@@ -278,29 +466,27 @@ __global__ void __launch_bounds__(256) marginal_kernel(MargParams p) {
     if (threadIdx.x == 64) p.seg[eq.s_off + (long long)m.row * NE + NACC] = m.count;
 }
 
-// inclusive prefix along the segments of each axis, in place.  grid = (ndim, n_eq), block = 64
-struct PrefixParams {
+// window Gram = direct sum of the segment rows of the window; row W = every point (all of axis 0).
+// grid = (W + 1, n_eq), block = 64
+struct WindowParams {
     Geom g;
     const EqDesc* eqs;
-    int n_eq;
-    double* seg;
+    const double* seg;
+    double* win;
 };
 
-__global__ void prefix_kernel(PrefixParams p) {
-    const int e = blockIdx.y, d = blockIdx.x;
-    const EqDesc& eq = p.eqs[e];
+__global__ void window_gram_kernel(WindowParams p) {
+    const EqDesc& eq = p.eqs[blockIdx.y];
     const int NE = nacc_of(eq.T) + 1;
-    const int r0 = p.g.axis_row_base[d], r1 = p.g.axis_row_base[d + 1];
-    double* S = p.seg + eq.s_off;
+    const int w = blockIdx.x;
+    const int r0 = p.g.win_lo_row[w], r1 = p.g.win_hi_row[w];
+    const double* S = p.seg + eq.s_off;
     for (int a = threadIdx.x; a < NE; a += blockDim.x) {
-        double run = 0.0;
-        for (int r = r0; r < r1; ++r) {
-            run += S[(long long)r * NE + a];
-            S[(long long)r * NE + a] = run;
-        }
+        double s = 0.0;
+        for (int r = r0; r < r1; ++r) s += S[(long long)r * NE + a];
+        p.win[eq.w_off + (long long)w * NE + a] = s;
     }
 }
-
 // ------------------------------------------------------------------------------------------
 // solve: one CTA per eval.  calculate_weights (supplementary.py:455-469) = every window's ridge
 // system solved by a GS-lane group (Gaussian elimination with partial pivoting, as LAPACK gesv);
@@ -313,7 +499,7 @@ struct SolveParams {
     const int* eval_list;
     const int* eval_eq;
     const int* eval_tgt;
-    const double* seg;       // prefix-summed segment Grams
+    const double* win;       // window Grams [W + 1][NE] per equation (row W = all points)
     const int* mode;         // per eval: 0 LASSO, 1 given weights + window solves, 2 given weights only (may be null)
     const double* given_wterm;   // [n_eval][TMAX] coefficient per term index (modes 1, 2)
     const double* given_b;       // [n_eval]
@@ -357,12 +543,12 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
     const int T = eq.T, F = T - 1;
     const int NE = nacc_of(T) + 1;
     const int W = p.g.n_windows;
-    const double* P = p.seg + eq.s_off;
+    const double* P = p.win + eq.w_off;
 
     // total Gram
     for (int q = tid; q < (T + 1) * (T + 1); q += SOLVE_THREADS) {
         const int i = q / (T + 1), j = q % (T + 1);
-        Gt[i * KS + j] = P[(long long)p.g.total_row * NE + gidx(i, j, T)];
+        Gt[i * KS + j] = P[(long long)W * NE + gidx(i, j, T)];
     }
     if (tid == 0) {
         int n = 0;
@@ -390,21 +576,18 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
             int w = it * NG + grp;
             const bool valid = w < W;
             if (!valid) w = W - 1;
-            const double* Phi = P + (long long)p.g.win_hi_row[w] * NE;
-            const int lo_row = p.g.win_lo_row[w];
-            const double* Plo = P + (long long)(lo_row < 0 ? 0 : lo_row) * NE;
-            const double lo_on = lo_row < 0 ? 0.0 : 1.0;
+            const double* Phi = P + (long long)w * NE;
             double (*Mg)[GS + 1] = M[grp];
             if (lr < n) {
                 const int i = cols[lr];
                 for (int c = 0; c < n; ++c) {
                     const int gi = gidx(i, cols[c], T);
-                    double v = Phi[gi] - lo_on * Plo[gi];
+                    double v = Phi[gi];
                     if (c == lr) v += RIDGE;
                     Mg[lr][c] = v;
                 }
                 const int gi = gidx(i, tgt, T);
-                Mg[lr][n] = Phi[gi] - lo_on * Plo[gi];
+                Mg[lr][n] = Phi[gi];
             }
             __syncwarp();
             for (int k = 0; k < n; ++k) {
@@ -590,135 +773,215 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
     }
 }
 
+
 // ------------------------------------------------------------------------------------------
-// pass B: residual sums per eval: sum|r|, sum|t|, sum r^2 with r = t - (F w + b)
-// (fitness.py:135-142 and 70-83).  One CTA handles a strip of points of ONE equation and all of
-// its evals (slot d = target term d), so the term columns are assembled once for all targets.
-// grid = (blocks_per_eq, n_eq_launch); partial sums per block, reduced in fixed order afterwards.
+// pass B: residual sums per eval: sum|r|, sum|t|, sum r2^2 with r = t - (F w + b1), r2 = t - (F w + b)
+// (fitness.py:135-142 and 70-83).  A WARP owns one equation (all of its evals: slot d = target term
+// d) for the whole kernel: its program and weights sit in a per-warp shared scratch, its sums in
+// registers.  The CTA (up to RES_WARPS equations) walks over tiles of RES_TILE consecutive points,
+// blockIdx.y-strided; the tile of every token of the launch group is double-buffered in shared
+// memory with cp.async, lane <-> point, two points per decode.  One partial row per (CTA.y,
+// equation) is written at the end and reduced in fixed order by residual_final_kernel.
 // ------------------------------------------------------------------------------------------
 struct ResidParams {
-    Geom g;
+    long long N;
     const EqDesc* eqs;
     const FactorDesc* factors;
-    const int* eq_list;
-    const int* slot_eval;    // [n_eq][TMAX] eval id of (equation, target term) or -1
+    const int* eq_list;      // equations of this launch (most terms first)
+    int n_eq;
+    int U;
+    int n_tiles;
+    const double* tok[MAXU];
+    const int* slot_eval;    // [n_eq_total][TMAX] eval id of (equation, target term) or -1
     const double* wterm;     // [n_eval][TMAX]
     const double* intercept; // [n_eval]
     const double* intercept_l1;  // [n_eval]
-    double* partial;         // [n_eq_launch][gridDim.x][TMAX][3]
-    int points_per_block;
+    double* partial;         // [gridDim.y][n_eq][TMAX][3]
 };
 
+struct ResidWarp {           // per-warp shared scratch
+    WarpProg prog;
+    double sw[TMAX * TMAX];  // [d][j] coefficient of term j for the eval with target d
+    double sb[TMAX], sdb[TMAX];
+};
+
+// one tile for one equation; a[d*3 + q] are the running sums of the warp's lane
 template <int T>
-__global__ void __launch_bounds__(256) residual_kernel(ResidParams p) {
-    __shared__ FactorDesc sf[T * FMAXF];
-    __shared__ int foff[T + 1];
-    __shared__ double sw_[T][T];
-    __shared__ double sb_[T], sdb_[T];
-    __shared__ int s_slot[T];
-    __shared__ unsigned long long s_nz;
-    __shared__ unsigned int s_used, s_valid;
-    __shared__ double sred[8][T][3];
-
-    const int tid = threadIdx.x;
-    const int e = p.eq_list[blockIdx.y];
-    const EqDesc& eq = p.eqs[e];
-    const int fbase = eq.fac_off[0];
-    if (tid <= T) foff[tid] = eq.fac_off[tid] - fbase;
-    const int nfac = eq.fac_off[T] - fbase;
-    if (tid < nfac) sf[tid] = p.factors[fbase + tid];
-    if (tid < T) s_slot[tid] = p.slot_eval[e * TMAX + tid];
-    __syncthreads();
-    if (tid < T * T) {
-        const int d = tid / T, j = tid % T;
-        const int evd = s_slot[d];
-        sw_[d][j] = evd >= 0 ? p.wterm[(long long)evd * TMAX + j] : 0.0;
-        if (j == 0) {
-            sb_[d] = evd >= 0 ? p.intercept_l1[evd] : 0.0;
-            sdb_[d] = evd >= 0 ? p.intercept_l1[evd] - p.intercept[evd] : 0.0;
-        }
-    }
-    __syncthreads();
-    if (tid == 0) {
-        unsigned long long nz = 0ull;
-        unsigned int used = 0u, valid = 0u;
-        for (int d = 0; d < T; ++d) {
-            if (s_slot[d] < 0) continue;
-            valid |= 1u << d;
-            used |= 1u << d;
-            for (int j = 0; j < T; ++j)
-                if (sw_[d][j] != 0.0) { nz |= 1ull << (d * 8 + j); used |= 1u << j; }
-        }
-        s_nz = nz; s_used = used; s_valid = valid;
-    }
-    __syncthreads();
-    const unsigned long long nz = s_nz;
-    const unsigned int used = s_used, valid = s_valid;
-
-    double a1[T], a2[T], a3[T];
-#pragma unroll
-    for (int d = 0; d < T; ++d) { a1[d] = 0.0; a2[d] = 0.0; a3[d] = 0.0; }
-
-    const long long start = (long long)blockIdx.x * p.points_per_block;
-    long long stop = start + p.points_per_block;
-    if (stop > p.g.N) stop = p.g.N;
-    for (long long idx = start + tid; idx < stop; idx += 256) {
-        double c[T];
+__device__ __forceinline__ void residual_tile(const double* tile, const ResidWarp* ws, const FactorDesc* fac,
+                                              int npts, int lane, unsigned nz_lo, unsigned nz_hi, unsigned used,
+                                              unsigned valid, double (&a)[TMAX * 3]) {
+    const WarpProg* wp = &ws->prog;
+    const bool fast = wp->fast != 0;
+    for (int i = lane; i < npts; i += 64) {
+        const double* pt = tile + i;
+        const bool ok1 = (i + 32) < npts;
+        double c0[T], c1[T];
 #pragma unroll
         for (int t = 0; t < T; ++t) {
-            double v = 0.0;
+            double v0 = 0.0, v1 = 0.0;
             if (used >> t & 1u) {
-                const int f0 = foff[t], f1 = foff[t + 1];
-                v = apply_factor(sf[f0], ld_stream(sf[f0].ptr + idx));
-                for (int f = f0 + 1; f < f1; ++f) v *= apply_factor(sf[f], ld_stream(sf[f].ptr + idx));
+                if (fast) {
+                    const int4 d = wp->op[t];
+                    v0 = ipow123(pt[d.x], d.y);
+                    v1 = ipow123(pt[d.x + 32], d.y);
+                    if (d.z >= 0) { v0 *= ipow123(pt[d.z], d.w); v1 *= ipow123(pt[d.z + 32], d.w); }
+                } else {
+                    v0 = eval_term_generic(fac, wp->foff[t], wp->foff[t + 1], pt, RES_TILE);
+                    v1 = ok1 ? eval_term_generic(fac, wp->foff[t], wp->foff[t + 1], pt + 32, RES_TILE) : 0.0;
+                }
             }
-            c[t] = v;
+            c0[t] = v0; c1[t] = v1;
         }
 #pragma unroll
         for (int d = 0; d < T; ++d) {
             if (valid >> d & 1u) {
                 // np.dot(features, w) + b, then target - that  (fitness.py:137-140)
-                double pred = 0.0;
+                const unsigned rowm = ((d < 4 ? nz_lo : nz_hi) >> ((d & 3) * 8)) & 0xffu;
+                double p0 = 0.0, p1 = 0.0;
 #pragma unroll
                 for (int j = 0; j < T; ++j)
-                    if (nz >> (d * 8 + j) & 1ull) pred = fma(sw_[d][j], c[j], pred);
-                const double r = c[d] - (pred + sb_[d]);
-                const double r2 = r + sdb_[d];       // L2Fitness keeps the LASSO intercept (fitness.py:80)
-                a1[d] += fabs(r);
-                a2[d] += fabs(c[d]);
-                a3[d] = fma(r2, r2, a3[d]);
+                    if (rowm >> j & 1u) {
+                        const double w = ws->sw[d * TMAX + j];
+                        p0 = fma(w, c0[j], p0);
+                        p1 = fma(w, c1[j], p1);
+                    }
+                const double b1 = ws->sb[d], db = ws->sdb[d];
+                const double r0 = c0[d] - (p0 + b1);
+                const double q0 = r0 + db;            // L2Fitness keeps the LASSO intercept (fitness.py:80)
+                a[d * 3 + 0] += fabs(r0);
+                a[d * 3 + 1] += fabs(c0[d]);
+                a[d * 3 + 2] = fma(q0, q0, a[d * 3 + 2]);
+                if (ok1) {
+                    const double r1 = c1[d] - (p1 + b1);
+                    const double q1 = r1 + db;
+                    a[d * 3 + 0] += fabs(r1);
+                    a[d * 3 + 1] += fabs(c1[d]);
+                    a[d * 3 + 2] = fma(q1, q1, a[d * 3 + 2]);
+                }
             }
         }
     }
-    // block reduction: warp shuffle then fixed-order sum over the 8 warps
-    const int lane = tid & 31, wp = tid >> 5;
-#pragma unroll
-    for (int d = 0; d < T; ++d) {
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            a1[d] += __shfl_down_sync(0xffffffffu, a1[d], off);
-            a2[d] += __shfl_down_sync(0xffffffffu, a2[d], off);
-            a3[d] += __shfl_down_sync(0xffffffffu, a3[d], off);
+}
+
+__global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_tile_kernel(ResidParams p) {
+    extern __shared__ __align__(16) double smem[];
+    __shared__ const double* s_tok[MAXU];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nwarps = blockDim.x >> 5;
+    double* buf0 = smem;                                         // [2][U][RES_TILE]
+    const size_t buf_doubles = (size_t)p.U * RES_TILE;
+    ResidWarp* ws = (ResidWarp*)(smem + 2 * buf_doubles) + warp;
+    if (tid < MAXU) s_tok[tid] = p.tok[tid];
+
+    // ---- per-warp setup: the equation, its evals and weights
+    const int le = blockIdx.x * nwarps + warp;
+    const bool active = le < p.n_eq;
+    int T = 1;
+    unsigned valid = 0u, used = 0u, nz_lo = 0u, nz_hi = 0u;
+    if (active) {
+        const int e = p.eq_list[le];
+        const EqDesc* eq = p.eqs + e;
+        T = eq->T;
+        if (lane < TMAX) {
+            int4 d = eq->fastop[lane];
+            d.x *= RES_TILE;
+            if (d.z >= 0) d.z *= RES_TILE;
+            ws->prog.op[lane] = d;
         }
-        if (lane == 0) { sred[wp][d][0] = a1[d]; sred[wp][d][1] = a2[d]; sred[wp][d][2] = a3[d]; }
-    }
-    __syncthreads();
-    if (tid < T * 3) {
-        const int d = tid / 3, q = tid % 3;
-        double s = 0.0;
+        if (lane <= TMAX) ws->prog.foff[lane] = eq->fac_off[lane];
+        if (lane == 0) { ws->prog.T = T; ws->prog.fast = eq->fast; }
+        // lane d < T holds the eval id of target d
+        const int my_ev = (lane < T) ? p.slot_eval[e * TMAX + lane] : -1;
+        valid = __ballot_sync(0xffffffffu, my_ev >= 0);
+        if (lane < TMAX) {
+            const double b1 = my_ev >= 0 ? p.intercept_l1[my_ev] : 0.0;
+            ws->sb[lane] = b1;
+            ws->sdb[lane] = my_ev >= 0 ? b1 - p.intercept[my_ev] : 0.0;
+        }
 #pragma unroll
-        for (int w8 = 0; w8 < 8; ++w8) s += sred[w8][d][q];
-        p.partial[(((long long)blockIdx.y * gridDim.x + blockIdx.x) * TMAX + d) * 3 + q] = s;
+        for (int h = 0; h < 2; ++h) {
+            const int idx = lane + 32 * h;
+            const int d = idx >> 3, j = idx & 7;
+            const int evd = __shfl_sync(0xffffffffu, my_ev, d);
+            const double w = (evd >= 0 && j < T) ? p.wterm[(long long)evd * TMAX + j] : 0.0;
+            ws->sw[idx] = w;
+            const unsigned m = __ballot_sync(0xffffffffu, w != 0.0);
+            if (h == 0) nz_lo = m; else nz_hi = m;
+        }
+        used = valid;
+#pragma unroll
+        for (int d = 0; d < 4; ++d) used |= ((nz_lo >> (d * 8)) & 0xffu) | ((nz_hi >> (d * 8)) & 0xffu);
+    }
+    double a[TMAX * 3];
+#pragma unroll
+    for (int k = 0; k < TMAX * 3; ++k) a[k] = 0.0;
+    __syncthreads();
+
+    // ---- double-buffered walk over the tiles
+    auto issue = [&](int tI, double* dst_buf) {
+        const long long start = (long long)tI * RES_TILE;
+        const int npts = (int)((p.N - start) < RES_TILE ? (p.N - start) : RES_TILE);
+        const int total = p.U * (RES_TILE / 2);
+        for (int q = tid; q < total; q += blockDim.x) {
+            const int part = q & (RES_TILE / 2 - 1), us = q / (RES_TILE / 2);
+            const int c0 = part * 2;
+            const double* src = s_tok[us] + start + c0;
+            double* dst = dst_buf + (size_t)us * RES_TILE + c0;
+            if (c0 + 2 <= npts) cp_async16(dst, src);
+            else if (c0 < npts) cp_async8(dst, src);
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    int tI = blockIdx.y;
+    if (tI < p.n_tiles) issue(tI, buf0);
+    for (int k = 0; tI < p.n_tiles; tI += gridDim.y, ++k) {
+        double* cur = buf0 + (size_t)(k & 1) * buf_doubles;
+        const int nxt = tI + gridDim.y;
+        if (nxt < p.n_tiles) {
+            issue(nxt, buf0 + (size_t)((k + 1) & 1) * buf_doubles);
+            asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        }
+        __syncthreads();
+        if (active && valid) {
+            const long long start = (long long)tI * RES_TILE;
+            const int npts = (int)((p.N - start) < RES_TILE ? (p.N - start) : RES_TILE);
+#define RT(TT) residual_tile<TT>(cur, ws, p.factors, npts, lane, nz_lo, nz_hi, used, valid, a)
+            switch (T) {
+                case 1: RT(1); break;
+                case 2: RT(2); break;
+                case 3: RT(3); break;
+                case 4: RT(4); break;
+                case 5: RT(5); break;
+                case 6: RT(6); break;
+                case 7: RT(7); break;
+                default: RT(8); break;
+            }
+#undef RT
+        }
+        __syncthreads();            // everyone is done with `cur` before it is refilled
+    }
+    if (active) {
+        double* out = p.partial + ((size_t)blockIdx.y * p.n_eq + le) * TMAX * 3;
+#pragma unroll
+        for (int k = 0; k < TMAX * 3; ++k) {
+            double v = a[k];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+            if (lane == 0) out[k] = v;
+        }
     }
 }
 
-// fixed-order reduction of the per-block partial sums -> sums[eval][3]
+// fixed-order reduction of the per-CTA partial sums -> sums[eval][3]
 struct ResidFinalParams {
     const int* eq_list;
     const int* slot_eval;
     const double* partial;
     double* sums;
-    int blocks_per_eq;
+    int n_eq;
+    int n_cta;
 };
 
 __global__ void residual_final_kernel(ResidFinalParams p) {
@@ -726,13 +989,12 @@ __global__ void residual_final_kernel(ResidFinalParams p) {
     const int e = p.eq_list[le];
     const int tid = threadIdx.x;          // TMAX*3 threads
     if (tid >= TMAX * 3) return;
-    const int d = tid / 3, q = tid % 3;
+    const int d = tid / 3;
     const int ev = p.slot_eval[e * TMAX + d];
     if (ev < 0) return;
     double s = 0.0;
-    for (int b = 0; b < p.blocks_per_eq; ++b)
-        s += p.partial[(((long long)le * p.blocks_per_eq + b) * TMAX + d) * 3 + q];
-    p.sums[(long long)ev * 3 + q] = s;
+    for (int b = 0; b < p.n_cta; ++b) s += p.partial[((size_t)b * p.n_eq + le) * TMAX * 3 + tid];
+    p.sums[(long long)ev * 3 + (tid - d * 3)] = s;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -772,6 +1034,14 @@ struct AxisPlan {
     }
 };
 
+// split cells longer than `maxlen` into sub-cells (same segment id)
+static std::vector<AxisPlan::Cell> split_cells(const std::vector<AxisPlan::Cell>& in, int maxlen) {
+    std::vector<AxisPlan::Cell> out;
+    for (auto& c : in)
+        for (int lo = c.lo; lo < c.hi; lo += maxlen) out.push_back({c.seg, lo, std::min(c.hi, lo + maxlen)});
+    return out;
+}
+
 struct DevBuf {
     void* ptr = nullptr;
     size_t cap = 0;
@@ -799,16 +1069,17 @@ struct epde_ctx {
     std::map<int, double*> tokens;
     AxisPlan axes[EPDE_MAX_NDIM];
     bool geom_ready = false;
-    int BX = 256;
     Geom geom;
     int n_cells = 0;             // nA * nB * npieces
     DevBuf d_geom;               // packed geometry tables
-    DevBuf d_cells, d_seg, d_enc, d_out, d_partial, d_given;
+    DevBuf d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given;
     void* h_pinned = nullptr; size_t h_pinned_cap = 0;
     epde_batch* live = nullptr;
     long long launches = 0;
-    size_t cell_budget_bytes = (size_t)8 << 30;   // scratch cap for the cell Grams of one group
+    size_t cell_budget_bytes = (size_t)12 << 30;   // scratch cap for the cell Grams of one launch group
     int sm_count = 148;
+    int max_smem = 227 * 1024;
+    int gram_warps = GRAM_WARPS;   // EPDE_GRAM_WARPS=16 selects the 16-warp / 128-register variant
     // optional per-kernel-class device timing (epde_ctx_set_timing)
     bool timing = false;
     struct Span { int cls; cudaEvent_t a, b; };
@@ -868,39 +1139,42 @@ static int build_geometry(epde_ctx* c) {
     std::vector<AxisPlan::Cell> cellsA, cellsB;
     long long strideA = 0, strideB = 0;
     if (nd == 3) {
-        cellsA = c->axes[0].cells; cellsB = c->axes[1].cells;
+        cellsB = split_cells(c->axes[1].cells, TILE_ROWS);
+        int widestB = 1;
+        for (auto& cl : cellsB) widestB = std::max(widestB, cl.hi - cl.lo);
+        cellsA = split_cells(c->axes[0].cells, std::max(1, TILE_ROWS / widestB));
         strideA = c->shape[1] * c->shape[2]; strideB = c->shape[2];
     } else if (nd == 2) {
-        cellsA = {{0, 0, 1}}; cellsB = c->axes[0].cells;
+        cellsA = {{0, 0, 1}};
+        cellsB = split_cells(c->axes[0].cells, TILE_ROWS);
         strideA = 0; strideB = c->shape[1];
     } else {
         cellsA = {{0, 0, 1}}; cellsB = {{0, 0, 1}};
     }
     const AxisPlan& lastp = c->axes[last];
     const long long nl = c->shape[last];
-    c->BX = nl <= 64 ? 64 : (nl <= 128 ? 128 : 256);
-    const int BX = c->BX;
-    // pieces: sub-segments of the last axis no wider than BX
+    // pieces: sub-segments of the last axis no wider than a tile
     std::vector<int> piece_start, piece_seg;
-    for (auto& cl : lastp.cells) {
-        for (int lo = cl.lo; lo < cl.hi; lo += BX) { piece_start.push_back(lo); piece_seg.push_back(cl.seg); }
-    }
+    for (auto& cl : lastp.cells)
+        for (int lo = cl.lo; lo < cl.hi; lo += TILE_COLS) { piece_start.push_back(lo); piece_seg.push_back(cl.seg); }
     piece_start.push_back((int)nl);
     const int npieces = (int)piece_seg.size();
-    // chunks: runs of pieces with total width <= BX
+    // chunks: runs of pieces with total width <= TILE_COLS
     struct Chunk { int p_lo, np, col_lo, ncols; };
     std::vector<Chunk> chunks;
     for (int pI = 0; pI < npieces;) {
         int q = pI;
-        while (q < npieces && piece_start[q + 1] - piece_start[pI] <= BX) ++q;
+        while (q < npieces && piece_start[q + 1] - piece_start[pI] <= TILE_COLS) ++q;
         chunks.push_back({pI, q - pI, piece_start[pI], piece_start[q] - piece_start[pI]});
         pI = q;
     }
     const int nA = (int)cellsA.size(), nB = (int)cellsB.size();
     std::vector<UnitDesc> units;
     units.reserve((size_t)nA * nB * chunks.size());
+    int max_rows = 1;
     for (int a = 0; a < nA; ++a)
-        for (int b = 0; b < nB; ++b)
+        for (int b = 0; b < nB; ++b) {
+            max_rows = std::max(max_rows, (cellsA[a].hi - cellsA[a].lo) * (cellsB[b].hi - cellsB[b].lo));
             for (auto& ch : chunks) {
                 UnitDesc u;
                 memset(&u, 0, sizeof u);
@@ -911,12 +1185,18 @@ static int build_geometry(epde_ctx* c) {
                 u.piece_lo = ch.p_lo; u.npieces = ch.np;
                 units.push_back(u);
             }
-    // segment rows: axes stacked; marginal descriptors
+        }
+    // segment rows: axes stacked; marginal descriptors (cells of one segment are contiguous)
     std::vector<int> axis_row_base(nd + 1, 0);
     for (int d = 0; d < nd; ++d) axis_row_base[d + 1] = axis_row_base[d] + c->axes[d].nseg;
     const int n_rows = axis_row_base[nd];
     std::vector<MargDesc> marg(n_rows);
-    const long long Nloc = c->N;
+    auto seg_range = [](const std::vector<AxisPlan::Cell>& cl, int s, int& lo, int& hi, long long& width) {
+        lo = -1; hi = -1; width = 0;
+        for (int q = 0; q < (int)cl.size(); ++q)
+            if (cl[q].seg == s) { if (lo < 0) lo = q; hi = q + 1; width += cl[q].hi - cl[q].lo; }
+        if (lo < 0) { lo = 0; hi = 0; }
+    };
     for (int d = 0; d < nd; ++d) {
         for (int s = 0; s < c->axes[d].nseg; ++s) {
             MargDesc m;
@@ -928,43 +1208,41 @@ static int build_geometry(epde_ctx* c) {
                 int lo = -1, hi = -1;
                 for (int q = 0; q < npieces; ++q)
                     if (piece_seg[q] == s) { if (lo < 0) lo = q; hi = q + 1; width += piece_start[q + 1] - piece_start[q]; }
-                if (lo < 0) { m.p_lo = 0; m.p_hi = 0; } else { m.p_lo = lo; m.p_hi = hi; }
-            } else {
-                const bool isA = (nd == 3 && d == 0);
-                const std::vector<AxisPlan::Cell>& cl = isA ? cellsA : cellsB;
-                int lo = -1, hi = -1;
-                for (int q = 0; q < (int)cl.size(); ++q)
-                    if (cl[q].seg == s) { lo = q; hi = q + 1; width = cl[q].hi - cl[q].lo; }
                 if (lo < 0) { lo = 0; hi = 0; }
-                if (isA) { m.a_lo = lo; m.a_hi = hi; } else { m.b_lo = lo; m.b_hi = hi; }
+                m.p_lo = lo; m.p_hi = hi;
+            } else if (nd == 3 && d == 0) {
+                seg_range(cellsA, s, m.a_lo, m.a_hi, width);
+            } else {
+                seg_range(cellsB, s, m.b_lo, m.b_hi, width);
             }
-            m.count = (double)(width * (Nloc / c->shape[d]));
+            m.count = (double)(width * (c->N / c->shape[d]));
             marg[m.row] = m;
         }
     }
-    // windows
-    std::vector<int> win_hi, win_lo;
+    // windows: segment-row ranges; last entry = every row of axis 0 (all points)
+    std::vector<int> win_lo, win_hi;
     for (int d = 0; d < nd; ++d)
         for (size_t w = 0; w < c->axes[d].starts.size(); ++w) {
-            win_hi.push_back(axis_row_base[d] + c->axes[d].seg_hi[w] - 1);
-            win_lo.push_back(c->axes[d].seg_lo[w] > 0 ? axis_row_base[d] + c->axes[d].seg_lo[w] - 1 : -1);
+            win_lo.push_back(axis_row_base[d] + c->axes[d].seg_lo[w]);
+            win_hi.push_back(axis_row_base[d] + c->axes[d].seg_hi[w]);
         }
+    const int W = (int)win_lo.size();
+    win_lo.push_back(axis_row_base[0]);
+    win_hi.push_back(axis_row_base[1]);
     // pack and upload
     auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
     size_t o_units = 0;
     size_t o_piece = align(o_units + units.size() * sizeof(UnitDesc));
     size_t o_marg = align(o_piece + piece_start.size() * sizeof(int));
-    size_t o_base = align(o_marg + marg.size() * sizeof(MargDesc));
-    size_t o_whi = align(o_base + axis_row_base.size() * sizeof(int));
-    size_t o_wlo = align(o_whi + win_hi.size() * sizeof(int));
-    size_t total = align(o_wlo + win_lo.size() * sizeof(int));
+    size_t o_wlo = align(o_marg + marg.size() * sizeof(MargDesc));
+    size_t o_whi = align(o_wlo + win_lo.size() * sizeof(int));
+    size_t total = align(o_whi + win_hi.size() * sizeof(int));
     std::vector<char> host(total, 0);
     memcpy(host.data() + o_units, units.data(), units.size() * sizeof(UnitDesc));
     memcpy(host.data() + o_piece, piece_start.data(), piece_start.size() * sizeof(int));
     memcpy(host.data() + o_marg, marg.data(), marg.size() * sizeof(MargDesc));
-    memcpy(host.data() + o_base, axis_row_base.data(), axis_row_base.size() * sizeof(int));
-    memcpy(host.data() + o_whi, win_hi.data(), win_hi.size() * sizeof(int));
     memcpy(host.data() + o_wlo, win_lo.data(), win_lo.size() * sizeof(int));
+    memcpy(host.data() + o_whi, win_hi.data(), win_hi.size() * sizeof(int));
     if (c->d_geom.ensure(total)) return 1;
     CK(cudaMemcpy(c->d_geom.ptr, host.data(), total, cudaMemcpyHostToDevice));
     char* base = (char*)c->d_geom.ptr;
@@ -974,102 +1252,115 @@ static int build_geometry(epde_ctx* c) {
     g.n_units = (int)units.size();
     g.n_cells = nA * nB * npieces;
     g.n_rows = n_rows;
-    g.n_windows = (int)win_hi.size();
+    g.n_windows = W;
     g.ndim = nd;
-    g.total_row = axis_row_base[1] - 1;
+    g.max_rows = max_rows;
+    g.aligned16 = (nd == 1 || (nl % 2 == 0)) ? 1 : 0;
     g.N = c->N;
     g.units = (const UnitDesc*)(base + o_units);
     g.piece_start = (const int*)(base + o_piece);
     g.marg = (const MargDesc*)(base + o_marg);
-    g.axis_row_base = (const int*)(base + o_base);
-    g.win_hi_row = (const int*)(base + o_whi);
     g.win_lo_row = (const int*)(base + o_wlo);
+    g.win_hi_row = (const int*)(base + o_whi);
     c->n_cells = nA * nB * npieces;
     c->geom_ready = true;
     return 0;
 }
 
+struct LaunchGroup {             // equations evaluated together: <= MAXU distinct tokens, cell table within budget
+    std::vector<int> eqs;        // most terms first
+    std::vector<int> token_ids;  // slot -> token id
+    int list_off = 0;            // offset of the group's equation list inside d_lists
+    long long cell_doubles = 0;
+};
+
 struct epde_batch {
     epde_ctx* ctx = nullptr;
     int n_eq = 0, n_eval = 0, n_fac = 0;
     std::vector<EqDesc> eqs;
-    std::vector<std::vector<int>> eq_by_T;      // index T -> equation ids
+    std::vector<LaunchGroup> groups;
     std::vector<int> evals_gs8, evals_gs16;
     // device pointers into ctx->d_enc
     EqDesc* d_eqs = nullptr;
     FactorDesc* d_factors = nullptr;
     int* d_eval_eq = nullptr; int* d_eval_tgt = nullptr; int* d_slot_eval = nullptr;
-    int* d_lists = nullptr;                      // eq lists by T, eval lists by GS
-    std::vector<int> list_off_T;                 // offsets into d_lists
+    int* d_lists = nullptr;                      // equation lists by group, eval lists by GS
     int off_gs8 = 0, off_gs16 = 0;
     // outputs in ctx->d_out
     double* d_coef = nullptr; double* d_intercept = nullptr; double* d_stab = nullptr;
     double* d_sw = nullptr; double* d_wterm = nullptr; double* d_sums = nullptr; double* d_b1 = nullptr;
     int* d_nact = nullptr; int* d_allzero = nullptr; int* d_iters = nullptr;
     size_t out_bytes = 0;
-    long long seg_doubles = 0;
+    long long seg_doubles = 0, win_doubles = 0;
     int* d_mode = nullptr; double* d_given_w = nullptr; double* d_given_b = nullptr;
     bool solved = false;
 };
 
-template <int T>
-static int launch_gram(epde_ctx* c, epde_batch* b, const int* d_list, int n_eq, double* cells) {
+static size_t gram_smem_bytes(const epde_ctx* c, int U, int nwarps) {
+    return sizeof(double) * ((size_t)U * c->geom.max_rows * TILE_COLS + (size_t)nwarps * RED_CHUNK * (TILE_COLS + 1)) +
+           (size_t)nwarps * sizeof(WarpProg);
+}
+
+static int launch_gram_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double* cells) {
     GramParams p;
-    p.g = c->geom; p.eqs = b->d_eqs; p.factors = b->d_factors; p.eq_list = d_list; p.n_eq = n_eq; p.cells = cells;
-    const size_t smem = sizeof(double) * RED_CHUNK * (c->BX + 1);
-    const long long grid = (long long)c->geom.n_units * n_eq;
-    if (grid > 2147483647LL) return fail("pass A grid too large (%lld CTAs)", grid);
-    { KernelSpan ks(c, EPDE_KERNEL_GRAM); gram_cells_kernel<T><<<(unsigned)grid, c->BX, smem, c->stream>>>(p); }
+    memset(&p, 0, sizeof p);
+    p.g = c->geom; p.eqs = b->d_eqs; p.factors = b->d_factors;
+    p.eq_list = b->d_lists + g.list_off; p.n_eq = (int)g.eqs.size();
+    p.U = (int)g.token_ids.size();
+    for (int u = 0; u < p.U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
+    p.cells = cells;
+    // 8 warps x <= 255 registers (two rows per decode for every T) or 16 warps x <= 128 registers
+    int nw_cfg = c->gram_warps;
+    int nwarps = std::max(1, std::min(nw_cfg, p.n_eq));
+    const size_t smem = gram_smem_bytes(c, p.U, nwarps);
+    if (smem > (size_t)c->max_smem)
+        return fail("pass A tile needs %zu bytes of shared memory (> %d)", smem, c->max_smem);
+    {
+        KernelSpan ks(c, EPDE_KERNEL_GRAM);
+        if (nw_cfg <= 8) gram_tile_kernel<8><<<(unsigned)c->geom.n_units, nwarps * 32, smem, c->stream>>>(p);
+        else gram_tile_kernel<16><<<(unsigned)c->geom.n_units, nwarps * 32, smem, c->stream>>>(p);
+    }
     CK(cudaGetLastError());
     return 0;
 }
 
-static int dispatch_gram(int T, epde_ctx* c, epde_batch* b, const int* d_list, int n_eq, double* cells) {
-    switch (T) {
-        case 1: return launch_gram<1>(c, b, d_list, n_eq, cells);
-        case 2: return launch_gram<2>(c, b, d_list, n_eq, cells);
-        case 3: return launch_gram<3>(c, b, d_list, n_eq, cells);
-        case 4: return launch_gram<4>(c, b, d_list, n_eq, cells);
-        case 5: return launch_gram<5>(c, b, d_list, n_eq, cells);
-        case 6: return launch_gram<6>(c, b, d_list, n_eq, cells);
-        case 7: return launch_gram<7>(c, b, d_list, n_eq, cells);
-        case 8: return launch_gram<8>(c, b, d_list, n_eq, cells);
-    }
-    return fail("unsupported term count %d", T);
-}
-
-template <int T>
-static int launch_resid(epde_ctx* c, epde_batch* b, const int* d_list, int n_eq, double* sums) {
-    // enough CTAs to fill the machine a few times over, at least 64K points each on big grids
-    long long bpe = (c->N + 65535) / 65536;
-    const long long want = std::max<long long>(1, (long long)c->sm_count * 8 / std::max(1, n_eq));
-    bpe = std::max<long long>(1, std::min<long long>(bpe, std::max<long long>(want, 1)));
-    if (bpe > 65535) bpe = 65535;
-    long long ppb = (c->N + bpe - 1) / bpe;
-    ppb = (ppb + 255) / 256 * 256;
-    bpe = (c->N + ppb - 1) / ppb;
-    if (c->d_partial.ensure(sizeof(double) * (size_t)n_eq * bpe * TMAX * 3)) return 1;
+static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double* sums) {
+    const int U = (int)g.token_ids.size();
+    const long long n_tiles = (c->N + RES_TILE - 1) / RES_TILE;
+    const int ne = (int)g.eqs.size();
+    const int nwarps = std::max(1, std::min(RES_WARPS, ne));
+    const int gx = (ne + nwarps - 1) / nwarps;
     ResidParams p;
-    p.g = c->geom; p.eqs = b->d_eqs; p.factors = b->d_factors; p.eq_list = d_list; p.slot_eval = b->d_slot_eval;
-    p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.intercept_l1 = b->d_b1; p.partial = (double*)c->d_partial.ptr;
-    p.points_per_block = (int)ppb;
-    { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_kernel<T><<<dim3((unsigned)bpe, n_eq), 256, 0, c->stream>>>(p); }
+    memset(&p, 0, sizeof p);
+    p.N = c->N; p.eqs = b->d_eqs; p.factors = b->d_factors;
+    p.eq_list = b->d_lists + g.list_off; p.n_eq = ne; p.U = U; p.n_tiles = (int)n_tiles;
+    for (int u = 0; u < U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
+    p.slot_eval = b->d_slot_eval; p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.intercept_l1 = b->d_b1;
+    const size_t smem = sizeof(double) * 2 * (size_t)U * RES_TILE + (size_t)nwarps * sizeof(ResidWarp);
+    if (smem > (size_t)c->max_smem) return fail("pass B tiles need %zu bytes of shared memory", smem);
+    // CTAs per SM: shared memory and the 64K-register file (<= 128 registers per thread)
+    const int per_sm = std::max(1, std::min((int)((size_t)(c->max_smem + 1024) / (smem + 1024)), 16 / nwarps));
+    long long gy = std::max<long long>(1, (long long)c->sm_count * per_sm / gx);
+    gy = std::min<long long>(gy, n_tiles);
+    gy = std::min<long long>(gy, 65535);
+    if (c->d_partial.ensure(sizeof(double) * (size_t)gy * ne * TMAX * 3)) return 1;
+    p.partial = (double*)c->d_partial.ptr;
+    { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_tile_kernel<<<dim3(gx, (unsigned)gy), nwarps * 32, smem, c->stream>>>(p); }
     CK(cudaGetLastError());
     ResidFinalParams fp;
-    fp.eq_list = d_list; fp.slot_eval = b->d_slot_eval; fp.partial = (const double*)c->d_partial.ptr; fp.sums = sums;
-    fp.blocks_per_eq = (int)bpe;
-    { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_final_kernel<<<n_eq, 32, 0, c->stream>>>(fp); }
+    fp.eq_list = p.eq_list; fp.slot_eval = b->d_slot_eval; fp.partial = p.partial; fp.sums = sums;
+    fp.n_eq = ne; fp.n_cta = (int)gy;
+    { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_final_kernel<<<ne, 32, 0, c->stream>>>(fp); }
     CK(cudaGetLastError());
     return 0;
 }
-
 // ------------------------------------------------------------------------------------------
 // C ABI
 // ------------------------------------------------------------------------------------------
 extern "C" {
 
 const char* epde_last_error(void) { return g_err.c_str(); }
-const char* epde_version(void) { return "epde_b200 0.1.0 sm_100a"; }
+const char* epde_version(void) { return "epde_b200 0.2.0 sm_100a"; }
 
 int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx** out) {
     if (!out || !inner_shape) return fail("epde_ctx_create: null argument");
@@ -1087,6 +1378,29 @@ int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx**
     c->device = device;
     c->ndim = ndim;
     c->sm_count = prop.multiProcessorCount;
+    c->max_smem = (int)prop.sharedMemPerBlockOptin;
+    if (const char* ev = getenv("EPDE_GRAM_WARPS")) c->gram_warps = (atoi(ev) > 8) ? 16 : 8;
+    {
+        // dynamic shared memory limit = opt-in maximum minus the kernels' static shared memory
+        const void* fns[3] = {(const void*)gram_tile_kernel<8>, (const void*)gram_tile_kernel<16>,
+                              (const void*)residual_tile_kernel};
+        int dyn_max = c->max_smem;
+        for (int k = 0; k < 3; ++k) {
+            cudaFuncAttributes fa;
+            cudaError_t fe = cudaFuncGetAttributes(&fa, fns[k]);
+            if (fe == cudaSuccess) {
+                const int dyn = c->max_smem - (int)fa.sharedSizeBytes;
+                fe = cudaFuncSetAttribute(fns[k], cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+                dyn_max = std::min(dyn_max, dyn);
+            }
+            if (fe != cudaSuccess) {
+                delete c;
+                return fail("epde_ctx_create: cannot configure shared memory (%s); is this an sm_100 device?",
+                            cudaGetErrorString(fe));
+            }
+        }
+        c->max_smem = dyn_max;
+    }
     c->N = 1;
     for (int d = 0; d < ndim; ++d) {
         if (inner_shape[d] < 2) { delete c; return fail("epde_ctx_create: axis %d has %lld points (< 2)", d, (long long)inner_shape[d]); }
@@ -1104,7 +1418,7 @@ int epde_ctx_destroy(epde_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     for (auto& kv : c->tokens) cudaFree(kv.second);
-    c->d_geom.release(); c->d_cells.release(); c->d_seg.release(); c->d_enc.release();
+    c->d_geom.release(); c->d_cells.release(); c->d_seg.release(); c->d_win.release(); c->d_enc.release();
     c->d_out.release(); c->d_partial.release(); c->d_given.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto& sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -1255,8 +1569,8 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
     b->n_fac = fac_off[n_terms];
     std::vector<FactorDesc> factors(b->n_fac);
     b->eqs.resize(n_eq);
-    b->eq_by_T.assign(TMAX + 1, {});
-    long long s_off = 0;
+    const int W = c->geom.n_windows;
+    long long s_off = 0, w_off = 0;
     for (int e = 0; e < n_eq; ++e) {
         const int T = term_off[e + 1] - term_off[e];
         if (T < 1 || T > TMAX) { delete b; return fail("equation %d has %d terms; supported: 1..%d", e, T, TMAX); }
@@ -1264,25 +1578,86 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
         memset(&q, 0, sizeof q);
         q.T = T;
         for (int t = 0; t <= T; ++t) q.fac_off[t] = fac_off[term_off[e] + t];
+        for (int t = T + 1; t <= TMAX; ++t) q.fac_off[t] = q.fac_off[T];
         for (int t = 0; t < T; ++t) {
             const int nf = q.fac_off[t + 1] - q.fac_off[t];
             if (nf < 1 || nf > FMAXF) { delete b; return fail("equation %d term %d has %d factors; supported: 1..%d", e, t, nf, FMAXF); }
         }
         q.s_off = s_off;
         s_off += (long long)c->geom.n_rows * (nacc_of(T) + 1);
-        b->eq_by_T[T].push_back(e);
+        q.w_off = w_off;
+        w_off += (long long)(W + 1) * (nacc_of(T) + 1);
     }
     b->seg_doubles = s_off;
+    b->win_doubles = w_off;
     for (int f = 0; f < b->n_fac; ++f) {
-        auto it = c->tokens.find(fac_token[f]);
-        if (it == c->tokens.end()) { delete b; return fail("factor %d references token %d which is not in the cache", f, fac_token[f]); }
+        if (!c->tokens.count(fac_token[f])) { delete b; return fail("factor %d references token %d which is not in the cache", f, fac_token[f]); }
         FactorDesc& d = factors[f];
-        d.ptr = it->second;
+        memset(&d, 0, sizeof d);
         d.power = fac_power[f];
         d.kind = fac_kind ? fac_kind[f] : 0;
         d.param = fac_param ? fac_param[f] : 0.0;
         if (d.kind < 0 || d.kind > 3) { delete b; return fail("factor %d has unknown kind %d", f, d.kind); }
         d.ipow = (d.power == 1.0) ? 1 : (d.power == 2.0) ? 2 : (d.power == 3.0) ? 3 : 0;
+    }
+    // ---- launch groups: equations sorted by term count (most first); a group holds <= MAXU distinct
+    //      tokens and a cell table within the scratch budget
+    std::vector<int> order(n_eq);
+    for (int e = 0; e < n_eq; ++e) order[e] = e;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int bb) { return b->eqs[a].T > b->eqs[bb].T; });
+    {
+        LaunchGroup cur;
+        std::set<int> cur_tok;
+        auto flush = [&]() {
+            if (cur.eqs.empty()) return;
+            cur.token_ids.assign(cur_tok.begin(), cur_tok.end());
+            b->groups.push_back(cur);
+            cur = LaunchGroup();
+            cur_tok.clear();
+        };
+        for (int e : order) {
+            const EqDesc& q = b->eqs[e];
+            std::set<int> mine;
+            for (int f = q.fac_off[0]; f < q.fac_off[q.T]; ++f) mine.insert(fac_token[f]);
+            if ((int)mine.size() > MAXU) { delete b; return fail("equation %d references %d distinct tokens; supported: %d", e, (int)mine.size(), MAXU); }
+            std::set<int> uni = cur_tok;
+            uni.insert(mine.begin(), mine.end());
+            const long long cd = (long long)c->n_cells * nacc_of(q.T);
+            if (!cur.eqs.empty() && ((int)uni.size() > MAXU ||
+                                     (size_t)(cur.cell_doubles + cd) * sizeof(double) > c->cell_budget_bytes)) {
+                flush();
+                uni = mine;
+            }
+            cur_tok = uni;
+            cur.eqs.push_back(e);
+            cur.cell_doubles += cd;
+        }
+        flush();
+    }
+    // per group: slots, cell offsets, fast-path encoding
+    for (size_t gi = 0; gi < b->groups.size(); ++gi) {
+        LaunchGroup& g = b->groups[gi];
+        std::map<int, int> slot;
+        for (size_t u = 0; u < g.token_ids.size(); ++u) slot[g.token_ids[u]] = (int)u;
+        long long c_off = 0;
+        for (int e : g.eqs) {
+            EqDesc& q = b->eqs[e];
+            q.group = (int)gi;
+            q.c_off = c_off;
+            c_off += (long long)c->n_cells * nacc_of(q.T);
+            q.fast = 1;
+            for (int t = 0; t < TMAX; ++t) q.fastop[t] = make_int4(0, 1, -1, 1);
+            for (int t = 0; t < q.T; ++t) {
+                const int f0 = q.fac_off[t], f1 = q.fac_off[t + 1];
+                for (int f = f0; f < f1; ++f) {
+                    factors[f].slot = slot[fac_token[f]];
+                    if (factors[f].kind != 0 || factors[f].ipow == 0) q.fast = 0;
+                }
+                if (f1 - f0 > 2) q.fast = 0;
+                q.fastop[t].x = factors[f0].slot; q.fastop[t].y = factors[f0].ipow;
+                if (f1 - f0 >= 2) { q.fastop[t].z = factors[f0 + 1].slot; q.fastop[t].w = factors[f0 + 1].ipow; }
+            }
+        }
     }
     std::vector<int> slot_eval((size_t)n_eq * TMAX, -1);
     for (int v = 0; v < n_eval; ++v) {
@@ -1293,12 +1668,11 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
         slot_eval[(size_t)e * TMAX + t] = v;
         if (b->eqs[e].T + 1 <= 8) b->evals_gs8.push_back(v); else b->evals_gs16.push_back(v);
     }
-    // lists: equations by T, evals by group size
+    // lists: equations by group, evals by solver group size
     std::vector<int> lists;
-    b->list_off_T.assign(TMAX + 2, 0);
-    for (int T = 1; T <= TMAX; ++T) {
-        b->list_off_T[T] = (int)lists.size();
-        lists.insert(lists.end(), b->eq_by_T[T].begin(), b->eq_by_T[T].end());
+    for (auto& g : b->groups) {
+        g.list_off = (int)lists.size();
+        lists.insert(lists.end(), g.eqs.begin(), g.eqs.end());
     }
     b->off_gs8 = (int)lists.size();
     lists.insert(lists.end(), b->evals_gs8.begin(), b->evals_gs8.end());
@@ -1314,6 +1688,8 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
     const size_t o_slot = align(o_evtg + sizeof(int) * std::max(1, n_eval));
     const size_t o_list = align(o_slot + sizeof(int) * slot_eval.size());
     const size_t total = align(o_list + sizeof(int) * lists.size());
+    // the pinned buffer may still feed an earlier asynchronous copy
+    cudaStreamSynchronize(c->stream);
     if (ensure_pinned(c, total) || c->d_enc.ensure(total)) { delete b; return 1; }
     char* h = (char*)c->h_pinned;
     memcpy(h + o_eqs, b->eqs.data(), sizeof(EqDesc) * n_eq);
@@ -1331,7 +1707,6 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
     b->d_slot_eval = (int*)(d + o_slot);
     b->d_lists = (int*)(d + o_list);
     // outputs
-    const int W = c->geom.n_windows;
     const size_t ne = (size_t)std::max(1, n_eval);
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align(o + bytes); return r; };
@@ -1398,25 +1773,17 @@ int epde_batch_gram(epde_batch* b, double* dev_seg) {
         if (c->d_seg.ensure(sizeof(double) * (size_t)b->seg_doubles)) return 1;
         dev_seg = (double*)c->d_seg.ptr;
     }
-    // equations are processed in groups (same T) whose cell Grams fit the scratch budget
-    for (int T = 1; T <= TMAX; ++T) {
-        const std::vector<int>& lst = b->eq_by_T[T];
-        if (lst.empty()) continue;
-        const size_t per_eq = sizeof(double) * (size_t)c->n_cells * nacc_of(T);
-        int group = (int)std::max<size_t>(1, c->cell_budget_bytes / per_eq);
-        group = std::min<int>(group, (int)lst.size());
-        if (c->d_cells.ensure(per_eq * group)) return 1;
-        for (int g0 = 0; g0 < (int)lst.size(); g0 += group) {
-            const int ng = std::min<int>(group, (int)lst.size() - g0);
-            // cell Grams of the group's i-th equation start at i * n_cells * NACC
-            const int* d_list = b->d_lists + b->list_off_T[T] + g0;
-            if (dispatch_gram(T, c, b, d_list, ng, (double*)c->d_cells.ptr)) return 1;
-            MargParams mp;
-            mp.g = c->geom; mp.eqs = b->d_eqs; mp.eq_list = d_list; mp.cells = (const double*)c->d_cells.ptr; mp.seg = dev_seg;
-            dim3 grid(c->geom.n_rows, ng);
-            { KernelSpan ks(c, EPDE_KERNEL_MARGINAL); marginal_kernel<<<grid, 256, 0, c->stream>>>(mp); }
-            CK(cudaGetLastError());
-        }
+    long long need = 0;
+    for (auto& g : b->groups) need = std::max(need, g.cell_doubles);
+    if (c->d_cells.ensure(sizeof(double) * (size_t)need)) return 1;
+    for (auto& g : b->groups) {
+        if (launch_gram_group(c, b, g, (double*)c->d_cells.ptr)) return 1;
+        MargParams mp;
+        mp.g = c->geom; mp.eqs = b->d_eqs; mp.eq_list = b->d_lists + g.list_off;
+        mp.cells = (const double*)c->d_cells.ptr; mp.seg = dev_seg;
+        dim3 grid(c->geom.n_rows, (unsigned)g.eqs.size());
+        { KernelSpan ks(c, EPDE_KERNEL_MARGINAL); marginal_kernel<<<grid, 256, 0, c->stream>>>(mp); }
+        CK(cudaGetLastError());
     }
     return 0;
 }
@@ -1427,13 +1794,14 @@ int epde_batch_solve(epde_batch* b, const double* dev_seg) {
     CK(cudaSetDevice(c->device));
     double* seg = dev_seg ? (double*)dev_seg : (double*)c->d_seg.ptr;
     if (!seg) return fail("epde_batch_solve: no segment Grams (call epde_batch_gram first)");
-    PrefixParams pp;
-    pp.g = c->geom; pp.eqs = b->d_eqs; pp.n_eq = b->n_eq; pp.seg = seg;
-    { KernelSpan ks(c, EPDE_KERNEL_MARGINAL); prefix_kernel<<<dim3(c->ndim, b->n_eq), 64, 0, c->stream>>>(pp); }
+    if (c->d_win.ensure(sizeof(double) * (size_t)b->win_doubles)) return 1;
+    WindowParams wp;
+    wp.g = c->geom; wp.eqs = b->d_eqs; wp.seg = seg; wp.win = (double*)c->d_win.ptr;
+    { KernelSpan ks(c, EPDE_KERNEL_MARGINAL); window_gram_kernel<<<dim3(c->geom.n_windows + 1, b->n_eq), 64, 0, c->stream>>>(wp); }
     CK(cudaGetLastError());
     if (b->n_eval > 0) {
         SolveParams sp;
-        sp.g = c->geom; sp.eqs = b->d_eqs; sp.eval_eq = b->d_eval_eq; sp.eval_tgt = b->d_eval_tgt; sp.seg = seg;
+        sp.g = c->geom; sp.eqs = b->d_eqs; sp.eval_eq = b->d_eval_eq; sp.eval_tgt = b->d_eval_tgt; sp.win = (const double*)c->d_win.ptr;
         sp.mode = b->d_mode; sp.given_wterm = b->d_given_w; sp.given_b = b->d_given_b;
         sp.coef = b->d_coef; sp.intercept = b->d_intercept; sp.intercept_l1 = b->d_b1; sp.stability = b->d_stab; sp.sw = b->d_sw;
         sp.wterm = b->d_wterm; sp.n_active = b->d_nact; sp.all_zero = b->d_allzero; sp.iters = b->d_iters;
@@ -1460,23 +1828,8 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
     CK(cudaSetDevice(c->device));
     double* sums = dev_sums ? dev_sums : b->d_sums;
     if (b->n_eval == 0) return 0;
-    for (int T = 1; T <= TMAX; ++T) {
-        const std::vector<int>& lst = b->eq_by_T[T];
-        if (lst.empty()) continue;
-        const int* d_list = b->d_lists + b->list_off_T[T];
-        int rc = 0;
-        switch (T) {
-            case 1: rc = launch_resid<1>(c, b, d_list, (int)lst.size(), sums); break;
-            case 2: rc = launch_resid<2>(c, b, d_list, (int)lst.size(), sums); break;
-            case 3: rc = launch_resid<3>(c, b, d_list, (int)lst.size(), sums); break;
-            case 4: rc = launch_resid<4>(c, b, d_list, (int)lst.size(), sums); break;
-            case 5: rc = launch_resid<5>(c, b, d_list, (int)lst.size(), sums); break;
-            case 6: rc = launch_resid<6>(c, b, d_list, (int)lst.size(), sums); break;
-            case 7: rc = launch_resid<7>(c, b, d_list, (int)lst.size(), sums); break;
-            case 8: rc = launch_resid<8>(c, b, d_list, (int)lst.size(), sums); break;
-        }
-        if (rc) return rc;
-    }
+    for (auto& g : b->groups)
+        if (launch_resid_group(c, b, g, sums)) return 1;
     return 0;
 }
 
