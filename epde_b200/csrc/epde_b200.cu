@@ -35,6 +35,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstddef>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -54,7 +55,7 @@
 #define GRAM_WARPS 8           // warps per pass-A CTA
 #define RED_CHUNK 8            // Gram entries reduced per shared-memory round of the cell flush
 #define MAXU 12                // distinct tokens per launch group (tile = MAXU x 64 x 32 doubles = 192 KB)
-#define RES_WARPS 16           // warps (= equations) per pass-B CTA
+#define RES_WARPS 8            // warps per pass-B CTA (8 x <= 255 registers, or 16 x <= 128: EPDE_RESID_WARPS)
 #define RES_TILE 1024          // points of a pass-B tile
 
 static thread_local std::string g_err;
@@ -190,7 +191,7 @@ __device__ __forceinline__ double eval_term_generic(const FactorDesc* fac, int f
 
 // per-warp copy of the equation being processed (shared memory)
 struct WarpProg {
-    int4 op[TMAX];           // fast terms: {offset0, ipow0, offset1 or -1, ipow1} (offsets in doubles)
+    int4 op[TMAX];           // fast terms: {offset0, ipow0, offset1 or -1, ipow1} (byte offsets of the slots)
     int foff[TMAX + 1];      // generic path: factor ranges
     int T, fast, pad0, pad1;
 };
@@ -215,6 +216,28 @@ struct GramParams {
     double* cells;           // cell-Gram scratch of the group
 };
 
+// explicit shared-space accesses: the per-equation worker functions are not inlined, so a generic
+// pointer would cost 64-bit address arithmetic and generic loads on every operand fetch
+__device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ double lds_f64(unsigned a) {
+    double v;
+    asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ int4 lds_v4(unsigned a) {
+    int4 v;
+    asm("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ double lds_f64_volatile(unsigned a) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_f64_volatile(unsigned a, double v) {
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory");
+}
+
 template <int T>
 __device__ __forceinline__ void gram_accumulate(double (&acc)[T * (T + 3) / 2], const double (&c)[T]) {
     int k = 0;
@@ -226,42 +249,50 @@ __device__ __forceinline__ void gram_accumulate(double (&acc)[T * (T + 3) / 2], 
     for (int i = 0; i < T; ++i) { acc[k] += c[i]; ++k; }
 }
 
-template <int T>
-__device__ __forceinline__ void fast_terms(const WarpProg* wp, const double* pr, double (&c)[T]) {
+// fast terms for R consecutive tile rows of one lane.  ops: shared address of the warp's int4 op table
+// {byte offset of factor 0's slot, ipow0, byte offset of factor 1's slot or -1, ipow1}; pr: shared
+// address of the lane's element in row `row` of slot 0; rows are ROWB bytes apart.
+template <int T, int R, int ROWB>
+__device__ __forceinline__ void fast_terms_r(unsigned ops, unsigned pr, double (&c)[R][T]) {
 #pragma unroll
     for (int t = 0; t < T; ++t) {
-        const int4 d = wp->op[t];
-        double x = ipow123(pr[d.x], d.y);
-        if (d.z >= 0) x *= ipow123(pr[d.z], d.w);
-        c[t] = x;
-    }
-}
-
-template <int T>
-__device__ __forceinline__ void fast_terms2(const WarpProg* wp, const double* pr, double (&c0)[T], double (&c1)[T]) {
+        const int4 d = lds_v4(ops + t * 16);
+        double x[R];
 #pragma unroll
-    for (int t = 0; t < T; ++t) {
-        const int4 d = wp->op[t];
-        double x0 = pr[d.x], x1 = pr[d.x + TILE_COLS];
+        for (int r = 0; r < R; ++r) x[r] = lds_f64(pr + d.x + r * ROWB);
         if (d.y >= 2) {
-            const double s0 = x0 * x0, s1 = x1 * x1;
-            if (d.y == 3) { x0 *= s0; x1 *= s1; } else { x0 = s0; x1 = s1; }
+            if (d.y == 3) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) x[r] = x[r] * x[r] * x[r];
+            } else {
+#pragma unroll
+                for (int r = 0; r < R; ++r) x[r] = x[r] * x[r];
+            }
         }
         if (d.z >= 0) {
-            double y0 = pr[d.z], y1 = pr[d.z + TILE_COLS];
+            double y[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) y[r] = lds_f64(pr + d.z + r * ROWB);
             if (d.w >= 2) {
-                const double s0 = y0 * y0, s1 = y1 * y1;
-                if (d.w == 3) { y0 *= s0; y1 *= s1; } else { y0 = s0; y1 = s1; }
+                if (d.w == 3) {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) y[r] = y[r] * y[r] * y[r];
+                } else {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) y[r] = y[r] * y[r];
+                }
             }
-            x0 *= y0; x1 *= y1;
+#pragma unroll
+            for (int r = 0; r < R; ++r) x[r] *= y[r];
         }
-        c0[t] = x0; c1[t] = x1;
+#pragma unroll
+        for (int r = 0; r < R; ++r) c[r][t] = x[r];
     }
 }
 
 // flush: sum the lanes (columns) of every piece, RED_CHUNK Gram entries per round
 template <int T>
-__device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2], int lane, double* red, double* out,
+__device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2], int lane, unsigned red, double* out,
                                             int piece_lo, int npieces, int col_lo, const int* __restrict__ piece_start) {
     constexpr int NACC = T * (T + 3) / 2;
     constexpr int RS = TILE_COLS + 1;
@@ -271,7 +302,7 @@ __device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2]
         __syncwarp();
 #pragma unroll
         for (int k = 0; k < RED_CHUNK; ++k)
-            if (b0 + k < NACC) red[k * RS + lane] = acc[b0 + k];
+            if (b0 + k < NACC) sts_f64_volatile(red + (k * RS + lane) * 8, acc[b0 + k]);
         __syncwarp();
         const int nout = npieces * cnt;
         for (int o = lane; o < nout; o += 32) {
@@ -279,36 +310,37 @@ __device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2]
             const int lo = piece_start[piece_lo + pp] - col_lo;
             const int hi = piece_start[piece_lo + pp + 1] - col_lo;
             double s = 0.0;
-            for (int cidx = lo; cidx < hi; ++cidx) s += red[k * RS + cidx];
+            for (int cidx = lo; cidx < hi; ++cidx) s += lds_f64_volatile(red + (k * RS + cidx) * 8);
             out[(long long)pp * NACC + b0 + k] = s;
         }
     }
     __syncwarp();
 }
 
-// fast path: every term = x^p [* y^q], p, q in {1, 2, 3}; TWO = two tile rows per decode
-template <int T, bool TWO>
-__device__ __noinline__ void gram_warp_fast(const double* tile, const WarpProg* wp, int nrows, int lane, double* red,
+// fast path: every term = x^p [* y^q], p, q in {1, 2, 3}; R tile rows per decode
+template <int T, int R>
+__device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, int nrows, int lane, unsigned red,
                                             double* out, int piece_lo, int npieces, int col_lo,
                                             const int* __restrict__ piece_start) {
     constexpr int NACC = T * (T + 3) / 2;
+    constexpr int ROWB = TILE_COLS * 8;
     double acc[NACC];
 #pragma unroll
     for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
-    const double* base = tile + lane;
+    const unsigned base = tile + lane * 8;
     int row = 0;
-    if (TWO) {
-        for (; row + 2 <= nrows; row += 2) {
-            double c0[T], c1[T];
-            fast_terms2<T>(wp, base + row * TILE_COLS, c0, c1);
-            gram_accumulate<T>(acc, c0);
-            gram_accumulate<T>(acc, c1);
+    if (R > 1) {
+        for (; row + R <= nrows; row += R) {
+            double c[R][T];
+            fast_terms_r<T, R, ROWB>(ops, base + row * ROWB, c);
+#pragma unroll
+            for (int r = 0; r < R; ++r) gram_accumulate<T>(acc, c[r]);
         }
     }
     for (; row < nrows; ++row) {
-        double c[T];
-        fast_terms<T>(wp, base + row * TILE_COLS, c);
-        gram_accumulate<T>(acc, c);
+        double c[1][T];
+        fast_terms_r<T, 1, ROWB>(ops, base + row * ROWB, c);
+        gram_accumulate<T>(acc, c[0]);
     }
     flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start);
 }
@@ -316,7 +348,7 @@ __device__ __noinline__ void gram_warp_fast(const double* tile, const WarpProg* 
 // generic path: any factor kind / power / factor count
 template <int T>
 __device__ __noinline__ void gram_warp_generic(const double* tile, int tstride, const WarpProg* wp,
-                                               const FactorDesc* fac, int nrows, int lane, double* red, double* out,
+                                               const FactorDesc* fac, int nrows, int lane, unsigned red, double* out,
                                                int piece_lo, int npieces, int col_lo,
                                                const int* __restrict__ piece_start) {
     constexpr int NACC = T * (T + 3) / 2;
@@ -338,10 +370,14 @@ template <int T, int NW>
 __device__ __forceinline__ void gram_warp(const double* tile, int tstride, const WarpProg* wp, const FactorDesc* fac,
                                           int nrows, int lane, double* red, double* out, int piece_lo, int npieces,
                                           int col_lo, const int* __restrict__ piece_start) {
-    // 8-warp CTAs may use 255 registers per thread: two rows per decode for every T
-    constexpr bool TWO = (NW <= 8) || (T <= 6);
-    if (wp->fast) gram_warp_fast<T, TWO>(tile, wp, nrows, lane, red, out, piece_lo, npieces, col_lo, piece_start);
-    else gram_warp_generic<T>(tile, tstride, wp, fac, nrows, lane, red, out, piece_lo, npieces, col_lo, piece_start);
+    // 8-warp CTAs may use 255 registers per thread: four rows per decode (two for the widest equations)
+    constexpr int R = (NW <= 8) ? (T <= 6 ? 4 : 2) : (T <= 4 ? 4 : (T <= 6 ? 2 : 1));
+    if (wp->fast)
+        gram_warp_fast<T, R>(smem_addr(tile), smem_addr(wp->op), nrows, lane, smem_addr(red), out, piece_lo, npieces,
+                             col_lo, piece_start);
+    else
+        gram_warp_generic<T>(tile, tstride, wp, fac, nrows, lane, smem_addr(red), out, piece_lo, npieces, col_lo,
+                             piece_start);
 }
 
 template <int NW>
@@ -395,9 +431,9 @@ __global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
         const int T = eq->T;
         __syncwarp();
         if (lane < TMAX) {
-            int4 d = eq->fastop[lane];
-            d.x *= tstride;
-            if (d.z >= 0) d.z *= tstride;
+            int4 d = eq->fastop[lane];            // slots -> byte offsets inside the tile
+            d.x *= tstride * 8;
+            if (d.z >= 0) d.z *= tstride * 8;
             wp->op[lane] = d;
         }
         if (lane <= TMAX) wp->foff[lane] = eq->fac_off[lane];
@@ -776,12 +812,12 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
 
 // ------------------------------------------------------------------------------------------
 // pass B: residual sums per eval: sum|r|, sum|t|, sum r2^2 with r = t - (F w + b1), r2 = t - (F w + b)
-// (fitness.py:135-142 and 70-83).  A WARP owns one equation (all of its evals: slot d = target term
-// d) for the whole kernel: its program and weights sit in a per-warp shared scratch, its sums in
-// registers.  The CTA (up to RES_WARPS equations) walks over tiles of RES_TILE consecutive points,
-// blockIdx.y-strided; the tile of every token of the launch group is double-buffered in shared
-// memory with cp.async, lane <-> point, two points per decode.  One partial row per (CTA.y,
-// equation) is written at the end and reduced in fixed order by residual_final_kernel.
+// (fitness.py:135-142 and 70-83).  Persistent CTAs walk over tiles of RES_TILE consecutive points
+// (double-buffered in shared memory with cp.async).  Each CTA first builds the "residual program" of
+// every equation of the launch in shared memory (term ops, weights of every eval, masks); then, per
+// tile, its warps take equations from the list dynamically (longest first) and evaluate all evals of
+// that equation on the tile, lane <-> point, two points per decode.  Tile sums are added to a per-CTA
+// shared table in tile order (fixed order), written once per CTA and reduced by residual_final_kernel.
 // ------------------------------------------------------------------------------------------
 struct ResidParams {
     long long N;
@@ -796,125 +832,197 @@ struct ResidParams {
     const double* wterm;     // [n_eval][TMAX]
     const double* intercept; // [n_eval]
     const double* intercept_l1;  // [n_eval]
-    double* partial;         // [gridDim.y][n_eq][TMAX][3]
+    double* partial;         // [gridDim.x][n_eq][TMAX][3]
 };
 
-struct ResidWarp {           // per-warp shared scratch
-    WarpProg prog;
+struct ResidProg {           // per-equation program in shared memory (16-byte aligned)
+    int4 op[TMAX];           // fast terms (byte offsets of the slots inside a tile buffer)
     double sw[TMAX * TMAX];  // [d][j] coefficient of term j for the eval with target d
     double sb[TMAX], sdb[TMAX];
+    int foff[TMAX + 1];
+    int T, fast;
+    unsigned valid, used, nz_lo, nz_hi;
+    int pad;
 };
 
-// one tile for one equation; a[d*3 + q] are the running sums of the warp's lane
+// residual contributions of two points (c[0], c[1]) to every valid eval of the equation
 template <int T>
-__device__ __forceinline__ void residual_tile(const double* tile, const ResidWarp* ws, const FactorDesc* fac,
-                                              int npts, int lane, unsigned nz_lo, unsigned nz_hi, unsigned used,
-                                              unsigned valid, double (&a)[TMAX * 3]) {
-    const WarpProg* wp = &ws->prog;
-    const bool fast = wp->fast != 0;
-    for (int i = lane; i < npts; i += 64) {
-        const double* pt = tile + i;
-        const bool ok1 = (i + 32) < npts;
-        double c0[T], c1[T];
+__device__ __forceinline__ void residual_accumulate(const double (&c)[2][T], bool ok1, unsigned valid, unsigned nz_lo,
+                                                    unsigned nz_hi, unsigned sw_a, unsigned sb_a, unsigned sdb_a,
+                                                    double (&a)[T * 3]) {
 #pragma unroll
-        for (int t = 0; t < T; ++t) {
-            double v0 = 0.0, v1 = 0.0;
-            if (used >> t & 1u) {
-                if (fast) {
-                    const int4 d = wp->op[t];
-                    v0 = ipow123(pt[d.x], d.y);
-                    v1 = ipow123(pt[d.x + 32], d.y);
-                    if (d.z >= 0) { v0 *= ipow123(pt[d.z], d.w); v1 *= ipow123(pt[d.z + 32], d.w); }
-                } else {
-                    v0 = eval_term_generic(fac, wp->foff[t], wp->foff[t + 1], pt, RES_TILE);
-                    v1 = ok1 ? eval_term_generic(fac, wp->foff[t], wp->foff[t + 1], pt + 32, RES_TILE) : 0.0;
-                }
-            }
-            c0[t] = v0; c1[t] = v1;
-        }
-#pragma unroll
-        for (int d = 0; d < T; ++d) {
-            if (valid >> d & 1u) {
-                // np.dot(features, w) + b, then target - that  (fitness.py:137-140)
-                const unsigned rowm = ((d < 4 ? nz_lo : nz_hi) >> ((d & 3) * 8)) & 0xffu;
-                double p0 = 0.0, p1 = 0.0;
+    for (int d = 0; d < T; ++d) {
+        if (valid >> d & 1u) {
+            // np.dot(features, w) + b, then target - that  (fitness.py:137-140)
+            const unsigned rowm = ((d < 4 ? nz_lo : nz_hi) >> ((d & 3) * 8)) & 0xffu;
+            double p0 = 0.0, p1 = 0.0;
+            if (rowm) {
 #pragma unroll
                 for (int j = 0; j < T; ++j)
                     if (rowm >> j & 1u) {
-                        const double w = ws->sw[d * TMAX + j];
-                        p0 = fma(w, c0[j], p0);
-                        p1 = fma(w, c1[j], p1);
+                        const double w = lds_f64(sw_a + (d * TMAX + j) * 8);
+                        p0 = fma(w, c[0][j], p0);
+                        p1 = fma(w, c[1][j], p1);
                     }
-                const double b1 = ws->sb[d], db = ws->sdb[d];
-                const double r0 = c0[d] - (p0 + b1);
-                const double q0 = r0 + db;            // L2Fitness keeps the LASSO intercept (fitness.py:80)
-                a[d * 3 + 0] += fabs(r0);
-                a[d * 3 + 1] += fabs(c0[d]);
-                a[d * 3 + 2] = fma(q0, q0, a[d * 3 + 2]);
-                if (ok1) {
-                    const double r1 = c1[d] - (p1 + b1);
-                    const double q1 = r1 + db;
-                    a[d * 3 + 0] += fabs(r1);
-                    a[d * 3 + 1] += fabs(c1[d]);
-                    a[d * 3 + 2] = fma(q1, q1, a[d * 3 + 2]);
-                }
+            }
+            const double b1 = lds_f64(sb_a + d * 8), db = lds_f64(sdb_a + d * 8);
+            const double r0 = c[0][d] - (p0 + b1);
+            const double q0 = r0 + db;            // L2Fitness keeps the LASSO intercept (fitness.py:80)
+            double r1 = c[1][d] - (p1 + b1);
+            double q1 = r1 + db;
+            double t1 = c[1][d];
+            if (!ok1) { r1 = 0.0; q1 = 0.0; t1 = 0.0; }
+            a[d * 3 + 0] += fabs(r0) + fabs(r1);
+            a[d * 3 + 1] += fabs(c[0][d]) + fabs(t1);
+            a[d * 3 + 2] = fma(q0, q0, fma(q1, q1, a[d * 3 + 2]));
+        }
+    }
+}
+
+template <int T>
+__device__ __forceinline__ void residual_reduce(const double (&a)[T * 3], unsigned valid, int lane, double* table_row) {
+#pragma unroll
+    for (int d = 0; d < T; ++d) {
+        if (valid >> d & 1u) {
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+                double v = a[d * 3 + q];
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+                if (lane == 0) table_row[d * 3 + q] += v;
             }
         }
     }
 }
 
-__global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_tile_kernel(ResidParams p) {
+// one (tile, equation) task, fast terms; returns through the shared table row
+template <int T>
+__device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, unsigned valid, unsigned used,
+                                                unsigned nz_lo, unsigned nz_hi, int npts, int lane, double* table_row) {
+    const unsigned sw_a = prog + (unsigned)offsetof(ResidProg, sw);
+    const unsigned sb_a = prog + (unsigned)offsetof(ResidProg, sb);
+    const unsigned sdb_a = prog + (unsigned)offsetof(ResidProg, sdb);
+    double a[T * 3];
+#pragma unroll
+    for (int k = 0; k < T * 3; ++k) a[k] = 0.0;
+    for (int i = lane; i < npts; i += 64) {
+        const bool ok1 = (i + 32) < npts;
+        double c[2][T];
+        const unsigned pt = tile + i * 8;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            double v0 = 0.0, v1 = 0.0;
+            if (used >> t & 1u) {
+                const int4 d = lds_v4(prog + t * 16);
+                v0 = lds_f64(pt + d.x);
+                v1 = lds_f64(pt + d.x + 256);
+                if (d.y >= 2) {
+                    if (d.y == 3) { v0 = v0 * v0 * v0; v1 = v1 * v1 * v1; } else { v0 *= v0; v1 *= v1; }
+                }
+                if (d.z >= 0) {
+                    double y0 = lds_f64(pt + d.z), y1 = lds_f64(pt + d.z + 256);
+                    if (d.w >= 2) {
+                        if (d.w == 3) { y0 = y0 * y0 * y0; y1 = y1 * y1 * y1; } else { y0 *= y0; y1 *= y1; }
+                    }
+                    v0 *= y0; v1 *= y1;
+                }
+            }
+            c[0][t] = v0; c[1][t] = v1;
+        }
+        residual_accumulate<T>(c, ok1, valid, nz_lo, nz_hi, sw_a, sb_a, sdb_a, a);
+    }
+    residual_reduce<T>(a, valid, lane, table_row);
+}
+
+// same, generic terms (any kind / power / factor count)
+template <int T>
+__device__ __noinline__ void residual_task_generic(const double* tile_g, unsigned prog, const ResidProg* rp,
+                                                   const FactorDesc* fac, int npts, int lane, double* table_row) {
+    const unsigned valid = rp->valid, used = rp->used, nz_lo = rp->nz_lo, nz_hi = rp->nz_hi;
+    const unsigned sw_a = prog + (unsigned)offsetof(ResidProg, sw);
+    const unsigned sb_a = prog + (unsigned)offsetof(ResidProg, sb);
+    const unsigned sdb_a = prog + (unsigned)offsetof(ResidProg, sdb);
+    double a[T * 3];
+#pragma unroll
+    for (int k = 0; k < T * 3; ++k) a[k] = 0.0;
+    for (int i = lane; i < npts; i += 64) {
+        const bool ok1 = (i + 32) < npts;
+        double c[2][T];
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            double v0 = 0.0, v1 = 0.0;
+            if (used >> t & 1u) {
+                v0 = eval_term_generic(fac, rp->foff[t], rp->foff[t + 1], tile_g + i, RES_TILE);
+                if (ok1) v1 = eval_term_generic(fac, rp->foff[t], rp->foff[t + 1], tile_g + i + 32, RES_TILE);
+            }
+            c[0][t] = v0; c[1][t] = v1;
+        }
+        residual_accumulate<T>(c, ok1, valid, nz_lo, nz_hi, sw_a, sb_a, sdb_a, a);
+    }
+    residual_reduce<T>(a, valid, lane, table_row);
+}
+
+template <int T>
+__device__ __forceinline__ void residual_task(unsigned tile, const double* tile_g, unsigned prog, const ResidProg* rp,
+                                              const FactorDesc* fac, int npts, int lane, double* table_row) {
+    if (rp->fast) residual_task_fast<T>(tile, prog, rp->valid, rp->used, rp->nz_lo, rp->nz_hi, npts, lane, table_row);
+    else residual_task_generic<T>(tile_g, prog, rp, fac, npts, lane, table_row);
+}
+
+template <int NW>
+__global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p) {
     extern __shared__ __align__(16) double smem[];
     __shared__ const double* s_tok[MAXU];
+    __shared__ int s_next;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int nwarps = blockDim.x >> 5;
     double* buf0 = smem;                                         // [2][U][RES_TILE]
     const size_t buf_doubles = (size_t)p.U * RES_TILE;
-    ResidWarp* ws = (ResidWarp*)(smem + 2 * buf_doubles) + warp;
+    ResidProg* progs = (ResidProg*)(smem + 2 * buf_doubles);     // [n_eq]
+    double* table = (double*)(progs + p.n_eq);                   // [n_eq][TMAX][3]
     if (tid < MAXU) s_tok[tid] = p.tok[tid];
+    for (int q = tid; q < p.n_eq * TMAX * 3; q += blockDim.x) table[q] = 0.0;
 
-    // ---- per-warp setup: the equation, its evals and weights
-    const int le = blockIdx.x * nwarps + warp;
-    const bool active = le < p.n_eq;
-    int T = 1;
-    unsigned valid = 0u, used = 0u, nz_lo = 0u, nz_hi = 0u;
-    if (active) {
+    // ---- build the programs: warp w builds equations w, w + nwarps, ...
+    for (int le = warp; le < p.n_eq; le += nwarps) {
         const int e = p.eq_list[le];
         const EqDesc* eq = p.eqs + e;
-        T = eq->T;
+        ResidProg* rp = progs + le;
+        const int T = eq->T;
         if (lane < TMAX) {
             int4 d = eq->fastop[lane];
-            d.x *= RES_TILE;
-            if (d.z >= 0) d.z *= RES_TILE;
-            ws->prog.op[lane] = d;
+            d.x *= RES_TILE * 8;
+            if (d.z >= 0) d.z *= RES_TILE * 8;
+            rp->op[lane] = d;
         }
-        if (lane <= TMAX) ws->prog.foff[lane] = eq->fac_off[lane];
-        if (lane == 0) { ws->prog.T = T; ws->prog.fast = eq->fast; }
+        if (lane <= TMAX) rp->foff[lane] = eq->fac_off[lane];
         // lane d < T holds the eval id of target d
         const int my_ev = (lane < T) ? p.slot_eval[e * TMAX + lane] : -1;
-        valid = __ballot_sync(0xffffffffu, my_ev >= 0);
+        const unsigned valid = __ballot_sync(0xffffffffu, my_ev >= 0);
         if (lane < TMAX) {
             const double b1 = my_ev >= 0 ? p.intercept_l1[my_ev] : 0.0;
-            ws->sb[lane] = b1;
-            ws->sdb[lane] = my_ev >= 0 ? b1 - p.intercept[my_ev] : 0.0;
+            rp->sb[lane] = b1;
+            rp->sdb[lane] = my_ev >= 0 ? b1 - p.intercept[my_ev] : 0.0;
         }
+        unsigned nz_lo = 0u, nz_hi = 0u;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int idx = lane + 32 * h;
             const int d = idx >> 3, j = idx & 7;
             const int evd = __shfl_sync(0xffffffffu, my_ev, d);
             const double w = (evd >= 0 && j < T) ? p.wterm[(long long)evd * TMAX + j] : 0.0;
-            ws->sw[idx] = w;
+            rp->sw[idx] = w;
             const unsigned m = __ballot_sync(0xffffffffu, w != 0.0);
             if (h == 0) nz_lo = m; else nz_hi = m;
         }
-        used = valid;
+        unsigned used = valid;
 #pragma unroll
         for (int d = 0; d < 4; ++d) used |= ((nz_lo >> (d * 8)) & 0xffu) | ((nz_hi >> (d * 8)) & 0xffu);
+        if (lane == 0) {
+            rp->T = T; rp->fast = eq->fast;
+            rp->valid = valid; rp->used = used; rp->nz_lo = nz_lo; rp->nz_hi = nz_hi;
+        }
     }
-    double a[TMAX * 3];
-#pragma unroll
-    for (int k = 0; k < TMAX * 3; ++k) a[k] = 0.0;
     __syncthreads();
 
     // ---- double-buffered walk over the tiles
@@ -932,46 +1040,48 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_tile_kernel(ResidP
         }
         asm volatile("cp.async.commit_group;\n" ::: "memory");
     };
-    int tI = blockIdx.y;
+    int tI = blockIdx.x;
     if (tI < p.n_tiles) issue(tI, buf0);
-    for (int k = 0; tI < p.n_tiles; tI += gridDim.y, ++k) {
+    for (int k = 0; tI < p.n_tiles; tI += gridDim.x, ++k) {
         double* cur = buf0 + (size_t)(k & 1) * buf_doubles;
-        const int nxt = tI + gridDim.y;
+        const int nxt = tI + gridDim.x;
         if (nxt < p.n_tiles) {
             issue(nxt, buf0 + (size_t)((k + 1) & 1) * buf_doubles);
             asm volatile("cp.async.wait_group 1;\n" ::: "memory");
         } else {
             asm volatile("cp.async.wait_group 0;\n" ::: "memory");
         }
+        if (tid == 0) s_next = nwarps;
         __syncthreads();
-        if (active && valid) {
-            const long long start = (long long)tI * RES_TILE;
-            const int npts = (int)((p.N - start) < RES_TILE ? (p.N - start) : RES_TILE);
-#define RT(TT) residual_tile<TT>(cur, ws, p.factors, npts, lane, nz_lo, nz_hi, used, valid, a)
-            switch (T) {
-                case 1: RT(1); break;
-                case 2: RT(2); break;
-                case 3: RT(3); break;
-                case 4: RT(4); break;
-                case 5: RT(5); break;
-                case 6: RT(6); break;
-                case 7: RT(7); break;
-                default: RT(8); break;
-            }
+        const long long start = (long long)tI * RES_TILE;
+        const int npts = (int)((p.N - start) < RES_TILE ? (p.N - start) : RES_TILE);
+        const unsigned cur_s = smem_addr(cur);
+        int le = warp;
+        while (le < p.n_eq) {
+            const ResidProg* rp = progs + le;
+            if (rp->valid) {
+                const unsigned prog_s = smem_addr(rp);
+                double* row = table + (size_t)le * TMAX * 3;
+#define RT(TT) residual_task<TT>(cur_s, cur, prog_s, rp, p.factors, npts, lane, row)
+                switch (rp->T) {
+                    case 1: RT(1); break;
+                    case 2: RT(2); break;
+                    case 3: RT(3); break;
+                    case 4: RT(4); break;
+                    case 5: RT(5); break;
+                    case 6: RT(6); break;
+                    case 7: RT(7); break;
+                    default: RT(8); break;
+                }
 #undef RT
+            }
+            if (lane == 0) le = atomicAdd(&s_next, 1);
+            le = __shfl_sync(0xffffffffu, le, 0);
         }
         __syncthreads();            // everyone is done with `cur` before it is refilled
     }
-    if (active) {
-        double* out = p.partial + ((size_t)blockIdx.y * p.n_eq + le) * TMAX * 3;
-#pragma unroll
-        for (int k = 0; k < TMAX * 3; ++k) {
-            double v = a[k];
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
-            if (lane == 0) out[k] = v;
-        }
-    }
+    double* out = p.partial + (size_t)blockIdx.x * p.n_eq * TMAX * 3;
+    for (int q = tid; q < p.n_eq * TMAX * 3; q += blockDim.x) out[q] = table[q];
 }
 
 // fixed-order reduction of the per-CTA partial sums -> sums[eval][3]
@@ -1079,6 +1189,7 @@ struct epde_ctx {
     size_t cell_budget_bytes = (size_t)12 << 30;   // scratch cap for the cell Grams of one launch group
     int sm_count = 148;
     int max_smem = 227 * 1024;
+    int resid_warps = RES_WARPS;
     int gram_warps = GRAM_WARPS;   // EPDE_GRAM_WARPS=16 selects the 16-warp / 128-register variant
     // optional per-kernel-class device timing (epde_ctx_set_timing)
     bool timing = false;
@@ -1327,31 +1438,41 @@ static int launch_gram_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, d
 static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double* sums) {
     const int U = (int)g.token_ids.size();
     const long long n_tiles = (c->N + RES_TILE - 1) / RES_TILE;
-    const int ne = (int)g.eqs.size();
-    const int nwarps = std::max(1, std::min(RES_WARPS, ne));
-    const int gx = (ne + nwarps - 1) / nwarps;
-    ResidParams p;
-    memset(&p, 0, sizeof p);
-    p.N = c->N; p.eqs = b->d_eqs; p.factors = b->d_factors;
-    p.eq_list = b->d_lists + g.list_off; p.n_eq = ne; p.U = U; p.n_tiles = (int)n_tiles;
-    for (int u = 0; u < U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
-    p.slot_eval = b->d_slot_eval; p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.intercept_l1 = b->d_b1;
-    const size_t smem = sizeof(double) * 2 * (size_t)U * RES_TILE + (size_t)nwarps * sizeof(ResidWarp);
-    if (smem > (size_t)c->max_smem) return fail("pass B tiles need %zu bytes of shared memory", smem);
-    // CTAs per SM: shared memory and the 64K-register file (<= 128 registers per thread)
-    const int per_sm = std::max(1, std::min((int)((size_t)(c->max_smem + 1024) / (smem + 1024)), 16 / nwarps));
-    long long gy = std::max<long long>(1, (long long)c->sm_count * per_sm / gx);
-    gy = std::min<long long>(gy, n_tiles);
-    gy = std::min<long long>(gy, 65535);
-    if (c->d_partial.ensure(sizeof(double) * (size_t)gy * ne * TMAX * 3)) return 1;
-    p.partial = (double*)c->d_partial.ptr;
-    { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_tile_kernel<<<dim3(gx, (unsigned)gy), nwarps * 32, smem, c->stream>>>(p); }
-    CK(cudaGetLastError());
-    ResidFinalParams fp;
-    fp.eq_list = p.eq_list; fp.slot_eval = b->d_slot_eval; fp.partial = p.partial; fp.sums = sums;
-    fp.n_eq = ne; fp.n_cta = (int)gy;
-    { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_final_kernel<<<ne, 32, 0, c->stream>>>(fp); }
-    CK(cudaGetLastError());
+    const int ne_all = (int)g.eqs.size();
+    // equations per launch: their programs and sum table live in shared memory next to the two tile buffers
+    const size_t tile_bytes = sizeof(double) * 2 * (size_t)U * RES_TILE;
+    const size_t per_eq = sizeof(ResidProg) + sizeof(double) * TMAX * 3;
+    if (tile_bytes + per_eq > (size_t)c->max_smem) return fail("pass B tiles need %zu bytes of shared memory", tile_bytes + per_eq);
+    const int cap = (int)(((size_t)c->max_smem - tile_bytes) / per_eq);
+    const int n_launch = (ne_all + cap - 1) / cap;
+    const int per_launch = (ne_all + n_launch - 1) / n_launch;
+    for (int e0 = 0; e0 < ne_all; e0 += per_launch) {
+        const int ne = std::min(per_launch, ne_all - e0);
+        const int nwarps = std::max(1, std::min(c->resid_warps, ne));
+        ResidParams p;
+        memset(&p, 0, sizeof p);
+        p.N = c->N; p.eqs = b->d_eqs; p.factors = b->d_factors;
+        p.eq_list = b->d_lists + g.list_off + e0; p.n_eq = ne; p.U = U; p.n_tiles = (int)n_tiles;
+        for (int u = 0; u < U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
+        p.slot_eval = b->d_slot_eval; p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.intercept_l1 = b->d_b1;
+        const size_t smem = tile_bytes + (size_t)ne * per_eq;
+        // CTAs per SM: shared memory and the 64K-register file (<= 128 registers per thread)
+        const int per_sm = std::max(1, std::min((int)((size_t)(c->max_smem + 1024) / (smem + 1024)), c->resid_warps / nwarps));
+        const int grid = (int)std::min<long long>(n_tiles, (long long)c->sm_count * per_sm);
+        if (c->d_partial.ensure(sizeof(double) * (size_t)grid * ne * TMAX * 3)) return 1;
+        p.partial = (double*)c->d_partial.ptr;
+        {
+            KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
+            if (c->resid_warps <= 8) residual_tile_kernel<8><<<grid, nwarps * 32, smem, c->stream>>>(p);
+            else residual_tile_kernel<16><<<grid, nwarps * 32, smem, c->stream>>>(p);
+        }
+        CK(cudaGetLastError());
+        ResidFinalParams fp;
+        fp.eq_list = p.eq_list; fp.slot_eval = b->d_slot_eval; fp.partial = p.partial; fp.sums = sums;
+        fp.n_eq = ne; fp.n_cta = grid;
+        { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_final_kernel<<<ne, 32, 0, c->stream>>>(fp); }
+        CK(cudaGetLastError());
+    }
     return 0;
 }
 // ------------------------------------------------------------------------------------------
@@ -1380,12 +1501,13 @@ int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx**
     c->sm_count = prop.multiProcessorCount;
     c->max_smem = (int)prop.sharedMemPerBlockOptin;
     if (const char* ev = getenv("EPDE_GRAM_WARPS")) c->gram_warps = (atoi(ev) > 8) ? 16 : 8;
+    if (const char* ev = getenv("EPDE_RESID_WARPS")) c->resid_warps = (atoi(ev) > 8) ? 16 : 8;
     {
         // dynamic shared memory limit = opt-in maximum minus the kernels' static shared memory
-        const void* fns[3] = {(const void*)gram_tile_kernel<8>, (const void*)gram_tile_kernel<16>,
-                              (const void*)residual_tile_kernel};
+        const void* fns[4] = {(const void*)gram_tile_kernel<8>, (const void*)gram_tile_kernel<16>,
+                              (const void*)residual_tile_kernel<8>, (const void*)residual_tile_kernel<16>};
         int dyn_max = c->max_smem;
-        for (int k = 0; k < 3; ++k) {
+        for (int k = 0; k < 4; ++k) {
             cudaFuncAttributes fa;
             cudaError_t fe = cudaFuncGetAttributes(&fa, fns[k]);
             if (fe == cudaSuccess) {
