@@ -835,138 +835,163 @@ struct ResidParams {
     double* partial;         // [gridDim.x][n_eq][TMAX][3]
 };
 
-struct ResidProg {           // per-equation program in shared memory (16-byte aligned)
-    int4 op[TMAX];           // fast terms (byte offsets of the slots inside a tile buffer)
-    double sw[TMAX * TMAX];  // [d][j] coefficient of term j for the eval with target d
+// Per-equation residual program in shared memory (16-byte aligned), COMPACTED: only the NU terms
+// some eval needs ("used": targets and surviving features) and only the NV evals that exist.
+// The residual of eval dd at a point is  r = sum_u m[dd][u] * c[u] - b1[dd]  with m = +1 at the target
+// column and -coefficient at the feature columns, so the inner loop has no data-dependent tests.
+struct ResidProg {
+    int4 op[TMAX];           // fast terms of the used columns (byte offsets of the slots inside a tile buffer)
+    double m[TMAX * TMAX];   // [dd][u]
     double sb[TMAX], sdb[TMAX];
-    int foff[TMAX + 1];
-    int T, fast;
-    unsigned valid, used, nz_lo, nz_hi;
-    int pad;
+    int term[TMAX];          // used column u -> term index (generic path)
+    int foff[TMAX + 1];      // factor ranges by TERM index (generic path)
+    int dmap[TMAX];          // compact eval dd -> target term d (row of the sum table)
+    int tcol[TMAX];          // compact eval dd -> used column of its target
+    int NU, NV, fast, pad;
 };
 
-// residual contributions of two points (c[0], c[1]) to every valid eval of the equation
-template <int T>
-__device__ __forceinline__ void residual_accumulate(const double (&c)[2][T], bool ok1, unsigned valid, unsigned nz_lo,
-                                                    unsigned nz_hi, unsigned sw_a, unsigned sb_a, unsigned sdb_a,
-                                                    double (&a)[T * 3]) {
+template <int NU>
+__device__ __forceinline__ void residual_point_block(const double (&c)[NU], int NV, unsigned m_a, unsigned sb_a,
+                                                     unsigned sdb_a, double (&a1)[NU], double (&a3)[NU], double (&sabs)[NU]) {
 #pragma unroll
-    for (int d = 0; d < T; ++d) {
-        if (valid >> d & 1u) {
-            // np.dot(features, w) + b, then target - that  (fitness.py:137-140)
-            const unsigned rowm = ((d < 4 ? nz_lo : nz_hi) >> ((d & 3) * 8)) & 0xffu;
-            double p0 = 0.0, p1 = 0.0;
-            if (rowm) {
+    for (int u = 0; u < NU; ++u) sabs[u] += fabs(c[u]);
 #pragma unroll
-                for (int j = 0; j < T; ++j)
-                    if (rowm >> j & 1u) {
-                        const double w = lds_f64(sw_a + (d * TMAX + j) * 8);
-                        p0 = fma(w, c[0][j], p0);
-                        p1 = fma(w, c[1][j], p1);
-                    }
-            }
-            const double b1 = lds_f64(sb_a + d * 8), db = lds_f64(sdb_a + d * 8);
-            const double r0 = c[0][d] - (p0 + b1);
-            const double q0 = r0 + db;            // L2Fitness keeps the LASSO intercept (fitness.py:80)
-            double r1 = c[1][d] - (p1 + b1);
-            double q1 = r1 + db;
-            double t1 = c[1][d];
-            if (!ok1) { r1 = 0.0; q1 = 0.0; t1 = 0.0; }
-            a[d * 3 + 0] += fabs(r0) + fabs(r1);
-            a[d * 3 + 1] += fabs(c[0][d]) + fabs(t1);
-            a[d * 3 + 2] = fma(q0, q0, fma(q1, q1, a[d * 3 + 2]));
+    for (int dd = 0; dd < NU; ++dd) {
+        if (dd < NV) {
+            double r = -lds_f64(sb_a + dd * 8);
+#pragma unroll
+            for (int u = 0; u < NU; ++u) r = fma(lds_f64(m_a + (dd * TMAX + u) * 8), c[u], r);
+            const double q = r + lds_f64(sdb_a + dd * 8);     // L2Fitness keeps the LASSO intercept (fitness.py:80)
+            a1[dd] += fabs(r);
+            a3[dd] = fma(q, q, a3[dd]);
         }
     }
 }
 
-template <int T>
-__device__ __forceinline__ void residual_reduce(const double (&a)[T * 3], unsigned valid, int lane, double* table_row) {
+// R points per decode: same arithmetic, weights fetched once for the R points
+template <int NU, int R>
+__device__ __forceinline__ void residual_points(const double (&c)[R][NU], int NV, unsigned m_a, unsigned sb_a,
+                                                unsigned sdb_a, double (&a1)[NU], double (&a3)[NU], double (&sabs)[NU]) {
 #pragma unroll
-    for (int d = 0; d < T; ++d) {
-        if (valid >> d & 1u) {
+    for (int u = 0; u < NU; ++u) {
+        double t = 0.0;
 #pragma unroll
-            for (int q = 0; q < 3; ++q) {
-                double v = a[d * 3 + q];
+        for (int r = 0; r < R; ++r) t += fabs(c[r][u]);
+        sabs[u] += t;
+    }
 #pragma unroll
-                for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
-                if (lane == 0) table_row[d * 3 + q] += v;
+    for (int dd = 0; dd < NU; ++dd) {
+        if (dd < NV) {
+            const double nb = -lds_f64(sb_a + dd * 8);
+            double rr[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) rr[r] = nb;
+#pragma unroll
+            for (int u = 0; u < NU; ++u) {
+                const double w = lds_f64(m_a + (dd * TMAX + u) * 8);
+#pragma unroll
+                for (int r = 0; r < R; ++r) rr[r] = fma(w, c[r][u], rr[r]);
+            }
+            const double db = lds_f64(sdb_a + dd * 8);        // L2Fitness keeps the LASSO intercept (fitness.py:80)
+            double s1 = 0.0, s3 = a3[dd];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                s1 += fabs(rr[r]);
+                const double q = rr[r] + db;
+                s3 = fma(q, q, s3);
+            }
+            a1[dd] += s1;
+            a3[dd] = s3;
+        }
+    }
+}
+
+template <int NU>
+__device__ __forceinline__ void residual_reduce(const double (&a1)[NU], const double (&a3)[NU], const double (&sabs)[NU],
+                                                const ResidProg* rp, int NV, int lane, double* table_row) {
+    double t_abs[NU];
+#pragma unroll
+    for (int u = 0; u < NU; ++u) {
+        double v = sabs[u];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+        t_abs[u] = v;
+    }
+#pragma unroll
+    for (int dd = 0; dd < NU; ++dd) {
+        if (dd < NV) {
+            double v1 = a1[dd], v3 = a3[dd];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                v1 += __shfl_xor_sync(0xffffffffu, v1, off);
+                v3 += __shfl_xor_sync(0xffffffffu, v3, off);
+            }
+            if (lane == 0) {
+                const int d = rp->dmap[dd], tc = rp->tcol[dd];
+                double ta = 0.0;
+#pragma unroll
+                for (int u = 0; u < NU; ++u) if (u == tc) ta = t_abs[u];
+                table_row[d * 3 + 0] += v1;
+                table_row[d * 3 + 1] += ta;
+                table_row[d * 3 + 2] += v3;
             }
         }
     }
 }
 
 // one (tile, equation) task, fast terms; returns through the shared table row
-template <int T>
-__device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, unsigned valid, unsigned used,
-                                                unsigned nz_lo, unsigned nz_hi, int npts, int lane, double* table_row) {
-    const unsigned sw_a = prog + (unsigned)offsetof(ResidProg, sw);
+template <int NU>
+__device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, const ResidProg* rp, int NV, int npts,
+                                                int lane, double* table_row) {
+    constexpr int R = (NU <= 6) ? 4 : 2;
+    const unsigned m_a = prog + (unsigned)offsetof(ResidProg, m);
     const unsigned sb_a = prog + (unsigned)offsetof(ResidProg, sb);
     const unsigned sdb_a = prog + (unsigned)offsetof(ResidProg, sdb);
-    double a[T * 3];
+    double a1[NU], a3[NU], sabs[NU];
 #pragma unroll
-    for (int k = 0; k < T * 3; ++k) a[k] = 0.0;
-    for (int i = lane; i < npts; i += 64) {
-        const bool ok1 = (i + 32) < npts;
-        double c[2][T];
-        const unsigned pt = tile + i * 8;
-#pragma unroll
-        for (int t = 0; t < T; ++t) {
-            double v0 = 0.0, v1 = 0.0;
-            if (used >> t & 1u) {
-                const int4 d = lds_v4(prog + t * 16);
-                v0 = lds_f64(pt + d.x);
-                v1 = lds_f64(pt + d.x + 256);
-                if (d.y >= 2) {
-                    if (d.y == 3) { v0 = v0 * v0 * v0; v1 = v1 * v1 * v1; } else { v0 *= v0; v1 *= v1; }
-                }
-                if (d.z >= 0) {
-                    double y0 = lds_f64(pt + d.z), y1 = lds_f64(pt + d.z + 256);
-                    if (d.w >= 2) {
-                        if (d.w == 3) { y0 = y0 * y0 * y0; y1 = y1 * y1 * y1; } else { y0 *= y0; y1 *= y1; }
-                    }
-                    v0 *= y0; v1 *= y1;
-                }
-            }
-            c[0][t] = v0; c[1][t] = v1;
-        }
-        residual_accumulate<T>(c, ok1, valid, nz_lo, nz_hi, sw_a, sb_a, sdb_a, a);
+    for (int k = 0; k < NU; ++k) { a1[k] = 0.0; a3[k] = 0.0; sabs[k] = 0.0; }
+    const int nfull = npts - npts % (32 * R);
+    int i = lane;
+    for (; i < nfull; i += 32 * R) {
+        double c[R][NU];
+        fast_terms_r<NU, R, 256>(prog, tile + i * 8, c);
+        residual_points<NU, R>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
     }
-    residual_reduce<T>(a, valid, lane, table_row);
+    for (; i < npts; i += 32) {
+        double c[1][NU];
+        fast_terms_r<NU, 1, 256>(prog, tile + i * 8, c);
+        residual_points<NU, 1>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
+    }
+    residual_reduce<NU>(a1, a3, sabs, rp, NV, lane, table_row);
 }
 
 // same, generic terms (any kind / power / factor count)
-template <int T>
+template <int NU>
 __device__ __noinline__ void residual_task_generic(const double* tile_g, unsigned prog, const ResidProg* rp,
-                                                   const FactorDesc* fac, int npts, int lane, double* table_row) {
-    const unsigned valid = rp->valid, used = rp->used, nz_lo = rp->nz_lo, nz_hi = rp->nz_hi;
-    const unsigned sw_a = prog + (unsigned)offsetof(ResidProg, sw);
+                                                   const FactorDesc* fac, int NV, int npts, int lane, double* table_row) {
+    const unsigned m_a = prog + (unsigned)offsetof(ResidProg, m);
     const unsigned sb_a = prog + (unsigned)offsetof(ResidProg, sb);
     const unsigned sdb_a = prog + (unsigned)offsetof(ResidProg, sdb);
-    double a[T * 3];
+    double a1[NU], a3[NU], sabs[NU];
 #pragma unroll
-    for (int k = 0; k < T * 3; ++k) a[k] = 0.0;
-    for (int i = lane; i < npts; i += 64) {
-        const bool ok1 = (i + 32) < npts;
-        double c[2][T];
+    for (int k = 0; k < NU; ++k) { a1[k] = 0.0; a3[k] = 0.0; sabs[k] = 0.0; }
+    for (int i = lane; i < npts; i += 32) {
+        double c[1][NU];
 #pragma unroll
-        for (int t = 0; t < T; ++t) {
-            double v0 = 0.0, v1 = 0.0;
-            if (used >> t & 1u) {
-                v0 = eval_term_generic(fac, rp->foff[t], rp->foff[t + 1], tile_g + i, RES_TILE);
-                if (ok1) v1 = eval_term_generic(fac, rp->foff[t], rp->foff[t + 1], tile_g + i + 32, RES_TILE);
-            }
-            c[0][t] = v0; c[1][t] = v1;
+        for (int u = 0; u < NU; ++u) {
+            const int t = rp->term[u];
+            c[0][u] = eval_term_generic(fac, rp->foff[t], rp->foff[t + 1], tile_g + i, RES_TILE);
         }
-        residual_accumulate<T>(c, ok1, valid, nz_lo, nz_hi, sw_a, sb_a, sdb_a, a);
+        residual_points<NU, 1>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
     }
-    residual_reduce<T>(a, valid, lane, table_row);
+    residual_reduce<NU>(a1, a3, sabs, rp, NV, lane, table_row);
 }
 
-template <int T>
+template <int NU>
 __device__ __forceinline__ void residual_task(unsigned tile, const double* tile_g, unsigned prog, const ResidProg* rp,
                                               const FactorDesc* fac, int npts, int lane, double* table_row) {
-    if (rp->fast) residual_task_fast<T>(tile, prog, rp->valid, rp->used, rp->nz_lo, rp->nz_hi, npts, lane, table_row);
-    else residual_task_generic<T>(tile_g, prog, rp, fac, npts, lane, table_row);
+    if (rp->fast) residual_task_fast<NU>(tile, prog, rp, rp->NV, npts, lane, table_row);
+    else residual_task_generic<NU>(tile_g, prog, rp, fac, rp->NV, npts, lane, table_row);
 }
 
 template <int NW>
@@ -989,39 +1014,57 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
         const EqDesc* eq = p.eqs + e;
         ResidProg* rp = progs + le;
         const int T = eq->T;
-        if (lane < TMAX) {
-            int4 d = eq->fastop[lane];
-            d.x *= RES_TILE * 8;
-            if (d.z >= 0) d.z *= RES_TILE * 8;
-            rp->op[lane] = d;
-        }
-        if (lane <= TMAX) rp->foff[lane] = eq->fac_off[lane];
         // lane d < T holds the eval id of target d
         const int my_ev = (lane < T) ? p.slot_eval[e * TMAX + lane] : -1;
         const unsigned valid = __ballot_sync(0xffffffffu, my_ev >= 0);
-        if (lane < TMAX) {
-            const double b1 = my_ev >= 0 ? p.intercept_l1[my_ev] : 0.0;
-            rp->sb[lane] = b1;
-            rp->sdb[lane] = my_ev >= 0 ? b1 - p.intercept[my_ev] : 0.0;
-        }
-        unsigned nz_lo = 0u, nz_hi = 0u;
+        double wv[2];
+        unsigned nz[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int idx = lane + 32 * h;
             const int d = idx >> 3, j = idx & 7;
             const int evd = __shfl_sync(0xffffffffu, my_ev, d);
-            const double w = (evd >= 0 && j < T) ? p.wterm[(long long)evd * TMAX + j] : 0.0;
-            rp->sw[idx] = w;
-            const unsigned m = __ballot_sync(0xffffffffu, w != 0.0);
-            if (h == 0) nz_lo = m; else nz_hi = m;
+            wv[h] = (evd >= 0 && j < T) ? p.wterm[(long long)evd * TMAX + j] : 0.0;
+            nz[h] = __ballot_sync(0xffffffffu, wv[h] != 0.0);
         }
         unsigned used = valid;
 #pragma unroll
-        for (int d = 0; d < 4; ++d) used |= ((nz_lo >> (d * 8)) & 0xffu) | ((nz_hi >> (d * 8)) & 0xffu);
-        if (lane == 0) {
-            rp->T = T; rp->fast = eq->fast;
-            rp->valid = valid; rp->used = used; rp->nz_lo = nz_lo; rp->nz_hi = nz_hi;
+        for (int d = 0; d < 4; ++d) used |= ((nz[0] >> (d * 8)) & 0xffu) | ((nz[1] >> (d * 8)) & 0xffu);
+        const int NU = __popc(used), NV = __popc(valid);
+        for (int q = lane; q < TMAX * TMAX; q += 32) rp->m[q] = 0.0;
+        if (lane < TMAX) { rp->op[lane] = make_int4(0, 1, -1, 1); rp->sb[lane] = 0.0; rp->sdb[lane] = 0.0; rp->term[lane] = 0; rp->dmap[lane] = 0; rp->tcol[lane] = 0; }
+        __syncwarp();
+        if (lane < T && (used >> lane & 1u)) {
+            const int u = __popc(used & ((1u << lane) - 1u));
+            int4 d = eq->fastop[lane];
+            d.x *= RES_TILE * 8;
+            if (d.z >= 0) d.z *= RES_TILE * 8;
+            rp->op[u] = d;
+            rp->term[u] = lane;
         }
+        if (lane <= TMAX) rp->foff[lane] = eq->fac_off[lane];
+        if (my_ev >= 0) {
+            const int dd = __popc(valid & ((1u << lane) - 1u));
+            const int tc = __popc(used & ((1u << lane) - 1u));
+            const double b1 = p.intercept_l1[my_ev];
+            rp->sb[dd] = b1;
+            rp->sdb[dd] = b1 - p.intercept[my_ev];
+            rp->dmap[dd] = lane;
+            rp->tcol[dd] = tc;
+            rp->m[dd * TMAX + tc] = 1.0;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int idx = lane + 32 * h;
+            const int d = idx >> 3, j = idx & 7;
+            if (wv[h] != 0.0) {
+                const int dd = __popc(valid & ((1u << d) - 1u));
+                const int u = __popc(used & ((1u << j) - 1u));
+                rp->m[dd * TMAX + u] = -wv[h];
+            }
+        }
+        if (lane == 0) { rp->NU = NU; rp->NV = NV; rp->fast = eq->fast; }
     }
     __syncthreads();
 
@@ -1059,11 +1102,11 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
         int le = warp;
         while (le < p.n_eq) {
             const ResidProg* rp = progs + le;
-            if (rp->valid) {
+            if (rp->NV > 0) {
                 const unsigned prog_s = smem_addr(rp);
                 double* row = table + (size_t)le * TMAX * 3;
-#define RT(TT) residual_task<TT>(cur_s, cur, prog_s, rp, p.factors, npts, lane, row)
-                switch (rp->T) {
+#define RT(UU) residual_task<UU>(cur_s, cur, prog_s, rp, p.factors, npts, lane, row)
+                switch (rp->NU) {
                     case 1: RT(1); break;
                     case 2: RT(2); break;
                     case 3: RT(3); break;
