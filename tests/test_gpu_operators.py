@@ -1,0 +1,285 @@
+"""GPU tests of the reference-API mirrors (epde_b200.operators) against the reference-generated
+golden fixtures: the operators are driven exactly as the reference's directors drive its own
+(wire -> apply -> read the mutated Equation), through stand-in Equation objects (tests/standins.py)."""
+import numpy as np
+import pytest
+
+import epde_b200
+from epde_b200 import operators as ops
+from oracle import epde_oracle as orc
+
+from conftest import EQ_FIXTURES, fixture_equations, load_fixture
+from helpers import assert_rel
+from standins import Equation, Factor, Term, equation_from_encoding
+
+pytestmark = pytest.mark.gpu
+COND_MAX = 1e9
+
+
+def wire(cls, penalty_coeff=0.2):
+    """as optimizers/moeadd/strategy.py:46-63 wires the reference's operators."""
+    op = cls(['penalty_coeff'])
+    op.params = {'penalty_coeff': penalty_coeff}
+    op.set_suboperators({'sparsity': ops.LASSOSparsity(), 'coeff_calc': ops.LinRegBasedCoeffsEquation()})
+    return op
+
+
+@pytest.fixture
+def bound_fixture(request):
+    name = request.param
+    fx = load_fixture(name)
+    shape = tuple(int(s) for s in fx['shape'])
+    eng = epde_b200.Engine(shape, device=0)
+    b = ops.bind(eng)
+    cache = ops.Cache()
+    labels = [str(l) for l in fx['labels']]
+    for lab, vec in zip(labels, fx['tokens']):
+        assert cache.add((lab, (1.0,)), vec) is True
+    yield name, fx, shape, labels, b
+    ops.unbind()
+    eng.close()
+
+
+@pytest.mark.parametrize('bound_fixture', EQ_FIXTURES, indirect=True)
+def test_out_of_place_fitness_matches_reference(bound_fixture):
+    """L2LRFitness.apply(force_out_of_place=True) per (equation, target): weights_internal,
+    weights_final, _cached_sw_weights on the Equation and the returned value / None."""
+    name, fx, shape, labels, _ = bound_fixture
+    eqs = fixture_equations(fx)
+    deriv = [l for l in labels if l != 'u']
+    l2lr = wire(ops.L2LRFitness)
+    checked = 0
+    for e, eq in enumerate(eqs):
+        sel = np.nonzero(fx['ev_eq'] == e)[0]
+        if not len(sel):
+            continue
+        ores = orc.evaluate_equation(fx['tokens'], shape, eq, targets=[int(fx['ev_tgt'][v]) for v in sel])
+        for v, o in zip(sel, ores):
+            if o.cond > COND_MAX:
+                continue
+            obj = equation_from_encoding(eq, labels, deriv)
+            obj.target_idx = int(fx['ev_tgt'][v])
+            fit = l2lr.apply(obj, {}, force_out_of_place=True)
+            T = len(eq)
+            ref_coef = fx['ev_coef'][v, :T - 1]
+            assert obj.weights_internal_evald and obj.weights_final_evald and obj._eval_cache == {}
+            assert np.array_equal(obj.weights_internal != 0, ref_coef != 0), f'{name} eval {v}: term set'
+            scale = np.abs(ref_coef).max() if np.abs(ref_coef).max() > 0 else 1.0
+            assert_rel(obj.weights_internal, ref_coef, f'{name} eval {v} weights_internal', atol=1e-9 * scale)
+            nact = int(fx['ev_nact'][v])
+            assert obj._cached_sw_weights.shape == (fx['ev_sw'].shape[1], nact + 1)
+            ref_final = [w for w in np.append(ref_coef, fx['ev_b'][v]) if w != 0]
+            assert len(obj.weights_final) == len(ref_final)
+            if np.isnan(fx['ev_fit'][v]):
+                assert fit is None
+            else:
+                assert_rel(fit, fx['ev_fit'][v], f'{name} eval {v} fitness')
+            checked += 1
+    assert checked >= 5
+
+
+@pytest.mark.parametrize('bound_fixture', EQ_FIXTURES, indirect=True)
+def test_right_part_selector_matches_reference(bound_fixture):
+    """EqRightPartSelector.apply + in-place L2LRFitness.apply (what SoEq.obj_fun triggers):
+    chosen target, kept terms, weights_final, fitness_value, coefficients_stability."""
+    name, fx, shape, labels, _ = bound_fixture
+    eqs = fixture_equations(fx)
+    deriv = [l for l in labels if l != 'u']
+    l2lr = wire(ops.L2LRFitness)
+    rps = ops.EqRightPartSelector()
+    rps.set_suboperators({'fitness_calculation': l2lr})
+    checked = 0
+    for e, eq in enumerate(eqs):
+        if not fx['rps_ok'][e]:
+            continue
+        sel = np.nonzero(fx['ev_eq'] == e)[0]
+        ores = orc.evaluate_equation(fx['tokens'], shape, eq, targets=[int(fx['ev_tgt'][v]) for v in sel])
+        if any(o.cond > COND_MAX for o in ores):
+            continue
+        obj = equation_from_encoding(eq, labels, deriv)
+        terms0 = list(obj.structure)
+        try:
+            rps.apply(obj, {})
+        except RuntimeError:       # the equation degenerated: the reference re-randomises (RNG-dependent)
+            continue
+        assert obj.right_part_selected and obj.simplified and obj.is_correct_right_part
+        keep = np.zeros(8, dtype=np.int8)
+        idx = [terms0.index(t) for t in obj.structure]
+        keep[idx] = 1
+        if not np.array_equal(keep, fx['rps_keep'][e]):
+            continue                # the reference took extra simplification rounds
+        assert idx[obj.target_idx] == int(fx['rps_target'][e]), f'{name} eq {e}: target'
+        l2lr.apply(obj, {})
+        assert obj.fitness_calculated and obj.stability_calculated and obj.aic_calculated
+        ref_wf = fx['rps_wfinal'][e]
+        ref_wf = ref_wf[~np.isnan(ref_wf)]
+        assert len(obj.weights_final) == len(ref_wf)
+        assert_rel(np.asarray(obj.weights_final), ref_wf, f'{name} eq {e} weights_final',
+                   atol=1e-9 * np.abs(ref_wf).max())
+        assert_rel(obj.fitness_value, fx['rps_fit'][e], f'{name} eq {e} fitness_value')
+        assert_rel(obj.coefficients_stability, fx['rps_stab'][e], f'{name} eq {e} stability', rtol=1e-5, atol=1e-14)
+        checked += 1
+    assert checked >= 1
+
+
+@pytest.mark.parametrize('bound_fixture', ['wave_b5'], indirect=True)
+def test_population_batch_equals_one_by_one(bound_fixture):
+    """apply_population / evaluate_population (one engine batch per round) == the per-equation calls."""
+    name, fx, shape, labels, _ = bound_fixture
+    eqs = fixture_equations(fx)
+    deriv = [l for l in labels if l != 'u']
+    l2lr = wire(ops.L2LRFitness)
+    rps = ops.EqRightPartSelector()
+    rps.set_suboperators({'fitness_calculation': l2lr})
+
+    def run(batched):
+        objs, good = [equation_from_encoding(eq, labels, deriv) for eq in eqs], []
+        if batched:
+            # equations that degenerate would stop the whole batch: find them one by one first
+            pass
+        for o in objs:
+            try:
+                rps.apply(o, {})
+                good.append(o)
+            except RuntimeError:
+                continue
+        return good
+
+    single = run(False)
+    for o in single:
+        l2lr.apply(o, {})
+    ok_ids = [i for i, eq in enumerate(eqs)
+              if any(len(o.structure) and o is s for s in single for o in [s])]
+    # the same equations again, as one population
+    objs = [equation_from_encoding(eq, labels, deriv) for eq in eqs]
+    keep = []
+    for o, eq in zip(objs, eqs):
+        probe = equation_from_encoding(eq, labels, deriv)
+        try:
+            rps.apply(probe, {})
+            keep.append(o)
+        except RuntimeError:
+            pass
+    assert len(keep) == len(single) and len(keep) >= 4 and ok_ids is not None
+    rps.apply_population(keep, {})
+    out = ops.evaluate_population(keep)
+    for a, b, (fit, stab) in zip(single, keep, out):
+        assert a.target_idx == b.target_idx and len(a.structure) == len(b.structure)
+        assert np.array_equal(np.asarray(a.weights_final), np.asarray(b.weights_final))
+        assert a.fitness_value == b.fitness_value == fit
+        assert a.coefficients_stability == b.coefficients_stability == stab
+
+
+def test_l2_fitness_and_penalty():
+    """L2Fitness.apply: out-of-place value == ||Fw + b - t||_2 of the oracle; penalty division when
+    sum(weights_final) == 0 (fitness.py:85-91); bad penalty_coeff raises ValueError."""
+    fx = load_fixture('wave_b5')
+    shape = tuple(int(s) for s in fx['shape'])
+    labels = [str(l) for l in fx['labels']]
+    eqs = fixture_equations(fx)
+    with epde_b200.Engine(shape, device=0) as eng:
+        ops.bind(eng)
+        try:
+            cache = ops.Cache()
+            for lab, vec in zip(labels, fx['tokens']):
+                cache.add((lab, (1.0,)), vec)
+            l2 = wire(ops.L2Fitness)
+            checked = 0
+            for v in range(len(fx['ev_eq'])):
+                if np.isnan(fx['ev_fit_l2'][v]):
+                    continue
+                eq = eqs[int(fx['ev_eq'][v])]
+                o = orc.evaluate_equation(fx['tokens'], shape, eq, targets=[int(fx['ev_tgt'][v])])[0]
+                if o.cond > COND_MAX:
+                    continue
+                obj = equation_from_encoding(eq, labels, [l for l in labels if l != 'u'])
+                obj.target_idx = int(fx['ev_tgt'][v])
+                val = l2.apply(obj, {}, force_out_of_place=True)
+                ref = fx['ev_fit_l2'][v]
+                if np.sum(obj.weights_final) == 0:
+                    ref = ref / 0.2
+                assert_rel(val, ref, f'eval {v} l2 fitness', atol=1e-9 * np.linalg.norm(orc.eval_term(fx['tokens'], eq[obj.target_idx])))
+                # in place from the stored weights: same number, written to the Equation
+                obj.weights_final = np.append(obj.weights_internal, o.intercept)
+                l2.apply(obj, {})
+                assert obj.fitness_calculated
+                assert_rel(obj.fitness_value, val, f'eval {v} l2 in place', rtol=1e-9)
+                checked += 1
+                if checked >= 12:
+                    break
+            assert checked >= 3
+            bad = ops.L2Fitness(['penalty_coeff'])
+            bad.params = {'penalty_coeff': 1.5}
+            bad.set_suboperators({'sparsity': ops.LASSOSparsity(), 'coeff_calc': ops.LinRegBasedCoeffsEquation()})
+            with pytest.raises(ValueError):
+                bad.apply(obj, {}, force_out_of_place=True)
+        finally:
+            ops.unbind()
+
+
+def test_operator_contract_and_errors():
+    """keys, tags, params key check, coeff-calc assertion, unbound engine: the reference's error
+    behaviour (template.py:49-55, coeff_calculation.py:47)."""
+    assert ops.LASSOSparsity.key == 'LASSOBasedSparsity'
+    assert ops.LinRegBasedCoeffsEquation.key == 'LinRegCoeffCalc'
+    assert ops.L2Fitness.key == 'DiscrepancyBasedFitness'
+    assert ops.L2LRFitness.key == 'DiscrepancyBasedFitnessWithCV'
+    assert ops.EqRightPartSelector.key == 'FitnessCheckingRightPartSelector'
+    assert ops.L2LRFitness().operator_tags == {'fitness evaluation', 'gene level', 'contains suboperators', 'inplace'}
+    assert ops.LASSOSparsity().operator_tags == {'sparsity', 'gene level', 'no suboperators', 'inplace'}
+    op = ops.L2LRFitness(['penalty_coeff'])
+    with pytest.raises(KeyError):
+        op.params = {'wrong': 1}
+    with pytest.raises(TypeError):
+        op.set_suboperators({'sparsity': 3})
+    eq = Equation([Term([Factor('u')]), Term([Factor('du/dx0', is_deriv=True)])])
+    with pytest.raises(AssertionError):
+        ops.LinRegBasedCoeffsEquation().apply(eq)
+    ops.unbind()
+    with pytest.raises(RuntimeError):
+        ops.LASSOSparsity().apply(eq, {})
+
+
+def test_cache_mirror_and_trig_family():
+    """Cache.add / get / in / delete_entry and in-kernel trig tokens (evaluators.py:141) through the
+    operator path, against the oracle."""
+    shape = (40, 36)
+    rng = np.random.default_rng(3)
+    t, x = np.meshgrid(np.linspace(0, 1, shape[0]), np.linspace(0, 2, shape[1]), indexing='ij')
+    u = np.sin(3 * x) * np.exp(-t) + 0.01 * rng.standard_normal(shape)
+    ut = -np.sin(3 * x) * np.exp(-t) + 0.01 * rng.standard_normal(shape)
+    with epde_b200.Engine(shape, device=0) as eng:
+        b = ops.bind(eng)
+        try:
+            cache = ops.Cache()
+            assert cache.inner_shape == shape
+            assert cache.add(('u', (1.0,)), u) and cache.add(('du/dx0', (1.0,)), ut)
+            assert cache.upload_grid(1, x)
+            assert (('u', (1.0,)), False) in cache and ('nope', (1.0,)) not in cache
+            assert np.array_equal(cache.get(('u', (1.0,))), u.reshape(-1))
+            assert cache.consumed_memory == 3 * u.size * 8
+            with pytest.raises(KeyError):
+                cache.get(('nope', (1.0,)))
+            with pytest.raises(ValueError):
+                cache.add(('bad', (1.0,)), np.zeros(5))
+            eq = Equation([Term([Factor('u', 1)]),
+                           Term([Factor('sin', 1, extra={'freq': 3.0, 'dim': 1})]),
+                           Term([Factor('cos', 2, extra={'freq': 1.5, 'dim': 1}), Factor('u', 1)]),
+                           Term([Factor('du/dx0', 1, is_deriv=True)])])
+            enc = ops.encode_equation(eq)
+            gid = b.token_ids[ops.Binding.grid_label(1)]
+            assert enc[1] == [(gid, 1.0, epde_b200.KIND_SIN, 3.0)]
+            assert enc[2][0] == (gid, 2.0, epde_b200.KIND_COS, 1.5)
+            sp = ops.LASSOSparsity()
+            sp.apply(eq, {})
+            toks = [None] * 3
+            toks[b.token_ids['u']] = u.reshape(-1)
+            toks[b.token_ids['du/dx0']] = ut.reshape(-1)
+            toks[gid] = x.reshape(-1)
+            o = orc.evaluate_equation(toks, shape, enc, targets=[3])[0]
+            assert np.array_equal(eq.weights_internal != 0, o.coef != 0)
+            assert_rel(eq.weights_internal, o.coef, 'trig coef', atol=1e-9 * np.abs(o.coef).max())
+            cache.delete_entry(('u', (1.0,)))
+            assert ('u', (1.0,)) not in cache
+        finally:
+            ops.unbind()
