@@ -55,7 +55,7 @@
 #define GRAM_WARPS 8           // warps per pass-A CTA
 #define RED_CHUNK 8            // Gram entries reduced per shared-memory round of the cell flush
 #define MAXU 12                // distinct tokens per launch group (tile = MAXU x 64 x 32 doubles = 192 KB)
-#define RES_WARPS 8            // warps per pass-B CTA (8 x <= 255 registers, or 16 x <= 128: EPDE_RESID_WARPS)
+#define RES_WARPS 8            // warps per pass-B CTA (8 x <= 255 registers)
 #define RES_TILE 1024          // points of a pass-B tile
 
 static thread_local std::string g_err;
@@ -97,7 +97,12 @@ struct EqDesc {
     long long s_off;         // doubles, into the segment-Gram table
     long long c_off;         // doubles, into the cell-Gram scratch of its launch group
     long long w_off;         // doubles, into the window-Gram table
-    int4 fastop[TMAX];       // fast terms: {slot0, ipow0, slot1 or -1, ipow1}
+    int4 fastop[TMAX];       // fast terms IN EVALUATION ORDER (most slot factors first): slots {A, C, B, D} of
+                             // the term's factors with integer powers expanded (u^2 * v -> u, u, v); -1 = absent
+    int n2, n3;              // terms with >= 2 / >= 3 slot factors (fast equations)
+    unsigned char pos[TMAX]; // term index -> evaluation position
+    unsigned char perm[TMAX];// evaluation position -> term index
+    unsigned char accmap[TMAX * (TMAX + 3) / 2];   // Gram accumulator in evaluation order -> index in term order
 };
 
 struct UnitDesc {            // one CTA work unit of pass A: a (sub-)cell of the leading axes x a column chunk
@@ -191,9 +196,10 @@ __device__ __forceinline__ double eval_term_generic(const FactorDesc* fac, int f
 
 // per-warp copy of the equation being processed (shared memory)
 struct WarpProg {
-    int4 op[TMAX];           // fast terms: {offset0, ipow0, offset1 or -1, ipow1} (byte offsets of the slots)
+    int4 op[TMAX];           // fast terms in evaluation order: byte offsets of slots {A, C, B, D}, -1 = absent
     int foff[TMAX + 1];      // generic path: factor ranges
-    int T, fast, pad0, pad1;
+    int T, fast, n2, n3;
+    unsigned char accmap[TMAX * (TMAX + 3) / 2 + 4];
 };
 
 // ------------------------------------------------------------------------------------------
@@ -249,51 +255,66 @@ __device__ __forceinline__ void gram_accumulate(double (&acc)[T * (T + 3) / 2], 
     for (int i = 0; i < T; ++i) { acc[k] += c[i]; ++k; }
 }
 
-// fast terms for R consecutive tile rows of one lane.  ops: shared address of the warp's int4 op table
-// {byte offset of factor 0's slot, ipow0, byte offset of factor 1's slot or -1, ipow1}; pr: shared
-// address of the lane's element in row `row` of slot 0; rows are ROWB bytes apart.
-template <int T, int R, int ROWB>
-__device__ __forceinline__ void fast_terms_r(unsigned ops, unsigned pr, double (&c)[R][T]) {
+// fast terms for R consecutive tile rows of one lane, branch free.  A fast term is a product of 1..4 token
+// values (integer powers expanded: u^2 * v = u * u * v).  Terms come in evaluation order, most factors
+// first.  N2 = number of leading terms that get a second-factor multiply, one of {0, 1, 2, T} (the class
+// >= the equation's count); DEEP: those N2 terms also get a third and fourth multiply.  A term inside a
+// class without that factor multiplies by 1.0 read from a small shared region of ones, so the body is
+// straight-line code the scheduler interleaves with the Gram FMAs.  ops: shared address of the int4 op
+// table (byte offsets of slots {A, C, B, D}, -1 = absent); pr: shared address of the lane's element in
+// row `row` of slot 0; rows are ROWB bytes apart; ones: shared address of >= R * ROWB bytes of 1.0.
+template <int T, int N2, bool DEEP>
+struct TermOffsets { int a[T]; int b[N2 > 0 ? N2 : 1]; int c[(DEEP && N2 > 0) ? N2 : 1]; int d[(DEEP && N2 > 0) ? N2 : 1]; };
+
+template <int T, int N2, bool DEEP>
+__device__ __forceinline__ void load_term_offsets(unsigned ops, TermOffsets<T, N2, DEEP>& o) {
 #pragma unroll
     for (int t = 0; t < T; ++t) {
-        const int4 d = lds_v4(ops + t * 16);
-        double x[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) x[r] = lds_f64(pr + d.x + r * ROWB);
-        if (d.y >= 2) {
-            if (d.y == 3) {
-#pragma unroll
-                for (int r = 0; r < R; ++r) x[r] = x[r] * x[r] * x[r];
-            } else {
-#pragma unroll
-                for (int r = 0; r < R; ++r) x[r] = x[r] * x[r];
-            }
+        const int4 q = lds_v4(ops + t * 16);
+        o.a[t] = q.x;
+        if (t < N2) {
+            o.b[t] = q.z;
+            if (DEEP) { o.c[t] = q.y; o.d[t] = q.w; }
         }
-        if (d.z >= 0) {
-            double y[R];
-#pragma unroll
-            for (int r = 0; r < R; ++r) y[r] = lds_f64(pr + d.z + r * ROWB);
-            if (d.w >= 2) {
-                if (d.w == 3) {
-#pragma unroll
-                    for (int r = 0; r < R; ++r) y[r] = y[r] * y[r] * y[r];
-                } else {
-#pragma unroll
-                    for (int r = 0; r < R; ++r) y[r] = y[r] * y[r];
-                }
-            }
-#pragma unroll
-            for (int r = 0; r < R; ++r) x[r] *= y[r];
-        }
-#pragma unroll
-        for (int r = 0; r < R; ++r) c[r][t] = x[r];
     }
 }
+
+template <int T, int N2, bool DEEP, int R, int ROWB>
+__device__ __forceinline__ void fast_terms_r(const TermOffsets<T, N2, DEEP>& o, unsigned pr, unsigned ones,
+                                             double (&c)[R][T]) {
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) c[r][t] = lds_f64(pr + o.a[t] + r * ROWB);
+    }
+#pragma unroll
+    for (int t = 0; t < N2; ++t) {
+        const unsigned ab = (o.b[t] >= 0) ? pr + o.b[t] : ones;
+#pragma unroll
+        for (int r = 0; r < R; ++r) c[r][t] *= lds_f64(ab + r * ROWB);
+    }
+    if (DEEP) {
+#pragma unroll
+        for (int t = 0; t < N2; ++t) {
+            const unsigned ac = (o.c[t] >= 0) ? pr + o.c[t] : ones;
+            const unsigned ad = (o.d[t] >= 0) ? pr + o.d[t] : ones;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                c[r][t] *= lds_f64(ac + r * ROWB);
+                c[r][t] *= lds_f64(ad + r * ROWB);
+            }
+        }
+    }
+}
+
+// class of a two-factor count: the smallest of {0, 1, 2, T} that is >= n2, as an index 0..3
+__device__ __forceinline__ int n2_class(int n2) { return n2 <= 2 ? n2 : 3; }
 
 // flush: sum the lanes (columns) of every piece, RED_CHUNK Gram entries per round
 template <int T>
 __device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2], int lane, unsigned red, double* out,
-                                            int piece_lo, int npieces, int col_lo, const int* __restrict__ piece_start) {
+                                            int piece_lo, int npieces, int col_lo, const int* __restrict__ piece_start,
+                                            const unsigned char* accmap) {
     constexpr int NACC = T * (T + 3) / 2;
     constexpr int RS = TILE_COLS + 1;
 #pragma unroll
@@ -311,38 +332,40 @@ __device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2]
             const int hi = piece_start[piece_lo + pp + 1] - col_lo;
             double s = 0.0;
             for (int cidx = lo; cidx < hi; ++cidx) s += lds_f64_volatile(red + (k * RS + cidx) * 8);
-            out[(long long)pp * NACC + b0 + k] = s;
+            out[(long long)pp * NACC + accmap[b0 + k]] = s;
         }
     }
     __syncwarp();
 }
 
-// fast path: every term = x^p [* y^q], p, q in {1, 2, 3}; R tile rows per decode
-template <int T, int R>
-__device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, int nrows, int lane, unsigned red,
+// fast path: every term = x^p [* y^q], p, q in {1, 2, 3}; R tile rows per iteration
+template <int T, int N2, bool DEEP, int R>
+__device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, unsigned ones, int nrows, int lane, unsigned red,
                                             double* out, int piece_lo, int npieces, int col_lo,
-                                            const int* __restrict__ piece_start) {
+                                            const int* __restrict__ piece_start, const unsigned char* accmap) {
     constexpr int NACC = T * (T + 3) / 2;
     constexpr int ROWB = TILE_COLS * 8;
     double acc[NACC];
 #pragma unroll
     for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
     const unsigned base = tile + lane * 8;
+    TermOffsets<T, N2, DEEP> off;
+    load_term_offsets<T, N2, DEEP>(ops, off);
     int row = 0;
     if (R > 1) {
         for (; row + R <= nrows; row += R) {
             double c[R][T];
-            fast_terms_r<T, R, ROWB>(ops, base + row * ROWB, c);
+            fast_terms_r<T, N2, DEEP, R, ROWB>(off, base + row * ROWB, ones, c);
 #pragma unroll
             for (int r = 0; r < R; ++r) gram_accumulate<T>(acc, c[r]);
         }
     }
     for (; row < nrows; ++row) {
         double c[1][T];
-        fast_terms_r<T, 1, ROWB>(ops, base + row * ROWB, c);
+        fast_terms_r<T, N2, DEEP, 1, ROWB>(off, base + row * ROWB, ones, c);
         gram_accumulate<T>(acc, c[0]);
     }
-    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start);
+    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start, accmap);
 }
 
 // generic path: any factor kind / power / factor count
@@ -363,21 +386,30 @@ __device__ __noinline__ void gram_warp_generic(const double* tile, int tstride, 
             c[t] = eval_term_generic(fac, wp->foff[t], wp->foff[t + 1], base + row * TILE_COLS, tstride);
         gram_accumulate<T>(acc, c);
     }
-    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start);
+    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start, wp->accmap);
 }
 
-template <int T, int NW>
+template <int T>
 __device__ __forceinline__ void gram_warp(const double* tile, int tstride, const WarpProg* wp, const FactorDesc* fac,
-                                          int nrows, int lane, double* red, double* out, int piece_lo, int npieces,
-                                          int col_lo, const int* __restrict__ piece_start) {
-    // 8-warp CTAs may use 255 registers per thread: four rows per decode (two for the widest equations)
-    constexpr int R = (NW <= 8) ? (T <= 6 ? 4 : 2) : (T <= 4 ? 4 : (T <= 6 ? 2 : 1));
-    if (wp->fast)
-        gram_warp_fast<T, R>(smem_addr(tile), smem_addr(wp->op), nrows, lane, smem_addr(red), out, piece_lo, npieces,
-                             col_lo, piece_start);
-    else
+                                          unsigned ones, int nrows, int lane, double* red, double* out, int piece_lo,
+                                          int npieces, int col_lo, const int* __restrict__ piece_start) {
+    // 8-warp CTAs may use 255 registers per thread: four rows per iteration (two for the widest equations)
+    constexpr int R = T <= 6 ? 4 : 2;
+    if (wp->fast) {
+#define GWF(NN, DD) gram_warp_fast<T, (NN), (DD), R>(smem_addr(tile), smem_addr(wp->op), ones, nrows, lane, \
+                                                     smem_addr(red), out, piece_lo, npieces, col_lo, piece_start, wp->accmap)
+        const bool deep = wp->n3 > 0;
+        switch (n2_class(wp->n2)) {
+            case 0: GWF(0, false); break;
+            case 1: if (deep) GWF(1, true); else GWF(1, false); break;
+            case 2: if (T >= 2) { if (deep) GWF(T >= 2 ? 2 : T, true); else GWF(T >= 2 ? 2 : T, false); break; }
+            default: if (deep) GWF(T, true); else GWF(T, false); break;
+        }
+#undef GWF
+    } else {
         gram_warp_generic<T>(tile, tstride, wp, fac, nrows, lane, smem_addr(red), out, piece_lo, npieces, col_lo,
                              piece_start);
+    }
 }
 
 template <int NW>
@@ -385,9 +417,11 @@ __global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
     extern __shared__ __align__(16) double smem[];
     __shared__ int s_next;
     __shared__ const double* s_tok[MAXU];
+    __shared__ __align__(16) double s_ones[128];     // 4 rows x 256 bytes of 1.0 (fast_terms_r)
     const int tid = threadIdx.x;
     const int nwarps = blockDim.x >> 5;
     const UnitDesc u = p.g.units[blockIdx.x];
+    for (int q = tid; q < 128; q += blockDim.x) s_ones[q] = 1.0;
     const int wb = u.b_hi - u.b_lo;
     const int nrows = (u.a_hi - u.a_lo) * wb;
     const int tstride = p.g.max_rows * TILE_COLS;
@@ -433,14 +467,17 @@ __global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
         if (lane < TMAX) {
             int4 d = eq->fastop[lane];            // slots -> byte offsets inside the tile
             d.x *= tstride * 8;
+            if (d.y >= 0) d.y *= tstride * 8;
             if (d.z >= 0) d.z *= tstride * 8;
+            if (d.w >= 0) d.w *= tstride * 8;
             wp->op[lane] = d;
         }
         if (lane <= TMAX) wp->foff[lane] = eq->fac_off[lane];
-        if (lane == 0) { wp->T = T; wp->fast = eq->fast; }
+        if (lane == 0) { wp->T = T; wp->fast = eq->fast; wp->n2 = eq->n2; wp->n3 = eq->n3; }
+        for (int k = lane; k < TMAX * (TMAX + 3) / 2; k += 32) wp->accmap[k] = eq->accmap[k];
         __syncwarp();
         double* out = p.cells + eq->c_off + ((long long)u.cell * p.g.npieces + u.piece_lo) * nacc_of(T);
-#define GW(TT) gram_warp<TT, NW>(tile, tstride, wp, p.factors, nrows, lane, red, out, u.piece_lo, u.npieces, u.col_lo, p.g.piece_start)
+#define GW(TT) gram_warp<TT>(tile, tstride, wp, p.factors, smem_addr(s_ones), nrows, lane, red, out, u.piece_lo, u.npieces, u.col_lo, p.g.piece_start)
         switch (T) {
             case 1: GW(1); break;
             case 2: GW(2); break;
@@ -847,7 +884,8 @@ struct ResidProg {
     int foff[TMAX + 1];      // factor ranges by TERM index (generic path)
     int dmap[TMAX];          // compact eval dd -> target term d (row of the sum table)
     int tcol[TMAX];          // compact eval dd -> used column of its target
-    int NU, NV, fast, pad;
+    int NU, NV, fast, n2;    // n2: used columns with >= 2 slot factors (they come first)
+    int n3, pad0, pad1, pad2;  // n3: used columns with >= 3 slot factors
 };
 
 template <int NU>
@@ -940,9 +978,9 @@ __device__ __forceinline__ void residual_reduce(const double (&a1)[NU], const do
 }
 
 // one (tile, equation) task, fast terms; returns through the shared table row
-template <int NU>
-__device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, const ResidProg* rp, int NV, int npts,
-                                                int lane, double* table_row) {
+template <int NU, int N2, bool DEEP>
+__device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, unsigned ones, const ResidProg* rp, int NV,
+                                                int npts, int lane, double* table_row) {
     constexpr int R = (NU <= 6) ? 4 : 2;
     const unsigned m_a = prog + (unsigned)offsetof(ResidProg, m);
     const unsigned sb_a = prog + (unsigned)offsetof(ResidProg, sb);
@@ -950,16 +988,18 @@ __device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, co
     double a1[NU], a3[NU], sabs[NU];
 #pragma unroll
     for (int k = 0; k < NU; ++k) { a1[k] = 0.0; a3[k] = 0.0; sabs[k] = 0.0; }
+    TermOffsets<NU, N2, DEEP> off;
+    load_term_offsets<NU, N2, DEEP>(prog, off);
     const int nfull = npts - npts % (32 * R);
     int i = lane;
     for (; i < nfull; i += 32 * R) {
         double c[R][NU];
-        fast_terms_r<NU, R, 256>(prog, tile + i * 8, c);
+        fast_terms_r<NU, N2, DEEP, R, 256>(off, tile + i * 8, ones, c);
         residual_points<NU, R>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
     }
     for (; i < npts; i += 32) {
         double c[1][NU];
-        fast_terms_r<NU, 1, 256>(prog, tile + i * 8, c);
+        fast_terms_r<NU, N2, DEEP, 1, 256>(off, tile + i * 8, ones, c);
         residual_points<NU, 1>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
     }
     residual_reduce<NU>(a1, a3, sabs, rp, NV, lane, table_row);
@@ -988,10 +1028,22 @@ __device__ __noinline__ void residual_task_generic(const double* tile_g, unsigne
 }
 
 template <int NU>
-__device__ __forceinline__ void residual_task(unsigned tile, const double* tile_g, unsigned prog, const ResidProg* rp,
-                                              const FactorDesc* fac, int npts, int lane, double* table_row) {
-    if (rp->fast) residual_task_fast<NU>(tile, prog, rp, rp->NV, npts, lane, table_row);
-    else residual_task_generic<NU>(tile_g, prog, rp, fac, rp->NV, npts, lane, table_row);
+__device__ __forceinline__ void residual_task(unsigned tile, const double* tile_g, unsigned prog, unsigned ones,
+                                              const ResidProg* rp, const FactorDesc* fac, int npts, int lane,
+                                              double* table_row) {
+    if (rp->fast) {
+#define RTF(NN, DD) residual_task_fast<NU, (NN), (DD)>(tile, prog, ones, rp, rp->NV, npts, lane, table_row)
+        const bool deep = rp->n3 > 0;
+        switch (n2_class(rp->n2)) {
+            case 0: RTF(0, false); break;
+            case 1: if (deep) RTF(1, true); else RTF(1, false); break;
+            case 2: if (NU >= 2) { if (deep) RTF(NU >= 2 ? 2 : NU, true); else RTF(NU >= 2 ? 2 : NU, false); break; }
+            default: if (deep) RTF(NU, true); else RTF(NU, false); break;
+        }
+#undef RTF
+    } else {
+        residual_task_generic<NU>(tile_g, prog, rp, fac, rp->NV, npts, lane, table_row);
+    }
 }
 
 template <int NW>
@@ -999,12 +1051,15 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
     extern __shared__ __align__(16) double smem[];
     __shared__ const double* s_tok[MAXU];
     __shared__ int s_next;
+    __shared__ __align__(16) double s_ones[128];     // 4 rows x 256 bytes of 1.0 (fast_terms_r)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int q = tid; q < 128; q += blockDim.x) s_ones[q] = 1.0;
     const int nwarps = blockDim.x >> 5;
     double* buf0 = smem;                                         // [2][U][RES_TILE]
     const size_t buf_doubles = (size_t)p.U * RES_TILE;
     ResidProg* progs = (ResidProg*)(smem + 2 * buf_doubles);     // [n_eq]
     double* table = (double*)(progs + p.n_eq);                   // [n_eq][TMAX][3]
+    int* order = (int*)(table + (size_t)p.n_eq * TMAX * 3);      // [n_eq] task order: same code variant adjacent
     if (tid < MAXU) s_tok[tid] = p.tok[tid];
     for (int q = tid; q < p.n_eq * TMAX * 3; q += blockDim.x) table[q] = 0.0;
 
@@ -1031,21 +1086,33 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
 #pragma unroll
         for (int d = 0; d < 4; ++d) used |= ((nz[0] >> (d * 8)) & 0xffu) | ((nz[1] >> (d * 8)) & 0xffu);
         const int NU = __popc(used), NV = __popc(valid);
+        // used columns in evaluation order (two-factor terms first): rank of this lane's term
+        int my_u = 0;
+        {
+            const int my_pos = (lane < T) ? eq->pos[lane] : 0;
+            for (int t2 = 0; t2 < T; ++t2)
+                if ((used >> t2 & 1u) && eq->pos[t2] < my_pos) ++my_u;
+        }
+        const int4 my_op = (lane < T) ? eq->fastop[eq->pos[lane]] : make_int4(0, -1, -1, -1);
+        const unsigned two = __ballot_sync(0xffffffffu, lane < T && (used >> lane & 1u) && my_op.z >= 0);
+        const unsigned three = __ballot_sync(0xffffffffu, lane < T && (used >> lane & 1u) && my_op.y >= 0);
         for (int q = lane; q < TMAX * TMAX; q += 32) rp->m[q] = 0.0;
-        if (lane < TMAX) { rp->op[lane] = make_int4(0, 1, -1, 1); rp->sb[lane] = 0.0; rp->sdb[lane] = 0.0; rp->term[lane] = 0; rp->dmap[lane] = 0; rp->tcol[lane] = 0; }
+        if (lane < TMAX) { rp->op[lane] = make_int4(0, -1, -1, -1); rp->sb[lane] = 0.0; rp->sdb[lane] = 0.0; rp->term[lane] = 0; rp->dmap[lane] = 0; rp->tcol[lane] = 0; }
         __syncwarp();
         if (lane < T && (used >> lane & 1u)) {
-            const int u = __popc(used & ((1u << lane) - 1u));
-            int4 d = eq->fastop[lane];
+            const int u = my_u;
+            int4 d = my_op;
             d.x *= RES_TILE * 8;
+            if (d.y >= 0) d.y *= RES_TILE * 8;
             if (d.z >= 0) d.z *= RES_TILE * 8;
+            if (d.w >= 0) d.w *= RES_TILE * 8;
             rp->op[u] = d;
             rp->term[u] = lane;
         }
         if (lane <= TMAX) rp->foff[lane] = eq->fac_off[lane];
         if (my_ev >= 0) {
             const int dd = __popc(valid & ((1u << lane) - 1u));
-            const int tc = __popc(used & ((1u << lane) - 1u));
+            const int tc = my_u;
             const double b1 = p.intercept_l1[my_ev];
             rp->sb[dd] = b1;
             rp->sdb[dd] = b1 - p.intercept[my_ev];
@@ -1058,13 +1125,32 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
         for (int h = 0; h < 2; ++h) {
             const int idx = lane + 32 * h;
             const int d = idx >> 3, j = idx & 7;
+            const int uj = __shfl_sync(0xffffffffu, my_u, j);
             if (wv[h] != 0.0) {
                 const int dd = __popc(valid & ((1u << d) - 1u));
-                const int u = __popc(used & ((1u << j) - 1u));
-                rp->m[dd * TMAX + u] = -wv[h];
+                rp->m[dd * TMAX + uj] = -wv[h];
             }
         }
-        if (lane == 0) { rp->NU = NU; rp->NV = NV; rp->fast = eq->fast; }
+        if (lane == 0) { rp->NU = NU; rp->NV = NV; rp->fast = eq->fast; rp->n2 = __popc(two); rp->n3 = __popc(three); }
+    }
+    __syncthreads();
+    // ---- task order: heaviest first, equations that run the same code variant (NU, factor class) next to each
+    //      other, so the warps of the CTA execute the same instructions at the same time (instruction cache)
+    {
+        auto key_of = [&](int le) {
+            const ResidProg* rp = progs + le;
+            if (rp->NV == 0) return -1;
+            return (rp->NU << 8) | (n2_class(rp->n2) << 4) | ((rp->n3 > 0) << 3) | (rp->fast ? 0 : 4);
+        };
+        for (int le = tid; le < p.n_eq; le += blockDim.x) {
+            const int k = key_of(le);
+            int rank = 0;
+            for (int j = 0; j < p.n_eq; ++j) {
+                const int kj = key_of(j);
+                rank += (kj > k || (kj == k && j < le)) ? 1 : 0;
+            }
+            order[rank] = le;
+        }
     }
     __syncthreads();
 
@@ -1099,13 +1185,14 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
         const long long start = (long long)tI * RES_TILE;
         const int npts = (int)((p.N - start) < RES_TILE ? (p.N - start) : RES_TILE);
         const unsigned cur_s = smem_addr(cur);
-        int le = warp;
-        while (le < p.n_eq) {
+        int ti = warp;
+        while (ti < p.n_eq) {
+            const int le = order[ti];
             const ResidProg* rp = progs + le;
             if (rp->NV > 0) {
                 const unsigned prog_s = smem_addr(rp);
                 double* row = table + (size_t)le * TMAX * 3;
-#define RT(UU) residual_task<UU>(cur_s, cur, prog_s, rp, p.factors, npts, lane, row)
+#define RT(UU) residual_task<UU>(cur_s, cur, prog_s, smem_addr(s_ones), rp, p.factors, npts, lane, row)
                 switch (rp->NU) {
                     case 1: RT(1); break;
                     case 2: RT(2); break;
@@ -1118,8 +1205,8 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
                 }
 #undef RT
             }
-            if (lane == 0) le = atomicAdd(&s_next, 1);
-            le = __shfl_sync(0xffffffffu, le, 0);
+            if (lane == 0) ti = atomicAdd(&s_next, 1);
+            ti = __shfl_sync(0xffffffffu, ti, 0);
         }
         __syncthreads();            // everyone is done with `cur` before it is refilled
     }
@@ -1233,7 +1320,7 @@ struct epde_ctx {
     int sm_count = 148;
     int max_smem = 227 * 1024;
     int resid_warps = RES_WARPS;
-    int gram_warps = GRAM_WARPS;   // EPDE_GRAM_WARPS=16 selects the 16-warp / 128-register variant
+    int gram_warps = GRAM_WARPS;
     // optional per-kernel-class device timing (epde_ctx_set_timing)
     bool timing = false;
     struct Span { int cls; cudaEvent_t a, b; };
@@ -1471,8 +1558,7 @@ static int launch_gram_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, d
         return fail("pass A tile needs %zu bytes of shared memory (> %d)", smem, c->max_smem);
     {
         KernelSpan ks(c, EPDE_KERNEL_GRAM);
-        if (nw_cfg <= 8) gram_tile_kernel<8><<<(unsigned)c->geom.n_units, nwarps * 32, smem, c->stream>>>(p);
-        else gram_tile_kernel<16><<<(unsigned)c->geom.n_units, nwarps * 32, smem, c->stream>>>(p);
+        gram_tile_kernel<GRAM_WARPS><<<(unsigned)c->geom.n_units, nwarps * 32, smem, c->stream>>>(p);
     }
     CK(cudaGetLastError());
     return 0;
@@ -1484,7 +1570,7 @@ static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, 
     const int ne_all = (int)g.eqs.size();
     // equations per launch: their programs and sum table live in shared memory next to the two tile buffers
     const size_t tile_bytes = sizeof(double) * 2 * (size_t)U * RES_TILE;
-    const size_t per_eq = sizeof(ResidProg) + sizeof(double) * TMAX * 3;
+    const size_t per_eq = sizeof(ResidProg) + sizeof(double) * TMAX * 3 + sizeof(int);
     if (tile_bytes + per_eq > (size_t)c->max_smem) return fail("pass B tiles need %zu bytes of shared memory", tile_bytes + per_eq);
     const int cap = (int)(((size_t)c->max_smem - tile_bytes) / per_eq);
     const int n_launch = (ne_all + cap - 1) / cap;
@@ -1506,8 +1592,7 @@ static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, 
         p.partial = (double*)c->d_partial.ptr;
         {
             KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
-            if (c->resid_warps <= 8) residual_tile_kernel<8><<<grid, nwarps * 32, smem, c->stream>>>(p);
-            else residual_tile_kernel<16><<<grid, nwarps * 32, smem, c->stream>>>(p);
+            residual_tile_kernel<RES_WARPS><<<grid, nwarps * 32, smem, c->stream>>>(p);
         }
         CK(cudaGetLastError());
         ResidFinalParams fp;
@@ -1543,14 +1628,11 @@ int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx**
     c->ndim = ndim;
     c->sm_count = prop.multiProcessorCount;
     c->max_smem = (int)prop.sharedMemPerBlockOptin;
-    if (const char* ev = getenv("EPDE_GRAM_WARPS")) c->gram_warps = (atoi(ev) > 8) ? 16 : 8;
-    if (const char* ev = getenv("EPDE_RESID_WARPS")) c->resid_warps = (atoi(ev) > 8) ? 16 : 8;
     {
         // dynamic shared memory limit = opt-in maximum minus the kernels' static shared memory
-        const void* fns[4] = {(const void*)gram_tile_kernel<8>, (const void*)gram_tile_kernel<16>,
-                              (const void*)residual_tile_kernel<8>, (const void*)residual_tile_kernel<16>};
+        const void* fns[2] = {(const void*)gram_tile_kernel<GRAM_WARPS>, (const void*)residual_tile_kernel<RES_WARPS>};
         int dyn_max = c->max_smem;
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 2; ++k) {
             cudaFuncAttributes fa;
             cudaError_t fe = cudaFuncGetAttributes(&fa, fns[k]);
             if (fe == cudaSuccess) {
@@ -1765,43 +1847,34 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
         if (d.kind < 0 || d.kind > 3) { delete b; return fail("factor %d has unknown kind %d", f, d.kind); }
         d.ipow = (d.power == 1.0) ? 1 : (d.power == 2.0) ? 2 : (d.power == 3.0) ? 3 : 0;
     }
-    // ---- launch groups: equations sorted by term count (most first); a group holds <= MAXU distinct
-    //      tokens and a cell table within the scratch budget
+    // ---- launch groups: a group shares one staged tile of <= MAXU distinct tokens.  Equations are taken most
+    //      terms first and placed first-fit into the open groups (token count and cell scratch permitting).
     std::vector<int> order(n_eq);
     for (int e = 0; e < n_eq; ++e) order[e] = e;
     std::stable_sort(order.begin(), order.end(), [&](int a, int bb) { return b->eqs[a].T > b->eqs[bb].T; });
-    {
-        LaunchGroup cur;
-        std::set<int> cur_tok;
-        auto flush = [&]() {
-            if (cur.eqs.empty()) return;
-            cur.token_ids.assign(cur_tok.begin(), cur_tok.end());
-            b->groups.push_back(cur);
-            cur = LaunchGroup();
-            cur_tok.clear();
-        };
-        for (int e : order) {
-            const EqDesc& q = b->eqs[e];
-            std::set<int> mine;
-            for (int f = q.fac_off[0]; f < q.fac_off[q.T]; ++f) mine.insert(fac_token[f]);
-            if ((int)mine.size() > MAXU) { delete b; return fail("equation %d references %d distinct tokens; supported: %d", e, (int)mine.size(), MAXU); }
-            std::set<int> uni = cur_tok;
+    std::vector<std::set<int>> group_tok;
+    for (int e : order) {
+        const EqDesc& q = b->eqs[e];
+        std::set<int> mine;
+        for (int f = q.fac_off[0]; f < q.fac_off[q.T]; ++f) mine.insert(fac_token[f]);
+        if ((int)mine.size() > MAXU) { delete b; return fail("equation %d references %d distinct tokens; supported: %d", e, (int)mine.size(), MAXU); }
+        const long long cd = (long long)c->n_cells * nacc_of(q.T);
+        int gi = -1;
+        for (size_t k = 0; k < b->groups.size() && gi < 0; ++k) {
+            std::set<int> uni = group_tok[k];
             uni.insert(mine.begin(), mine.end());
-            const long long cd = (long long)c->n_cells * nacc_of(q.T);
-            if (!cur.eqs.empty() && ((int)uni.size() > MAXU ||
-                                     (size_t)(cur.cell_doubles + cd) * sizeof(double) > c->cell_budget_bytes)) {
-                flush();
-                uni = mine;
-            }
-            cur_tok = uni;
-            cur.eqs.push_back(e);
-            cur.cell_doubles += cd;
+            if ((int)uni.size() <= MAXU &&
+                (size_t)(b->groups[k].cell_doubles + cd) * sizeof(double) <= c->cell_budget_bytes) gi = (int)k;
         }
-        flush();
+        if (gi < 0) { b->groups.push_back(LaunchGroup()); group_tok.push_back(std::set<int>()); gi = (int)b->groups.size() - 1; }
+        group_tok[gi].insert(mine.begin(), mine.end());
+        b->groups[gi].eqs.push_back(e);
+        b->groups[gi].cell_doubles += cd;
     }
     // per group: slots, cell offsets, fast-path encoding
     for (size_t gi = 0; gi < b->groups.size(); ++gi) {
         LaunchGroup& g = b->groups[gi];
+        g.token_ids.assign(group_tok[gi].begin(), group_tok[gi].end());
         std::map<int, int> slot;
         for (size_t u = 0; u < g.token_ids.size(); ++u) slot[g.token_ids[u]] = (int)u;
         long long c_off = 0;
@@ -1810,19 +1883,56 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
             q.group = (int)gi;
             q.c_off = c_off;
             c_off += (long long)c->n_cells * nacc_of(q.T);
+            // fast equation: every term is a product of <= 4 token values once integer powers are expanded
+            int nsf[TMAX];
+            int sf[TMAX][4];
             q.fast = 1;
-            for (int t = 0; t < TMAX; ++t) q.fastop[t] = make_int4(0, 1, -1, 1);
             for (int t = 0; t < q.T; ++t) {
-                const int f0 = q.fac_off[t], f1 = q.fac_off[t + 1];
-                for (int f = f0; f < f1; ++f) {
+                nsf[t] = 0;
+                for (int f = q.fac_off[t]; f < q.fac_off[t + 1]; ++f) {
                     factors[f].slot = slot[fac_token[f]];
-                    if (factors[f].kind != 0 || factors[f].ipow == 0) q.fast = 0;
+                    if (factors[f].kind != 0 || factors[f].ipow == 0) { q.fast = 0; continue; }
+                    for (int k = 0; k < factors[f].ipow; ++k) {
+                        if (nsf[t] < 4) sf[t][nsf[t]] = factors[f].slot;
+                        ++nsf[t];
+                    }
                 }
-                if (f1 - f0 > 2) q.fast = 0;
-                q.fastop[t].x = factors[f0].slot; q.fastop[t].y = factors[f0].ipow;
-                if (f1 - f0 >= 2) { q.fastop[t].z = factors[f0 + 1].slot; q.fastop[t].w = factors[f0 + 1].ipow; }
+                if (nsf[t] > 4) q.fast = 0;
+            }
+            for (int t = 0; t < TMAX; ++t) { q.fastop[t] = make_int4(0, -1, -1, -1); q.pos[t] = q.perm[t] = (unsigned char)t; }
+            // evaluation order: most slot factors first (fast equations only)
+            q.n2 = q.n3 = 0;
+            if (q.fast) {
+                int k = 0;
+                for (int want = 4; want >= 1; --want)
+                    for (int t = 0; t < q.T; ++t)
+                        if (nsf[t] == want) { q.perm[k] = (unsigned char)t; q.pos[t] = (unsigned char)k; ++k; }
+                for (int t = 0; t < q.T; ++t) {
+                    if (nsf[t] >= 2) ++q.n2;
+                    if (nsf[t] >= 3) ++q.n3;
+                    int4& op = q.fastop[q.pos[t]];
+                    op.x = sf[t][0];
+                    if (nsf[t] >= 2) op.z = sf[t][1];
+                    if (nsf[t] >= 3) op.y = sf[t][2];
+                    if (nsf[t] >= 4) op.w = sf[t][3];
+                }
+            }
+            {
+                int k = 0;
+                for (int i = 0; i < q.T; ++i)
+                    for (int j = i; j < q.T; ++j) q.accmap[k++] = (unsigned char)gidx(q.perm[i], q.perm[j], q.T);
+                for (int i = 0; i < q.T; ++i) q.accmap[k++] = (unsigned char)(q.T * (q.T + 1) / 2 + q.perm[i]);
             }
         }
+    }
+    // task order inside a group: most terms first, equations that run the same code variant (T, factor class)
+    // next to each other, so the warps of a CTA execute the same instructions at the same time
+    for (auto& g : b->groups) {
+        auto key = [&](int e) {
+            const EqDesc& q = b->eqs[e];
+            return (q.T << 8) | ((q.n2 <= 2 ? q.n2 : 3) << 4) | ((q.n3 > 0) << 3) | (q.fast ? 0 : 4);
+        };
+        std::stable_sort(g.eqs.begin(), g.eqs.end(), [&](int a, int bb) { return key(a) > key(bb); });
     }
     std::vector<int> slot_eval((size_t)n_eq * TMAX, -1);
     for (int v = 0; v < n_eval; ++v) {

@@ -171,7 +171,7 @@ def test_population_batch_equals_one_by_one(bound_fixture):
 
 
 def test_l2_fitness_and_penalty():
-    """L2Fitness.apply: out-of-place value == ||Fw + b - t||_2 of the oracle; penalty division when
+    """L2Fitness.apply: out-of-place value == ||Fw + b - t||_2 of the reference / oracle; penalty division when
     sum(weights_final) == 0 (fitness.py:85-91); bad penalty_coeff raises ValueError."""
     fx = load_fixture('wave_b5')
     shape = tuple(int(s) for s in fx['shape'])
@@ -186,8 +186,6 @@ def test_l2_fitness_and_penalty():
             l2 = wire(ops.L2Fitness)
             checked = 0
             for v in range(len(fx['ev_eq'])):
-                if np.isnan(fx['ev_fit_l2'][v]):
-                    continue
                 eq = eqs[int(fx['ev_eq'][v])]
                 o = orc.evaluate_equation(fx['tokens'], shape, eq, targets=[int(fx['ev_tgt'][v])])[0]
                 if o.cond > COND_MAX:
@@ -195,7 +193,10 @@ def test_l2_fitness_and_penalty():
                 obj = equation_from_encoding(eq, labels, [l for l in labels if l != 'u'])
                 obj.target_idx = int(fx['ev_tgt'][v])
                 val = l2.apply(obj, {}, force_out_of_place=True)
-                ref = fx['ev_fit_l2'][v]
+                # the reference's own L2Fitness broadcasts against the FULL-grid g_func (fitness.py:81-82),
+                # which only works with boundary 0; where the fixture holds its value use it, else the
+                # oracle's restatement on the interior
+                ref = o.fitness_l2 if np.isnan(fx['ev_fit_l2'][v]) else fx['ev_fit_l2'][v]
                 if np.sum(obj.weights_final) == 0:
                     ref = ref / 0.2
                 assert_rel(val, ref, f'eval {v} l2 fitness', atol=1e-9 * np.linalg.norm(orc.eval_term(fx['tokens'], eq[obj.target_idx])))
