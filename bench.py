@@ -245,13 +245,13 @@ def run_b200(args):
 
     shape, kind, eqs, evals = build_workload(args.workload, args.pop, args.seed)
     grid_sharded = args.workload == 'heat512' and world > 1
+    from epde_b200 import sharding
     if grid_sharded:
-        lo, hi = rank * shape[0] // world, (rank + 1) * shape[0] // world
-        local_shape, shard = (hi - lo,) + tuple(shape[1:]), (lo, shape[0])
+        (lo, hi), local_shape, shard = sharding.grid_slab(shape, rank, world)
         my_eqs, my_evals = eqs, evals
     else:
         lo, hi, local_shape, shard = 0, shape[0], tuple(shape), None
-        my_eqs = eqs[rank::world]
+        my_eqs = [eqs[i] for i in sharding.population_slice(len(eqs), rank, world)]
         my_evals = syn.make_evals(my_eqs)
     n_local = int(np.prod(local_shape))
 
@@ -331,13 +331,7 @@ def run_b200(args):
     # ---- end to end through the host API: host encodings in, host results out, every step
     def e2e_step():
         if grid_sharded:
-            with eng.batch(enc) as b:
-                b.gram(seg.data_ptr())
-                dist.all_reduce(seg)
-                b.solve(seg.data_ptr())
-                b.residual(sums.data_ptr())
-                dist.all_reduce(sums)
-                return b.fetch(sums.data_ptr(), want_sw=False)
+            return sharding.evaluate_grid_sharded(eng, enc, seg, sums, want_sw=False)
         return eng.evaluate(enc, want_sw=False)
 
     def timed_wall(step_fn, k):

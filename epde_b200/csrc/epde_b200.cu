@@ -99,7 +99,8 @@ struct EqDesc {
     long long w_off;         // doubles, into the window-Gram table
     int4 fastop[TMAX];       // fast terms IN EVALUATION ORDER (most slot factors first): slots {A, C, B, D} of
                              // the term's factors with integer powers expanded (u^2 * v -> u, u, v); -1 = absent
-    int n2, n3;              // terms with >= 2 / >= 3 slot factors (fast equations)
+    int2 fastop2[TMAX];      // slots {E, F} of terms with five / six slot factors
+    int n2, n3;              // terms with >= 2 slot factors; depth: 0 (<= 2 factors everywhere), 1 (<= 4), 2 (<= 6)
     unsigned char pos[TMAX]; // term index -> evaluation position
     unsigned char perm[TMAX];// evaluation position -> term index
     unsigned char accmap[TMAX * (TMAX + 3) / 2];   // Gram accumulator in evaluation order -> index in term order
@@ -198,6 +199,7 @@ __device__ __forceinline__ double eval_term_generic(const FactorDesc* fac, int f
 struct WarpProg {
     int4 op[TMAX];           // fast terms in evaluation order: byte offsets of slots {A, C, B, D}, -1 = absent
     int foff[TMAX + 1];      // generic path: factor ranges
+    int2 op2[TMAX];          // byte offsets of slots {E, F}
     int T, fast, n2, n3;
     unsigned char accmap[TMAX * (TMAX + 3) / 2 + 4];
 };
@@ -258,28 +260,38 @@ __device__ __forceinline__ void gram_accumulate(double (&acc)[T * (T + 3) / 2], 
 // fast terms for R consecutive tile rows of one lane, branch free.  A fast term is a product of 1..4 token
 // values (integer powers expanded: u^2 * v = u * u * v).  Terms come in evaluation order, most factors
 // first.  N2 = number of leading terms that get a second-factor multiply, one of {0, 1, 2, T} (the class
-// >= the equation's count); DEEP: those N2 terms also get a third and fourth multiply.  A term inside a
+// >= the equation's count); DEEP 1 / 2: those N2 terms also get factors three-four / three-six.  A term inside a
 // class without that factor multiplies by 1.0 read from a small shared region of ones, so the body is
 // straight-line code the scheduler interleaves with the Gram FMAs.  ops: shared address of the int4 op
 // table (byte offsets of slots {A, C, B, D}, -1 = absent); pr: shared address of the lane's element in
 // row `row` of slot 0; rows are ROWB bytes apart; ones: shared address of >= R * ROWB bytes of 1.0.
-template <int T, int N2, bool DEEP>
-struct TermOffsets { int a[T]; int b[N2 > 0 ? N2 : 1]; int c[(DEEP && N2 > 0) ? N2 : 1]; int d[(DEEP && N2 > 0) ? N2 : 1]; };
+template <int T, int N2, int DEEP>
+struct TermOffsets {
+    int a[T];
+    int b[N2 > 0 ? N2 : 1];
+    int c[(DEEP >= 1 && N2 > 0) ? N2 : 1], d[(DEEP >= 1 && N2 > 0) ? N2 : 1];
+    int e[(DEEP >= 2 && N2 > 0) ? N2 : 1], f[(DEEP >= 2 && N2 > 0) ? N2 : 1];
+};
 
-template <int T, int N2, bool DEEP>
-__device__ __forceinline__ void load_term_offsets(unsigned ops, TermOffsets<T, N2, DEEP>& o) {
+template <int T, int N2, int DEEP>
+__device__ __forceinline__ void load_term_offsets(unsigned ops, unsigned ops2, TermOffsets<T, N2, DEEP>& o) {
 #pragma unroll
     for (int t = 0; t < T; ++t) {
         const int4 q = lds_v4(ops + t * 16);
         o.a[t] = q.x;
         if (t < N2) {
             o.b[t] = q.z;
-            if (DEEP) { o.c[t] = q.y; o.d[t] = q.w; }
+            if (DEEP >= 1) { o.c[t] = q.y; o.d[t] = q.w; }
+            if (DEEP >= 2) {
+                int ex, fx;
+                asm("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(ex), "=r"(fx) : "r"(ops2 + t * 8));
+                o.e[t] = ex; o.f[t] = fx;
+            }
         }
     }
 }
 
-template <int T, int N2, bool DEEP, int R, int ROWB>
+template <int T, int N2, int DEEP, int R, int ROWB>
 __device__ __forceinline__ void fast_terms_r(const TermOffsets<T, N2, DEEP>& o, unsigned pr, unsigned ones,
                                              double (&c)[R][T]) {
 #pragma unroll
@@ -293,7 +305,7 @@ __device__ __forceinline__ void fast_terms_r(const TermOffsets<T, N2, DEEP>& o, 
 #pragma unroll
         for (int r = 0; r < R; ++r) c[r][t] *= lds_f64(ab + r * ROWB);
     }
-    if (DEEP) {
+    if (DEEP >= 1) {
 #pragma unroll
         for (int t = 0; t < N2; ++t) {
             const unsigned ac = (o.c[t] >= 0) ? pr + o.c[t] : ones;
@@ -302,6 +314,18 @@ __device__ __forceinline__ void fast_terms_r(const TermOffsets<T, N2, DEEP>& o, 
             for (int r = 0; r < R; ++r) {
                 c[r][t] *= lds_f64(ac + r * ROWB);
                 c[r][t] *= lds_f64(ad + r * ROWB);
+            }
+        }
+    }
+    if (DEEP >= 2) {
+#pragma unroll
+        for (int t = 0; t < N2; ++t) {
+            const unsigned ae = (o.e[t] >= 0) ? pr + o.e[t] : ones;
+            const unsigned af = (o.f[t] >= 0) ? pr + o.f[t] : ones;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                c[r][t] *= lds_f64(ae + r * ROWB);
+                c[r][t] *= lds_f64(af + r * ROWB);
             }
         }
     }
@@ -339,8 +363,8 @@ __device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2]
 }
 
 // fast path: every term = x^p [* y^q], p, q in {1, 2, 3}; R tile rows per iteration
-template <int T, int N2, bool DEEP, int R>
-__device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, unsigned ones, int nrows, int lane, unsigned red,
+template <int T, int N2, int DEEP, int R>
+__device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, unsigned ops2, unsigned ones, int nrows, int lane, unsigned red,
                                             double* out, int piece_lo, int npieces, int col_lo,
                                             const int* __restrict__ piece_start, const unsigned char* accmap) {
     constexpr int NACC = T * (T + 3) / 2;
@@ -350,7 +374,7 @@ __device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, unsigne
     for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
     const unsigned base = tile + lane * 8;
     TermOffsets<T, N2, DEEP> off;
-    load_term_offsets<T, N2, DEEP>(ops, off);
+    load_term_offsets<T, N2, DEEP>(ops, ops2, off);
     int row = 0;
     if (R > 1) {
         for (; row + R <= nrows; row += R) {
@@ -396,15 +420,16 @@ __device__ __forceinline__ void gram_warp(const double* tile, int tstride, const
     // 8-warp CTAs may use 255 registers per thread: four rows per iteration (two for the widest equations)
     constexpr int R = T <= 6 ? 4 : 2;
     if (wp->fast) {
-#define GWF(NN, DD) gram_warp_fast<T, (NN), (DD), R>(smem_addr(tile), smem_addr(wp->op), ones, nrows, lane, \
-                                                     smem_addr(red), out, piece_lo, npieces, col_lo, piece_start, wp->accmap)
-        const bool deep = wp->n3 > 0;
+#define GWF(NN, DD) gram_warp_fast<T, (NN), (DD), R>(smem_addr(tile), smem_addr(wp->op), smem_addr(wp->op2), ones, nrows, \
+                                                     lane, smem_addr(red), out, piece_lo, npieces, col_lo, piece_start, wp->accmap)
+#define GWD(NN) do { if (wp->n3 == 0) GWF(NN, 0); else if (wp->n3 == 1) GWF(NN, 1); else GWF(NN, 2); } while (0)
         switch (n2_class(wp->n2)) {
-            case 0: GWF(0, false); break;
-            case 1: if (deep) GWF(1, true); else GWF(1, false); break;
-            case 2: if (T >= 2) { if (deep) GWF(T >= 2 ? 2 : T, true); else GWF(T >= 2 ? 2 : T, false); break; }
-            default: if (deep) GWF(T, true); else GWF(T, false); break;
+            case 0: GWF(0, 0); break;
+            case 1: GWD(1); break;
+            case 2: if (T >= 2) { GWD(T >= 2 ? 2 : T); break; }
+            default: GWD(T); break;
         }
+#undef GWD
 #undef GWF
     } else {
         gram_warp_generic<T>(tile, tstride, wp, fac, nrows, lane, smem_addr(red), out, piece_lo, npieces, col_lo,
@@ -471,6 +496,10 @@ __global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
             if (d.z >= 0) d.z *= tstride * 8;
             if (d.w >= 0) d.w *= tstride * 8;
             wp->op[lane] = d;
+            int2 d2 = eq->fastop2[lane];
+            if (d2.x >= 0) d2.x *= tstride * 8;
+            if (d2.y >= 0) d2.y *= tstride * 8;
+            wp->op2[lane] = d2;
         }
         if (lane <= TMAX) wp->foff[lane] = eq->fac_off[lane];
         if (lane == 0) { wp->T = T; wp->fast = eq->fast; wp->n2 = eq->n2; wp->n3 = eq->n3; }
@@ -885,7 +914,8 @@ struct ResidProg {
     int dmap[TMAX];          // compact eval dd -> target term d (row of the sum table)
     int tcol[TMAX];          // compact eval dd -> used column of its target
     int NU, NV, fast, n2;    // n2: used columns with >= 2 slot factors (they come first)
-    int n3, pad0, pad1, pad2;  // n3: used columns with >= 3 slot factors
+    int n3, pad0, pad1, pad2;  // n3: depth over the used columns: 0 (<= 2 slot factors), 1 (<= 4), 2 (<= 6)
+    int2 op2[TMAX];            // byte offsets of slots {E, F}
 };
 
 template <int NU>
@@ -978,7 +1008,7 @@ __device__ __forceinline__ void residual_reduce(const double (&a1)[NU], const do
 }
 
 // one (tile, equation) task, fast terms; returns through the shared table row
-template <int NU, int N2, bool DEEP>
+template <int NU, int N2, int DEEP>
 __device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, unsigned ones, const ResidProg* rp, int NV,
                                                 int npts, int lane, double* table_row) {
     constexpr int R = (NU <= 6) ? 4 : 2;
@@ -989,7 +1019,7 @@ __device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, un
 #pragma unroll
     for (int k = 0; k < NU; ++k) { a1[k] = 0.0; a3[k] = 0.0; sabs[k] = 0.0; }
     TermOffsets<NU, N2, DEEP> off;
-    load_term_offsets<NU, N2, DEEP>(prog, off);
+    load_term_offsets<NU, N2, DEEP>(prog, prog + (unsigned)offsetof(ResidProg, op2), off);
     const int nfull = npts - npts % (32 * R);
     int i = lane;
     for (; i < nfull; i += 32 * R) {
@@ -1033,13 +1063,14 @@ __device__ __forceinline__ void residual_task(unsigned tile, const double* tile_
                                               double* table_row) {
     if (rp->fast) {
 #define RTF(NN, DD) residual_task_fast<NU, (NN), (DD)>(tile, prog, ones, rp, rp->NV, npts, lane, table_row)
-        const bool deep = rp->n3 > 0;
+#define RTD(NN) do { if (rp->n3 == 0) RTF(NN, 0); else if (rp->n3 == 1) RTF(NN, 1); else RTF(NN, 2); } while (0)
         switch (n2_class(rp->n2)) {
-            case 0: RTF(0, false); break;
-            case 1: if (deep) RTF(1, true); else RTF(1, false); break;
-            case 2: if (NU >= 2) { if (deep) RTF(NU >= 2 ? 2 : NU, true); else RTF(NU >= 2 ? 2 : NU, false); break; }
-            default: if (deep) RTF(NU, true); else RTF(NU, false); break;
+            case 0: RTF(0, 0); break;
+            case 1: RTD(1); break;
+            case 2: if (NU >= 2) { RTD(NU >= 2 ? 2 : NU); break; }
+            default: RTD(NU); break;
         }
+#undef RTD
 #undef RTF
     } else {
         residual_task_generic<NU>(tile_g, prog, rp, fac, rp->NV, npts, lane, table_row);
@@ -1095,9 +1126,11 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
         }
         const int4 my_op = (lane < T) ? eq->fastop[eq->pos[lane]] : make_int4(0, -1, -1, -1);
         const unsigned two = __ballot_sync(0xffffffffu, lane < T && (used >> lane & 1u) && my_op.z >= 0);
+        const int2 my_op2 = (lane < T) ? eq->fastop2[eq->pos[lane]] : make_int2(-1, -1);
         const unsigned three = __ballot_sync(0xffffffffu, lane < T && (used >> lane & 1u) && my_op.y >= 0);
+        const unsigned five = __ballot_sync(0xffffffffu, lane < T && (used >> lane & 1u) && my_op2.x >= 0);
         for (int q = lane; q < TMAX * TMAX; q += 32) rp->m[q] = 0.0;
-        if (lane < TMAX) { rp->op[lane] = make_int4(0, -1, -1, -1); rp->sb[lane] = 0.0; rp->sdb[lane] = 0.0; rp->term[lane] = 0; rp->dmap[lane] = 0; rp->tcol[lane] = 0; }
+        if (lane < TMAX) { rp->op[lane] = make_int4(0, -1, -1, -1); rp->op2[lane] = make_int2(-1, -1); rp->sb[lane] = 0.0; rp->sdb[lane] = 0.0; rp->term[lane] = 0; rp->dmap[lane] = 0; rp->tcol[lane] = 0; }
         __syncwarp();
         if (lane < T && (used >> lane & 1u)) {
             const int u = my_u;
@@ -1107,6 +1140,10 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
             if (d.z >= 0) d.z *= RES_TILE * 8;
             if (d.w >= 0) d.w *= RES_TILE * 8;
             rp->op[u] = d;
+            int2 d2 = my_op2;
+            if (d2.x >= 0) d2.x *= RES_TILE * 8;
+            if (d2.y >= 0) d2.y *= RES_TILE * 8;
+            rp->op2[u] = d2;
             rp->term[u] = lane;
         }
         if (lane <= TMAX) rp->foff[lane] = eq->fac_off[lane];
@@ -1131,7 +1168,7 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
                 rp->m[dd * TMAX + uj] = -wv[h];
             }
         }
-        if (lane == 0) { rp->NU = NU; rp->NV = NV; rp->fast = eq->fast; rp->n2 = __popc(two); rp->n3 = __popc(three); }
+        if (lane == 0) { rp->NU = NU; rp->NV = NV; rp->fast = eq->fast; rp->n2 = __popc(two); rp->n3 = five ? 2 : (three ? 1 : 0); }
     }
     __syncthreads();
     // ---- task order: heaviest first, equations that run the same code variant (NU, factor class) next to each
@@ -1140,7 +1177,7 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
         auto key_of = [&](int le) {
             const ResidProg* rp = progs + le;
             if (rp->NV == 0) return -1;
-            return (rp->NU << 8) | (n2_class(rp->n2) << 4) | ((rp->n3 > 0) << 3) | (rp->fast ? 0 : 4);
+            return (rp->NU << 8) | (n2_class(rp->n2) << 4) | (rp->n3 << 2) | (rp->fast ? 0 : 2);
         };
         for (int le = tid; le < p.n_eq; le += blockDim.x) {
             const int k = key_of(le);
@@ -1883,9 +1920,9 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
             q.group = (int)gi;
             q.c_off = c_off;
             c_off += (long long)c->n_cells * nacc_of(q.T);
-            // fast equation: every term is a product of <= 4 token values once integer powers are expanded
+            // fast equation: every term is a product of <= 6 token values once integer powers are expanded
             int nsf[TMAX];
-            int sf[TMAX][4];
+            int sf[TMAX][6];
             q.fast = 1;
             for (int t = 0; t < q.T; ++t) {
                 nsf[t] = 0;
@@ -1893,28 +1930,34 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
                     factors[f].slot = slot[fac_token[f]];
                     if (factors[f].kind != 0 || factors[f].ipow == 0) { q.fast = 0; continue; }
                     for (int k = 0; k < factors[f].ipow; ++k) {
-                        if (nsf[t] < 4) sf[t][nsf[t]] = factors[f].slot;
+                        if (nsf[t] < 6) sf[t][nsf[t]] = factors[f].slot;
                         ++nsf[t];
                     }
                 }
-                if (nsf[t] > 4) q.fast = 0;
+                if (nsf[t] > 6) q.fast = 0;
             }
-            for (int t = 0; t < TMAX; ++t) { q.fastop[t] = make_int4(0, -1, -1, -1); q.pos[t] = q.perm[t] = (unsigned char)t; }
+            for (int t = 0; t < TMAX; ++t) {
+                q.fastop[t] = make_int4(0, -1, -1, -1); q.fastop2[t] = make_int2(-1, -1);
+                q.pos[t] = q.perm[t] = (unsigned char)t;
+            }
             // evaluation order: most slot factors first (fast equations only)
             q.n2 = q.n3 = 0;
             if (q.fast) {
                 int k = 0;
-                for (int want = 4; want >= 1; --want)
+                for (int want = 6; want >= 1; --want)
                     for (int t = 0; t < q.T; ++t)
                         if (nsf[t] == want) { q.perm[k] = (unsigned char)t; q.pos[t] = (unsigned char)k; ++k; }
                 for (int t = 0; t < q.T; ++t) {
                     if (nsf[t] >= 2) ++q.n2;
-                    if (nsf[t] >= 3) ++q.n3;
+                    if (nsf[t] >= 3 && q.n3 < 1) q.n3 = 1;
+                    if (nsf[t] >= 5) q.n3 = 2;
                     int4& op = q.fastop[q.pos[t]];
                     op.x = sf[t][0];
                     if (nsf[t] >= 2) op.z = sf[t][1];
                     if (nsf[t] >= 3) op.y = sf[t][2];
                     if (nsf[t] >= 4) op.w = sf[t][3];
+                    if (nsf[t] >= 5) q.fastop2[q.pos[t]].x = sf[t][4];
+                    if (nsf[t] >= 6) q.fastop2[q.pos[t]].y = sf[t][5];
                 }
             }
             {
@@ -1930,7 +1973,7 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
     for (auto& g : b->groups) {
         auto key = [&](int e) {
             const EqDesc& q = b->eqs[e];
-            return (q.T << 8) | ((q.n2 <= 2 ? q.n2 : 3) << 4) | ((q.n3 > 0) << 3) | (q.fast ? 0 : 4);
+            return (q.T << 8) | ((q.n2 <= 2 ? q.n2 : 3) << 4) | (q.n3 << 2) | (q.fast ? 0 : 2);
         };
         std::stable_sort(g.eqs.begin(), g.eqs.end(), [&](int a, int bb) { return key(a) > key(bb); });
     }
