@@ -56,7 +56,7 @@
 #define RED_CHUNK 8            // Gram entries reduced per shared-memory round of the cell flush
 #define MAXU 12                // distinct tokens per launch group (tile = MAXU x 64 x 32 doubles = 192 KB)
 #define RES_WARPS 8            // warps per pass-B CTA (8 x <= 255 registers)
-#define RES_TILE 1024          // points of a pass-B tile
+#define RES_TILE_MIN 1024      // points of a pass-B tile
 
 static thread_local std::string g_err;
 
@@ -878,7 +878,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
 
 // ------------------------------------------------------------------------------------------
 // pass B: residual sums per eval: sum|r|, sum|t|, sum r2^2 with r = t - (F w + b1), r2 = t - (F w + b)
-// (fitness.py:135-142 and 70-83).  Persistent CTAs walk over tiles of RES_TILE consecutive points
+// (fitness.py:135-142 and 70-83).  Persistent CTAs walk over tiles of tile_pts consecutive points
 // (double-buffered in shared memory with cp.async).  Each CTA first builds the "residual program" of
 // every equation of the launch in shared memory (term ops, weights of every eval, masks); then, per
 // tile, its warps take equations from the list dynamically (longest first) and evaluate all evals of
@@ -893,6 +893,7 @@ struct ResidParams {
     int n_eq;
     int U;
     int n_tiles;
+    int tile_pts;            // points per tile (multiple of 1024)
     const double* tok[MAXU];
     const int* slot_eval;    // [n_eq_total][TMAX] eval id of (equation, target term) or -1
     const double* wterm;     // [n_eval][TMAX]
@@ -942,10 +943,14 @@ __device__ __forceinline__ void residual_points(const double (&c)[R][NU], int NV
                                                 unsigned sdb_a, double (&a1)[NU], double (&a3)[NU], double (&sabs)[NU]) {
 #pragma unroll
     for (int u = 0; u < NU; ++u) {
-        double t = 0.0;
+        if (R == 4) {
+            sabs[u] += (fabs(c[0][u]) + fabs(c[1][u])) + (fabs(c[2][u]) + fabs(c[3][u]));
+        } else {
+            double t = 0.0;
 #pragma unroll
-        for (int r = 0; r < R; ++r) t += fabs(c[r][u]);
-        sabs[u] += t;
+            for (int r = 0; r < R; ++r) t += fabs(c[r][u]);
+            sabs[u] += t;
+        }
     }
 #pragma unroll
     for (int dd = 0; dd < NU; ++dd) {
@@ -961,15 +966,23 @@ __device__ __forceinline__ void residual_points(const double (&c)[R][NU], int NV
                 for (int r = 0; r < R; ++r) rr[r] = fma(w, c[r][u], rr[r]);
             }
             const double db = lds_f64(sdb_a + dd * 8);        // L2Fitness keeps the LASSO intercept (fitness.py:80)
-            double s1 = 0.0, s3 = a3[dd];
+            // pairwise (fixed order) instead of a serial chain: the R points are independent
+            double q[R];
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                s1 += fabs(rr[r]);
-                const double q = rr[r] + db;
-                s3 = fma(q, q, s3);
+            for (int r = 0; r < R; ++r) q[r] = rr[r] + db;
+            if (R == 4) {
+                a1[dd] += (fabs(rr[0]) + fabs(rr[1])) + (fabs(rr[2]) + fabs(rr[3]));
+                a3[dd] += fma(q[0], q[0], q[1] * q[1]) + fma(q[2], q[2], q[3] * q[3]);
+            } else if (R == 2) {
+                a1[dd] += fabs(rr[0]) + fabs(rr[1]);
+                a3[dd] += fma(q[0], q[0], q[1] * q[1]);
+            } else {
+                double s1 = 0.0, s3 = a3[dd];
+#pragma unroll
+                for (int r = 0; r < R; ++r) { s1 += fabs(rr[r]); s3 = fma(q[r], q[r], s3); }
+                a1[dd] += s1;
+                a3[dd] = s3;
             }
-            a1[dd] += s1;
-            a3[dd] = s3;
         }
     }
 }
@@ -1037,7 +1050,7 @@ __device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, un
 
 // same, generic terms (any kind / power / factor count)
 template <int NU>
-__device__ __noinline__ void residual_task_generic(const double* tile_g, unsigned prog, const ResidProg* rp,
+__device__ __noinline__ void residual_task_generic(const double* tile_g, int tile_pts, unsigned prog, const ResidProg* rp,
                                                    const FactorDesc* fac, int NV, int npts, int lane, double* table_row) {
     const unsigned m_a = prog + (unsigned)offsetof(ResidProg, m);
     const unsigned sb_a = prog + (unsigned)offsetof(ResidProg, sb);
@@ -1050,7 +1063,7 @@ __device__ __noinline__ void residual_task_generic(const double* tile_g, unsigne
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
             const int t = rp->term[u];
-            c[0][u] = eval_term_generic(fac, rp->foff[t], rp->foff[t + 1], tile_g + i, RES_TILE);
+            c[0][u] = eval_term_generic(fac, rp->foff[t], rp->foff[t + 1], tile_g + i, tile_pts);
         }
         residual_points<NU, 1>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
     }
@@ -1058,7 +1071,7 @@ __device__ __noinline__ void residual_task_generic(const double* tile_g, unsigne
 }
 
 template <int NU>
-__device__ __forceinline__ void residual_task(unsigned tile, const double* tile_g, unsigned prog, unsigned ones,
+__device__ __forceinline__ void residual_task(unsigned tile, const double* tile_g, int tile_pts, unsigned prog, unsigned ones,
                                               const ResidProg* rp, const FactorDesc* fac, int npts, int lane,
                                               double* table_row) {
     if (rp->fast) {
@@ -1073,7 +1086,7 @@ __device__ __forceinline__ void residual_task(unsigned tile, const double* tile_
 #undef RTD
 #undef RTF
     } else {
-        residual_task_generic<NU>(tile_g, prog, rp, fac, rp->NV, npts, lane, table_row);
+        residual_task_generic<NU>(tile_g, tile_pts, prog, rp, fac, rp->NV, npts, lane, table_row);
     }
 }
 
@@ -1086,9 +1099,10 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int q = tid; q < 128; q += blockDim.x) s_ones[q] = 1.0;
     const int nwarps = blockDim.x >> 5;
-    double* buf0 = smem;                                         // [2][U][RES_TILE]
-    const size_t buf_doubles = (size_t)p.U * RES_TILE;
-    ResidProg* progs = (ResidProg*)(smem + 2 * buf_doubles);     // [n_eq]
+    double* buf0 = smem;                                         // [U][tile_pts]
+    const int TP = p.tile_pts;
+    const size_t buf_doubles = (size_t)p.U * TP;
+    ResidProg* progs = (ResidProg*)(smem + buf_doubles);         // [n_eq]
     double* table = (double*)(progs + p.n_eq);                   // [n_eq][TMAX][3]
     int* order = (int*)(table + (size_t)p.n_eq * TMAX * 3);      // [n_eq] task order: same code variant adjacent
     if (tid < MAXU) s_tok[tid] = p.tok[tid];
@@ -1135,14 +1149,14 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
         if (lane < T && (used >> lane & 1u)) {
             const int u = my_u;
             int4 d = my_op;
-            d.x *= RES_TILE * 8;
-            if (d.y >= 0) d.y *= RES_TILE * 8;
-            if (d.z >= 0) d.z *= RES_TILE * 8;
-            if (d.w >= 0) d.w *= RES_TILE * 8;
+            d.x *= TP * 8;
+            if (d.y >= 0) d.y *= TP * 8;
+            if (d.z >= 0) d.z *= TP * 8;
+            if (d.w >= 0) d.w *= TP * 8;
             rp->op[u] = d;
             int2 d2 = my_op2;
-            if (d2.x >= 0) d2.x *= RES_TILE * 8;
-            if (d2.y >= 0) d2.y *= RES_TILE * 8;
+            if (d2.x >= 0) d2.x *= TP * 8;
+            if (d2.y >= 0) d2.y *= TP * 8;
             rp->op2[u] = d2;
             rp->term[u] = lane;
         }
@@ -1191,36 +1205,27 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
     }
     __syncthreads();
 
-    // ---- double-buffered walk over the tiles
-    auto issue = [&](int tI, double* dst_buf) {
-        const long long start = (long long)tI * RES_TILE;
-        const int npts = (int)((p.N - start) < RES_TILE ? (p.N - start) : RES_TILE);
-        const int total = p.U * (RES_TILE / 2);
-        for (int q = tid; q < total; q += blockDim.x) {
-            const int part = q & (RES_TILE / 2 - 1), us = q / (RES_TILE / 2);
-            const int c0 = part * 2;
-            const double* src = s_tok[us] + start + c0;
-            double* dst = dst_buf + (size_t)us * RES_TILE + c0;
-            if (c0 + 2 <= npts) cp_async16(dst, src);
-            else if (c0 < npts) cp_async8(dst, src);
-        }
-        asm volatile("cp.async.commit_group;\n" ::: "memory");
-    };
-    int tI = blockIdx.x;
-    if (tI < p.n_tiles) issue(tI, buf0);
-    for (int k = 0; tI < p.n_tiles; tI += gridDim.x, ++k) {
-        double* cur = buf0 + (size_t)(k & 1) * buf_doubles;
-        const int nxt = tI + gridDim.x;
-        if (nxt < p.n_tiles) {
-            issue(nxt, buf0 + (size_t)((k + 1) & 1) * buf_doubles);
-            asm volatile("cp.async.wait_group 1;\n" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    // ---- walk over the tiles.  One buffer: the fill of a tile (a few microseconds from L2 / HBM) is short next to
+    //      the ~100 equation tasks computed on it, and the larger tile halves the per-task overheads.
+    for (int tI = blockIdx.x; tI < p.n_tiles; tI += gridDim.x) {
+        double* cur = buf0;
+        const long long start = (long long)tI * TP;
+        const int npts = (int)((p.N - start) < TP ? (p.N - start) : TP);
+        {
+            const int half = TP / 2;
+            const int total = p.U * half;
+            for (int q = tid; q < total; q += blockDim.x) {
+                const int us = q / half, part = q - us * half;
+                const int c0 = part * 2;
+                const double* src = s_tok[us] + start + c0;
+                double* dst = cur + (size_t)us * TP + c0;
+                if (c0 + 2 <= npts) cp_async16(dst, src);
+                else if (c0 < npts) cp_async8(dst, src);
+            }
+            cp_async_wait_all();
         }
         if (tid == 0) s_next = nwarps;
         __syncthreads();
-        const long long start = (long long)tI * RES_TILE;
-        const int npts = (int)((p.N - start) < RES_TILE ? (p.N - start) : RES_TILE);
         const unsigned cur_s = smem_addr(cur);
         int ti = warp;
         while (ti < p.n_eq) {
@@ -1229,7 +1234,7 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
             if (rp->NV > 0) {
                 const unsigned prog_s = smem_addr(rp);
                 double* row = table + (size_t)le * TMAX * 3;
-#define RT(UU) residual_task<UU>(cur_s, cur, prog_s, smem_addr(s_ones), rp, p.factors, npts, lane, row)
+#define RT(UU) residual_task<UU>(cur_s, cur, TP, prog_s, smem_addr(s_ones), rp, p.factors, npts, lane, row)
                 switch (rp->NU) {
                     case 1: RT(1); break;
                     case 2: RT(2); break;
@@ -1603,11 +1608,15 @@ static int launch_gram_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, d
 
 static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double* sums) {
     const int U = (int)g.token_ids.size();
-    const long long n_tiles = (c->N + RES_TILE - 1) / RES_TILE;
+    // tile = 1024 points, one buffer (measured at 512^3, population 128: 1024 single-buffered 127 ms, 1024
+    // double-buffered 136 ms, 2048 single-buffered 205 ms); EPDE_RES_TILE overrides for experiments
+    const size_t per_eq = sizeof(ResidProg) + sizeof(double) * TMAX * 3 + sizeof(int);
+    int tile_pts = RES_TILE_MIN;
+    if (const char* ev = getenv("EPDE_RES_TILE")) { const int v = atoi(ev); if (v == 1024 || v == 2048 || v == 4096) tile_pts = v; }
+    const long long n_tiles = (c->N + tile_pts - 1) / tile_pts;
     const int ne_all = (int)g.eqs.size();
     // equations per launch: their programs and sum table live in shared memory next to the two tile buffers
-    const size_t tile_bytes = sizeof(double) * 2 * (size_t)U * RES_TILE;
-    const size_t per_eq = sizeof(ResidProg) + sizeof(double) * TMAX * 3 + sizeof(int);
+    const size_t tile_bytes = sizeof(double) * (size_t)U * tile_pts;
     if (tile_bytes + per_eq > (size_t)c->max_smem) return fail("pass B tiles need %zu bytes of shared memory", tile_bytes + per_eq);
     const int cap = (int)(((size_t)c->max_smem - tile_bytes) / per_eq);
     const int n_launch = (ne_all + cap - 1) / cap;
@@ -1618,13 +1627,13 @@ static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, 
         ResidParams p;
         memset(&p, 0, sizeof p);
         p.N = c->N; p.eqs = b->d_eqs; p.factors = b->d_factors;
-        p.eq_list = b->d_lists + g.list_off + e0; p.n_eq = ne; p.U = U; p.n_tiles = (int)n_tiles;
+        p.eq_list = b->d_lists + g.list_off + e0; p.n_eq = ne; p.U = U; p.n_tiles = (int)n_tiles; p.tile_pts = tile_pts;
         for (int u = 0; u < U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
         p.slot_eval = b->d_slot_eval; p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.intercept_l1 = b->d_b1;
         const size_t smem = tile_bytes + (size_t)ne * per_eq;
-        // CTAs per SM: shared memory and the 64K-register file (<= 128 registers per thread)
-        const int per_sm = std::max(1, std::min((int)((size_t)(c->max_smem + 1024) / (smem + 1024)), c->resid_warps / nwarps));
-        const int grid = (int)std::min<long long>(n_tiles, (long long)c->sm_count * per_sm);
+        // one persistent CTA per SM: the tile -> CTA assignment (and with it the summation order) depends only on
+        // the grid size, never on what else is in the batch
+        const int grid = (int)std::min<long long>(n_tiles, (long long)c->sm_count);
         if (c->d_partial.ensure(sizeof(double) * (size_t)grid * ne * TMAX * 3)) return 1;
         p.partial = (double*)c->d_partial.ptr;
         {
