@@ -112,7 +112,8 @@ struct UnitDesc {            // one CTA work unit of pass A: a (sub-)cell of the
     int col_lo, ncols;       // columns (last axis) handled, ncols <= TILE_COLS
     int cell;                // (cellA * nB + cellB)
     int piece_lo, npieces;   // pieces (sub-segments of the last axis) covered by the chunk
-    int pad0, pad1, pad2;
+    int wlog;                // >= 0: every piece of the unit is exactly 2^wlog columns wide (shuffle flush); -1: general
+    int pad1, pad2;
 };
 
 struct MargDesc {            // one output row of the segment-Gram table
@@ -201,6 +202,7 @@ struct WarpProg {
     int foff[TMAX + 1];      // generic path: factor ranges
     int2 op2[TMAX];          // byte offsets of slots {E, F}
     int T, fast, n2, n3;
+    long long c_off;         // doubles, into the cell-Gram scratch of the launch group
     unsigned char accmap[TMAX * (TMAX + 3) / 2 + 4];
 };
 
@@ -338,9 +340,28 @@ __device__ __forceinline__ int n2_class(int n2) { return n2 <= 2 ? n2 : 3; }
 template <int T>
 __device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2], int lane, unsigned red, double* out,
                                             int piece_lo, int npieces, int col_lo, const int* __restrict__ piece_start,
-                                            const unsigned char* accmap) {
+                                            const unsigned char* accmap, int wlog) {
     constexpr int NACC = T * (T + 3) / 2;
     constexpr int RS = TILE_COLS + 1;
+    if (wlog >= 0) {
+        // every piece is 2^wlog lanes wide and starts on a multiple of it: butterfly inside the lane groups
+        // (NACC independent chains per step), then the first lane of each group stores its piece
+        double v[NACC];
+#pragma unroll
+        for (int k = 0; k < NACC; ++k) v[k] = acc[k];
+        for (int off = 1; off < (1 << wlog); off <<= 1) {
+#pragma unroll
+            for (int k = 0; k < NACC; ++k) v[k] += __shfl_xor_sync(0xffffffffu, v[k], off);
+        }
+        const int pp = lane >> wlog;
+        if ((lane & ((1 << wlog) - 1)) == 0 && pp < npieces) {
+            double* o = out + (long long)pp * NACC;
+#pragma unroll
+            for (int k = 0; k < NACC; ++k) o[accmap[k]] = v[k];
+        }
+        __syncwarp();
+        return;
+    }
 #pragma unroll
     for (int b0 = 0; b0 < NACC; b0 += RED_CHUNK) {
         const int cnt = (NACC - b0) < RED_CHUNK ? (NACC - b0) : RED_CHUNK;
@@ -366,7 +387,7 @@ __device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2]
 template <int T, int N2, int DEEP, int R>
 __device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, unsigned ops2, unsigned ones, int nrows, int lane, unsigned red,
                                             double* out, int piece_lo, int npieces, int col_lo,
-                                            const int* __restrict__ piece_start, const unsigned char* accmap) {
+                                            const int* __restrict__ piece_start, const unsigned char* accmap, int wlog) {
     constexpr int NACC = T * (T + 3) / 2;
     constexpr int ROWB = TILE_COLS * 8;
     double acc[NACC];
@@ -389,7 +410,7 @@ __device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, unsigne
         fast_terms_r<T, N2, DEEP, 1, ROWB>(off, base + row * ROWB, ones, c);
         gram_accumulate<T>(acc, c[0]);
     }
-    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start, accmap);
+    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start, accmap, wlog);
 }
 
 // generic path: any factor kind / power / factor count
@@ -397,7 +418,7 @@ template <int T>
 __device__ __noinline__ void gram_warp_generic(const double* tile, int tstride, const WarpProg* wp,
                                                const FactorDesc* fac, int nrows, int lane, unsigned red, double* out,
                                                int piece_lo, int npieces, int col_lo,
-                                               const int* __restrict__ piece_start) {
+                                               const int* __restrict__ piece_start, int wlog) {
     constexpr int NACC = T * (T + 3) / 2;
     double acc[NACC];
 #pragma unroll
@@ -410,18 +431,18 @@ __device__ __noinline__ void gram_warp_generic(const double* tile, int tstride, 
             c[t] = eval_term_generic(fac, wp->foff[t], wp->foff[t + 1], base + row * TILE_COLS, tstride);
         gram_accumulate<T>(acc, c);
     }
-    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start, wp->accmap);
+    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start, wp->accmap, wlog);
 }
 
 template <int T>
 __device__ __forceinline__ void gram_warp(const double* tile, int tstride, const WarpProg* wp, const FactorDesc* fac,
                                           unsigned ones, int nrows, int lane, double* red, double* out, int piece_lo,
-                                          int npieces, int col_lo, const int* __restrict__ piece_start) {
+                                          int npieces, int col_lo, const int* __restrict__ piece_start, int wlog) {
     // 8-warp CTAs may use 255 registers per thread: four rows per iteration (two for the widest equations)
     constexpr int R = T <= 6 ? 4 : 2;
     if (wp->fast) {
 #define GWF(NN, DD) gram_warp_fast<T, (NN), (DD), R>(smem_addr(tile), smem_addr(wp->op), smem_addr(wp->op2), ones, nrows, \
-                                                     lane, smem_addr(red), out, piece_lo, npieces, col_lo, piece_start, wp->accmap)
+                                                     lane, smem_addr(red), out, piece_lo, npieces, col_lo, piece_start, wp->accmap, wlog)
 #define GWD(NN) do { if (wp->n3 == 0) GWF(NN, 0); else if (wp->n3 == 1) GWF(NN, 1); else GWF(NN, 2); } while (0)
         switch (n2_class(wp->n2)) {
             case 0: GWF(0, 0); break;
@@ -433,7 +454,7 @@ __device__ __forceinline__ void gram_warp(const double* tile, int tstride, const
 #undef GWF
     } else {
         gram_warp_generic<T>(tile, tstride, wp, fac, nrows, lane, smem_addr(red), out, piece_lo, npieces, col_lo,
-                             piece_start);
+                             piece_start, wlog);
     }
 }
 
@@ -445,50 +466,18 @@ __global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
     __shared__ __align__(16) double s_ones[128];     // 4 rows x 256 bytes of 1.0 (fast_terms_r)
     const int tid = threadIdx.x;
     const int nwarps = blockDim.x >> 5;
-    const UnitDesc u = p.g.units[blockIdx.x];
+    const int warp = tid >> 5, lane = tid & 31;
     for (int q = tid; q < 128; q += blockDim.x) s_ones[q] = 1.0;
-    const int wb = u.b_hi - u.b_lo;
-    const int nrows = (u.a_hi - u.a_lo) * wb;
     const int tstride = p.g.max_rows * TILE_COLS;
     double* tile = smem;                                              // [U][max_rows][32]
     double* red_all = tile + (size_t)p.U * tstride;                   // [nwarps][RED_CHUNK][33]
-    WarpProg* progs = (WarpProg*)(red_all + nwarps * RED_CHUNK * (TILE_COLS + 1));
+    WarpProg* progs = (WarpProg*)(red_all + nwarps * RED_CHUNK * (TILE_COLS + 1));   // [n_eq]
     if (tid < MAXU) s_tok[tid] = p.tok[tid];
-    __syncthreads();
 
-    // ---- stage the tile: 16-byte cp.async where rows are aligned and full, 8-byte / zero fill otherwise
-    {
-        const bool vec = p.g.aligned16 && !(u.col_lo & 1);
-        const int total = p.U * nrows * (TILE_COLS / 2);
-        for (int q = tid; q < total; q += blockDim.x) {
-            const int part = q & (TILE_COLS / 2 - 1);
-            const int rr = q / (TILE_COLS / 2);
-            const int row = rr % nrows, us = rr / nrows;
-            const int ia = u.a_lo + row / wb, ib = u.b_lo + row % wb;
-            const int c0 = part * 2;
-            const double* src = s_tok[us] + ((long long)ia * p.g.strideA + (long long)ib * p.g.strideB + u.col_lo + c0);
-            double* dst = tile + (size_t)us * tstride + row * TILE_COLS + c0;
-            if (vec && c0 + 2 <= u.ncols) {
-                cp_async16(dst, src);
-            } else {
-                if (c0 < u.ncols) cp_async8(dst, src); else dst[0] = 0.0;
-                if (c0 + 1 < u.ncols) cp_async8(dst + 1, src + 1); else dst[1] = 0.0;
-            }
-        }
-        cp_async_wait_all();
-        if (tid == 0) s_next = nwarps;
-        __syncthreads();
-    }
-
-    const int warp = tid >> 5, lane = tid & 31;
-    WarpProg* wp = progs + warp;
-    double* red = red_all + warp * RED_CHUNK * (TILE_COLS + 1);
-    int le = warp;
-    while (le < p.n_eq) {
-        const int e = p.eq_list[le];
-        const EqDesc* eq = p.eqs + e;
-        const int T = eq->T;
-        __syncwarp();
+    // ---- per-equation programs, built once per (persistent) CTA: a task then starts from shared memory only
+    for (int le = warp; le < p.n_eq; le += nwarps) {
+        const EqDesc* eq = p.eqs + p.eq_list[le];
+        WarpProg* wp = progs + le;
         if (lane < TMAX) {
             int4 d = eq->fastop[lane];            // slots -> byte offsets inside the tile
             d.x *= tstride * 8;
@@ -502,24 +491,60 @@ __global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
             wp->op2[lane] = d2;
         }
         if (lane <= TMAX) wp->foff[lane] = eq->fac_off[lane];
-        if (lane == 0) { wp->T = T; wp->fast = eq->fast; wp->n2 = eq->n2; wp->n3 = eq->n3; }
+        if (lane == 0) { wp->T = eq->T; wp->fast = eq->fast; wp->n2 = eq->n2; wp->n3 = eq->n3; wp->c_off = eq->c_off; }
         for (int k = lane; k < TMAX * (TMAX + 3) / 2; k += 32) wp->accmap[k] = eq->accmap[k];
-        __syncwarp();
-        double* out = p.cells + eq->c_off + ((long long)u.cell * p.g.npieces + u.piece_lo) * nacc_of(T);
-#define GW(TT) gram_warp<TT>(tile, tstride, wp, p.factors, smem_addr(s_ones), nrows, lane, red, out, u.piece_lo, u.npieces, u.col_lo, p.g.piece_start)
-        switch (T) {
-            case 1: GW(1); break;
-            case 2: GW(2); break;
-            case 3: GW(3); break;
-            case 4: GW(4); break;
-            case 5: GW(5); break;
-            case 6: GW(6); break;
-            case 7: GW(7); break;
-            default: GW(8); break;
+    }
+    __syncthreads();
+
+    double* red = red_all + warp * RED_CHUNK * (TILE_COLS + 1);
+    for (int ui = blockIdx.x; ui < p.g.n_units; ui += gridDim.x) {
+        const UnitDesc u = p.g.units[ui];
+        const int wb = u.b_hi - u.b_lo;
+        const int nrows = (u.a_hi - u.a_lo) * wb;
+        // ---- stage the tile: 16-byte cp.async where rows are aligned and full, 8-byte / zero fill otherwise
+        {
+            const bool vec = p.g.aligned16 && !(u.col_lo & 1);
+            const int total = p.U * nrows * (TILE_COLS / 2);
+            for (int q = tid; q < total; q += blockDim.x) {
+                const int part = q & (TILE_COLS / 2 - 1);
+                const int rr = q / (TILE_COLS / 2);
+                const int row = rr % nrows, us = rr / nrows;
+                const int ia = u.a_lo + row / wb, ib = u.b_lo + row % wb;
+                const int c0 = part * 2;
+                const double* src = s_tok[us] + ((long long)ia * p.g.strideA + (long long)ib * p.g.strideB + u.col_lo + c0);
+                double* dst = tile + (size_t)us * tstride + row * TILE_COLS + c0;
+                if (vec && c0 + 2 <= u.ncols) {
+                    cp_async16(dst, src);
+                } else {
+                    if (c0 < u.ncols) cp_async8(dst, src); else dst[0] = 0.0;
+                    if (c0 + 1 < u.ncols) cp_async8(dst + 1, src + 1); else dst[1] = 0.0;
+                }
+            }
+            cp_async_wait_all();
+            if (tid == 0) s_next = nwarps;
+            __syncthreads();
         }
+        int le = warp;
+        while (le < p.n_eq) {
+            const WarpProg* wp = progs + le;
+            const int T = wp->T;
+            double* out = p.cells + wp->c_off + ((long long)u.cell * p.g.npieces + u.piece_lo) * nacc_of(T);
+#define GW(TT) gram_warp<TT>(tile, tstride, wp, p.factors, smem_addr(s_ones), nrows, lane, red, out, u.piece_lo, u.npieces, u.col_lo, p.g.piece_start, u.wlog)
+            switch (T) {
+                case 1: GW(1); break;
+                case 2: GW(2); break;
+                case 3: GW(3); break;
+                case 4: GW(4); break;
+                case 5: GW(5); break;
+                case 6: GW(6); break;
+                case 7: GW(7); break;
+                default: GW(8); break;
+            }
 #undef GW
-        if (lane == 0) le = atomicAdd(&s_next, 1);
-        le = __shfl_sync(0xffffffffu, le, 0);
+            if (lane == 0) le = atomicAdd(&s_next, 1);
+            le = __shfl_sync(0xffffffffu, le, 0);
+        }
+        __syncthreads();            // everyone is done with the tile before it is refilled
     }
 }
 
@@ -1466,6 +1491,13 @@ static int build_geometry(epde_ctx* c) {
                 u.col_lo = ch.col_lo; u.ncols = ch.ncols;
                 u.cell = a * nB + b;
                 u.piece_lo = ch.p_lo; u.npieces = ch.np;
+                u.wlog = -1;
+                for (int wl = 0; wl <= 5 && u.wlog < 0; ++wl) {
+                    bool ok = true;
+                    for (int q = 0; q < ch.np && ok; ++q)
+                        ok = (piece_start[ch.p_lo + q + 1] - piece_start[ch.p_lo + q]) == (1 << wl);
+                    if (ok) u.wlog = wl;
+                }
                 units.push_back(u);
             }
         }
@@ -1579,9 +1611,9 @@ struct epde_batch {
     bool solved = false;
 };
 
-static size_t gram_smem_bytes(const epde_ctx* c, int U, int nwarps) {
+static size_t gram_smem_bytes(const epde_ctx* c, int U, int nwarps, int n_eq) {
     return sizeof(double) * ((size_t)U * c->geom.max_rows * TILE_COLS + (size_t)nwarps * RED_CHUNK * (TILE_COLS + 1)) +
-           (size_t)nwarps * sizeof(WarpProg);
+           (size_t)n_eq * sizeof(WarpProg);
 }
 
 static int launch_gram_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double* cells) {
@@ -1592,17 +1624,27 @@ static int launch_gram_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, d
     p.U = (int)g.token_ids.size();
     for (int u = 0; u < p.U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
     p.cells = cells;
-    // 8 warps x <= 255 registers (two rows per decode for every T) or 16 warps x <= 128 registers
-    int nw_cfg = c->gram_warps;
-    int nwarps = std::max(1, std::min(nw_cfg, p.n_eq));
-    const size_t smem = gram_smem_bytes(c, p.U, nwarps);
-    if (smem > (size_t)c->max_smem)
-        return fail("pass A tile needs %zu bytes of shared memory (> %d)", smem, c->max_smem);
-    {
-        KernelSpan ks(c, EPDE_KERNEL_GRAM);
-        gram_tile_kernel<GRAM_WARPS><<<(unsigned)c->geom.n_units, nwarps * 32, smem, c->stream>>>(p);
+    // persistent CTAs (one per SM) walk over the units; the programs of the launch's equations live in shared
+    // memory next to the tile, so a group whose programs do not fit is split into several launches
+    const int ne_all = (int)g.eqs.size();
+    const size_t fixed = gram_smem_bytes(c, p.U, c->gram_warps, 0);
+    if (fixed + sizeof(WarpProg) > (size_t)c->max_smem)
+        return fail("pass A tile needs %zu bytes of shared memory (> %d)", fixed + sizeof(WarpProg), c->max_smem);
+    const int cap = (int)(((size_t)c->max_smem - fixed) / sizeof(WarpProg));
+    const int n_launch = (ne_all + cap - 1) / cap;
+    const int per_launch = (ne_all + n_launch - 1) / n_launch;
+    for (int e0 = 0; e0 < ne_all; e0 += per_launch) {
+        p.eq_list = b->d_lists + g.list_off + e0;
+        p.n_eq = std::min(per_launch, ne_all - e0);
+        const int nwarps = std::max(1, std::min(c->gram_warps, p.n_eq));
+        const size_t smem = gram_smem_bytes(c, p.U, nwarps, p.n_eq);
+        const unsigned grid = (unsigned)std::min(c->geom.n_units, c->sm_count);
+        {
+            KernelSpan ks(c, EPDE_KERNEL_GRAM);
+            gram_tile_kernel<GRAM_WARPS><<<grid, nwarps * 32, smem, c->stream>>>(p);
+        }
+        CK(cudaGetLastError());
     }
-    CK(cudaGetLastError());
     return 0;
 }
 
