@@ -333,8 +333,16 @@ __device__ __forceinline__ void fast_terms_r(const TermOffsets<T, N2, DEEP>& o, 
     }
 }
 
-// class of a two-factor count: the smallest of {0, 1, 2, T} that is >= n2, as an index 0..3
-__device__ __forceinline__ int n2_class(int n2) { return n2 <= 2 ? n2 : 3; }
+// class of a two-factor count: the smallest of {0, 1, 2, T} that is >= n2, as an index 0..3.
+// coarse (pass B): N2 in {0, 2, T} and DEPTH in {0, 2} only -- half the code variants, so fewer instruction-cache
+// misses when the warps of a CTA run different equations, at the price of a few more multiplies by 1.0
+// (measured at 512^3: pass B 128 -> 122 ms; pass A, which is shared-memory-bandwidth bound, 53 -> 58 ms, so
+// pass A keeps the fine classes)
+#define COARSE_CLASSES_B 1
+__device__ __forceinline__ int n2_class(int n2, bool coarse) {
+    if (coarse) return n2 == 0 ? 0 : (n2 <= 2 ? 2 : 3);
+    return n2 <= 2 ? n2 : 3;
+}
 
 // flush: sum the lanes (columns) of every piece, RED_CHUNK Gram entries per round
 template <int T>
@@ -444,7 +452,7 @@ __device__ __forceinline__ void gram_warp(const double* tile, int tstride, const
 #define GWF(NN, DD) gram_warp_fast<T, (NN), (DD), R>(smem_addr(tile), smem_addr(wp->op), smem_addr(wp->op2), ones, nrows, \
                                                      lane, smem_addr(red), out, piece_lo, npieces, col_lo, piece_start, wp->accmap, wlog)
 #define GWD(NN) do { if (wp->n3 == 0) GWF(NN, 0); else if (wp->n3 == 1) GWF(NN, 1); else GWF(NN, 2); } while (0)
-        switch (n2_class(wp->n2)) {
+        switch (n2_class(wp->n2, false)) {
             case 0: GWF(0, 0); break;
             case 1: GWD(1); break;
             case 2: if (T >= 2) { GWD(T >= 2 ? 2 : T); break; }
@@ -1101,10 +1109,16 @@ __device__ __forceinline__ void residual_task(unsigned tile, const double* tile_
                                               double* table_row) {
     if (rp->fast) {
 #define RTF(NN, DD) residual_task_fast<NU, (NN), (DD)>(tile, prog, ones, rp, rp->NV, npts, lane, table_row)
+#if COARSE_CLASSES_B
+#define RTD(NN) do { if (rp->n3 == 0) RTF(NN, 0); else RTF(NN, 2); } while (0)
+#else
 #define RTD(NN) do { if (rp->n3 == 0) RTF(NN, 0); else if (rp->n3 == 1) RTF(NN, 1); else RTF(NN, 2); } while (0)
-        switch (n2_class(rp->n2)) {
+#endif
+        switch (n2_class(rp->n2, COARSE_CLASSES_B)) {
             case 0: RTF(0, 0); break;
+#if !COARSE_CLASSES_B
             case 1: RTD(1); break;
+#endif
             case 2: if (NU >= 2) { RTD(NU >= 2 ? 2 : NU); break; }
             default: RTD(NU); break;
         }
@@ -1216,7 +1230,7 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
         auto key_of = [&](int le) {
             const ResidProg* rp = progs + le;
             if (rp->NV == 0) return -1;
-            return (rp->NU << 8) | (n2_class(rp->n2) << 4) | (rp->n3 << 2) | (rp->fast ? 0 : 2);
+            return (rp->NU << 8) | (n2_class(rp->n2, COARSE_CLASSES_B) << 4) | ((COARSE_CLASSES_B ? (rp->n3 > 0 ? 2 : 0) : rp->n3) << 2) | (rp->fast ? 0 : 2);
         };
         for (int le = tid; le < p.n_eq; le += blockDim.x) {
             const int k = key_of(le);
