@@ -47,6 +47,9 @@ def parse_args():
     ap.add_argument('--seed', type=int, default=5)
     ap.add_argument('--cpu-seconds', type=float, default=20.0, help='budget of the cpu_baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--norms', default='l1', choices=['l1', 'both'],
+                    help="residual norms of pass B: 'l1' = the unit of SURVEY 8d (LASSO + L1 fitness + stability, the "
+                         "MOEADD path); 'both' also accumulates L2Fitness' sum of squares")
     return ap.parse_args()
 
 
@@ -249,6 +252,8 @@ def workload_config(args, shape, eqs, evals, world):
                          ('population round-robin, no collective' if world > 1 else 'single GPU')),
             'l2_policy': 'token set larger than L2' if int(np.prod(shape)) * 8 * 3 > 126e6 else
                          'L2 flushed (256 MB write) between timed steps',
+            'norms': 'L1 fitness + stability (L2LRFitness, the unit of SURVEY 8d)' if getattr(args, 'norms', 'l1') == 'l1'
+                     else 'L1 + L2 fitness + stability',
             'seed': args.seed}
 
 
@@ -307,6 +312,8 @@ def run_b200(args):
 
     # ---- device-resident step: encoding already on the device, results stay on the device
     batch = eng.batch(enc)
+    want_l2 = args.norms == 'both'
+    batch.set_norms(want_l2)
     seg = torch.zeros(batch.gram_size, dtype=torch.float64, device=dev)
     sums = torch.zeros(batch.residual_size, dtype=torch.float64, device=dev)
 
@@ -359,8 +366,8 @@ def run_b200(args):
     # ---- end to end through the host API: host encodings in, host results out, every step
     def e2e_step():
         if grid_sharded:
-            return sharding.evaluate_grid_sharded(eng, enc, seg, sums, want_sw=False)
-        return eng.evaluate(enc, want_sw=False)
+            return sharding.evaluate_grid_sharded(eng, enc, seg, sums, want_sw=False, want_l2=want_l2)
+        return eng.evaluate(enc, want_sw=False, want_l2=want_l2)
 
     def timed_wall(step_fn, k):
         barrier()

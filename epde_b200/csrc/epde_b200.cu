@@ -933,6 +933,10 @@ struct ResidParams {
     const double* intercept; // [n_eval]
     const double* intercept_l1;  // [n_eval]
     double* partial;         // [gridDim.x][n_eq][TMAX][3]
+    struct ResidProg* progs; // global: [n_eq] sorted programs, then [n_eq] staging (residual_prog_kernel)
+    int seg_eqs;             // programs per segment (shared-memory resident)
+    int batch_tiles;         // tiles a CTA walks per segment before moving to the next segment
+    int nbuf;                // 1 or 2 tile buffers
 };
 
 // Per-equation residual program in shared memory (16-byte aligned), COMPACTED: only the NU terms
@@ -948,9 +952,11 @@ struct ResidProg {
     int dmap[TMAX];          // compact eval dd -> target term d (row of the sum table)
     int tcol[TMAX];          // compact eval dd -> used column of its target
     int NU, NV, fast, n2;    // n2: used columns with >= 2 slot factors (they come first)
-    int n3, pad0, pad1, pad2;  // n3: depth over the used columns: 0 (<= 2 slot factors), 1 (<= 4), 2 (<= 6)
+    int n3, le, pad1, pad2;    // n3: depth over the used columns: 0 (<= 2 slot factors), 1 (<= 4), 2 (<= 6); le: list position
     int2 op2[TMAX];            // byte offsets of slots {E, F}
 };
+
+static_assert(sizeof(ResidProg) % 16 == 0, "ResidProg is copied in 16-byte pieces");
 
 template <int NU>
 __device__ __forceinline__ void residual_point_block(const double (&c)[NU], int NV, unsigned m_a, unsigned sb_a,
@@ -971,7 +977,7 @@ __device__ __forceinline__ void residual_point_block(const double (&c)[NU], int 
 }
 
 // R points per decode: same arithmetic, weights fetched once for the R points
-template <int NU, int R>
+template <int NU, int R, bool L2>
 __device__ __forceinline__ void residual_points(const double (&c)[R][NU], int NV, unsigned m_a, unsigned sb_a,
                                                 unsigned sdb_a, double (&a1)[NU], double (&a3)[NU], double (&sabs)[NU]) {
 #pragma unroll
@@ -998,6 +1004,12 @@ __device__ __forceinline__ void residual_points(const double (&c)[R][NU], int NV
 #pragma unroll
                 for (int r = 0; r < R; ++r) rr[r] = fma(w, c[r][u], rr[r]);
             }
+            if (!L2) {      // L1 norms only (L2LRFitness, fitness.py:142): no sum of squares
+                if (R == 4) a1[dd] += (fabs(rr[0]) + fabs(rr[1])) + (fabs(rr[2]) + fabs(rr[3]));
+                else if (R == 2) a1[dd] += fabs(rr[0]) + fabs(rr[1]);
+                else a1[dd] += fabs(rr[0]);
+                continue;
+            }
             const double db = lds_f64(sdb_a + dd * 8);        // L2Fitness keeps the LASSO intercept (fitness.py:80)
             // pairwise (fixed order) instead of a serial chain: the R points are independent
             double q[R];
@@ -1020,7 +1032,7 @@ __device__ __forceinline__ void residual_points(const double (&c)[R][NU], int NV
     }
 }
 
-template <int NU>
+template <int NU, bool L2>
 __device__ __forceinline__ void residual_reduce(const double (&a1)[NU], const double (&a3)[NU], const double (&sabs)[NU],
                                                 const ResidProg* rp, int NV, int lane, double* table_row) {
     double t_abs[NU];
@@ -1038,7 +1050,7 @@ __device__ __forceinline__ void residual_reduce(const double (&a1)[NU], const do
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) {
                 v1 += __shfl_xor_sync(0xffffffffu, v1, off);
-                v3 += __shfl_xor_sync(0xffffffffu, v3, off);
+                if (L2) v3 += __shfl_xor_sync(0xffffffffu, v3, off);
             }
             if (lane == 0) {
                 const int d = rp->dmap[dd], tc = rp->tcol[dd];
@@ -1054,7 +1066,7 @@ __device__ __forceinline__ void residual_reduce(const double (&a1)[NU], const do
 }
 
 // one (tile, equation) task, fast terms; returns through the shared table row
-template <int NU, int N2, int DEEP>
+template <int NU, int N2, int DEEP, bool L2>
 __device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, unsigned ones, const ResidProg* rp, int NV,
                                                 int npts, int lane, double* table_row) {
     constexpr int R = (NU <= 6) ? 4 : 2;
@@ -1071,18 +1083,18 @@ __device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, un
     for (; i < nfull; i += 32 * R) {
         double c[R][NU];
         fast_terms_r<NU, N2, DEEP, R, 256>(off, tile + i * 8, ones, c);
-        residual_points<NU, R>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
+        residual_points<NU, R, L2>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
     }
     for (; i < npts; i += 32) {
         double c[1][NU];
         fast_terms_r<NU, N2, DEEP, 1, 256>(off, tile + i * 8, ones, c);
-        residual_points<NU, 1>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
+        residual_points<NU, 1, L2>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
     }
-    residual_reduce<NU>(a1, a3, sabs, rp, NV, lane, table_row);
+    residual_reduce<NU, L2>(a1, a3, sabs, rp, NV, lane, table_row);
 }
 
 // same, generic terms (any kind / power / factor count)
-template <int NU>
+template <int NU, bool L2>
 __device__ __noinline__ void residual_task_generic(const double* tile_g, int tile_pts, unsigned prog, const ResidProg* rp,
                                                    const FactorDesc* fac, int NV, int npts, int lane, double* table_row) {
     const unsigned m_a = prog + (unsigned)offsetof(ResidProg, m);
@@ -1098,17 +1110,17 @@ __device__ __noinline__ void residual_task_generic(const double* tile_g, int til
             const int t = rp->term[u];
             c[0][u] = eval_term_generic(fac, rp->foff[t], rp->foff[t + 1], tile_g + i, tile_pts);
         }
-        residual_points<NU, 1>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
+        residual_points<NU, 1, L2>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
     }
-    residual_reduce<NU>(a1, a3, sabs, rp, NV, lane, table_row);
+    residual_reduce<NU, L2>(a1, a3, sabs, rp, NV, lane, table_row);
 }
 
-template <int NU>
+template <int NU, bool L2>
 __device__ __forceinline__ void residual_task(unsigned tile, const double* tile_g, int tile_pts, unsigned prog, unsigned ones,
                                               const ResidProg* rp, const FactorDesc* fac, int npts, int lane,
                                               double* table_row) {
     if (rp->fast) {
-#define RTF(NN, DD) residual_task_fast<NU, (NN), (DD)>(tile, prog, ones, rp, rp->NV, npts, lane, table_row)
+#define RTF(NN, DD) residual_task_fast<NU, (NN), (DD), L2>(tile, prog, ones, rp, rp->NV, npts, lane, table_row)
 #if COARSE_CLASSES_B
 #define RTD(NN) do { if (rp->n3 == 0) RTF(NN, 0); else RTF(NN, 2); } while (0)
 #else
@@ -1125,33 +1137,23 @@ __device__ __forceinline__ void residual_task(unsigned tile, const double* tile_
 #undef RTD
 #undef RTF
     } else {
-        residual_task_generic<NU>(tile_g, tile_pts, prog, rp, fac, rp->NV, npts, lane, table_row);
+        residual_task_generic<NU, L2>(tile_g, tile_pts, prog, rp, fac, rp->NV, npts, lane, table_row);
     }
 }
 
-template <int NW>
-__global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p) {
-    extern __shared__ __align__(16) double smem[];
-    __shared__ const double* s_tok[MAXU];
-    __shared__ int s_next;
-    __shared__ __align__(16) double s_ones[128];     // 4 rows x 256 bytes of 1.0 (fast_terms_r)
+// program kernel (one CTA): builds the residual program of every equation of the launch from the solve outputs and
+// stores them in global memory SORTED by code variant (heaviest first), so that a segment of consecutive programs
+// runs (almost) one code variant with tasks of similar length.
+__global__ void __launch_bounds__(256) residual_prog_kernel(ResidParams p) {
+    extern __shared__ int s_key[];                    // [n_eq]
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    for (int q = tid; q < 128; q += blockDim.x) s_ones[q] = 1.0;
     const int nwarps = blockDim.x >> 5;
-    double* buf0 = smem;                                         // [U][tile_pts]
     const int TP = p.tile_pts;
-    const size_t buf_doubles = (size_t)p.U * TP;
-    ResidProg* progs = (ResidProg*)(smem + buf_doubles);         // [n_eq]
-    double* table = (double*)(progs + p.n_eq);                   // [n_eq][TMAX][3]
-    int* order = (int*)(table + (size_t)p.n_eq * TMAX * 3);      // [n_eq] task order: same code variant adjacent
-    if (tid < MAXU) s_tok[tid] = p.tok[tid];
-    for (int q = tid; q < p.n_eq * TMAX * 3; q += blockDim.x) table[q] = 0.0;
-
-    // ---- build the programs: warp w builds equations w, w + nwarps, ...
+    ResidProg* tmp = p.progs + p.n_eq;                // unsorted staging area behind the sorted programs
     for (int le = warp; le < p.n_eq; le += nwarps) {
         const int e = p.eq_list[le];
         const EqDesc* eq = p.eqs + e;
-        ResidProg* rp = progs + le;
+        ResidProg* rp = tmp + le;
         const int T = eq->T;
         // lane d < T holds the eval id of target d
         const int my_ev = (lane < T) ? p.slot_eval[e * TMAX + lane] : -1;
@@ -1170,7 +1172,7 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
 #pragma unroll
         for (int d = 0; d < 4; ++d) used |= ((nz[0] >> (d * 8)) & 0xffu) | ((nz[1] >> (d * 8)) & 0xffu);
         const int NU = __popc(used), NV = __popc(valid);
-        // used columns in evaluation order (two-factor terms first): rank of this lane's term
+        // used columns in evaluation order (most slot factors first): rank of this lane's term
         int my_u = 0;
         {
             const int my_pos = (lane < T) ? eq->pos[lane] : 0;
@@ -1178,37 +1180,39 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
                 if ((used >> t2 & 1u) && eq->pos[t2] < my_pos) ++my_u;
         }
         const int4 my_op = (lane < T) ? eq->fastop[eq->pos[lane]] : make_int4(0, -1, -1, -1);
-        const unsigned two = __ballot_sync(0xffffffffu, lane < T && (used >> lane & 1u) && my_op.z >= 0);
         const int2 my_op2 = (lane < T) ? eq->fastop2[eq->pos[lane]] : make_int2(-1, -1);
-        const unsigned three = __ballot_sync(0xffffffffu, lane < T && (used >> lane & 1u) && my_op.y >= 0);
-        const unsigned five = __ballot_sync(0xffffffffu, lane < T && (used >> lane & 1u) && my_op2.x >= 0);
+        const bool mine = lane < T && (used >> lane & 1u);
+        const unsigned two = __ballot_sync(0xffffffffu, mine && my_op.z >= 0);
+        const unsigned three = __ballot_sync(0xffffffffu, mine && my_op.y >= 0);
+        const unsigned five = __ballot_sync(0xffffffffu, mine && my_op2.x >= 0);
         for (int q = lane; q < TMAX * TMAX; q += 32) rp->m[q] = 0.0;
-        if (lane < TMAX) { rp->op[lane] = make_int4(0, -1, -1, -1); rp->op2[lane] = make_int2(-1, -1); rp->sb[lane] = 0.0; rp->sdb[lane] = 0.0; rp->term[lane] = 0; rp->dmap[lane] = 0; rp->tcol[lane] = 0; }
+        if (lane < TMAX) {
+            rp->op[lane] = make_int4(0, -1, -1, -1); rp->op2[lane] = make_int2(-1, -1);
+            rp->sb[lane] = 0.0; rp->sdb[lane] = 0.0; rp->term[lane] = 0; rp->dmap[lane] = 0; rp->tcol[lane] = 0;
+        }
         __syncwarp();
-        if (lane < T && (used >> lane & 1u)) {
-            const int u = my_u;
+        if (mine) {
             int4 d = my_op;
             d.x *= TP * 8;
             if (d.y >= 0) d.y *= TP * 8;
             if (d.z >= 0) d.z *= TP * 8;
             if (d.w >= 0) d.w *= TP * 8;
-            rp->op[u] = d;
+            rp->op[my_u] = d;
             int2 d2 = my_op2;
             if (d2.x >= 0) d2.x *= TP * 8;
             if (d2.y >= 0) d2.y *= TP * 8;
-            rp->op2[u] = d2;
-            rp->term[u] = lane;
+            rp->op2[my_u] = d2;
+            rp->term[my_u] = lane;
         }
         if (lane <= TMAX) rp->foff[lane] = eq->fac_off[lane];
         if (my_ev >= 0) {
             const int dd = __popc(valid & ((1u << lane) - 1u));
-            const int tc = my_u;
             const double b1 = p.intercept_l1[my_ev];
             rp->sb[dd] = b1;
             rp->sdb[dd] = b1 - p.intercept[my_ev];
             rp->dmap[dd] = lane;
-            rp->tcol[dd] = tc;
-            rp->m[dd * TMAX + tc] = 1.0;
+            rp->tcol[dd] = my_u;
+            rp->m[dd * TMAX + my_u] = 1.0;
         }
         __syncwarp();
 #pragma unroll
@@ -1221,75 +1225,137 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
                 rp->m[dd * TMAX + uj] = -wv[h];
             }
         }
-        if (lane == 0) { rp->NU = NU; rp->NV = NV; rp->fast = eq->fast; rp->n2 = __popc(two); rp->n3 = five ? 2 : (three ? 1 : 0); }
-    }
-    __syncthreads();
-    // ---- task order: heaviest first, equations that run the same code variant (NU, factor class) next to each
-    //      other, so the warps of the CTA execute the same instructions at the same time (instruction cache)
-    {
-        auto key_of = [&](int le) {
-            const ResidProg* rp = progs + le;
-            if (rp->NV == 0) return -1;
-            return (rp->NU << 8) | (n2_class(rp->n2, COARSE_CLASSES_B) << 4) | ((COARSE_CLASSES_B ? (rp->n3 > 0 ? 2 : 0) : rp->n3) << 2) | (rp->fast ? 0 : 2);
-        };
-        for (int le = tid; le < p.n_eq; le += blockDim.x) {
-            const int k = key_of(le);
-            int rank = 0;
-            for (int j = 0; j < p.n_eq; ++j) {
-                const int kj = key_of(j);
-                rank += (kj > k || (kj == k && j < le)) ? 1 : 0;
-            }
-            order[rank] = le;
+        if (lane == 0) {
+            const int n2 = __popc(two), n3 = five ? 2 : (three ? 1 : 0);
+            rp->NU = NU; rp->NV = NV; rp->fast = eq->fast; rp->n2 = n2; rp->n3 = n3; rp->le = le;
+            s_key[le] = (NV == 0) ? -1
+                                  : ((NU << 12) | (n2_class(n2, COARSE_CLASSES_B) << 9) |
+                                     ((COARSE_CLASSES_B ? (n3 > 0 ? 2 : 0) : n3) << 7) | ((eq->fast ? 0 : 1) << 6) | (NV << 2));
         }
     }
+    __syncthreads();
+    __threadfence_block();
+    // rank sort (keys descending, ties by list position), then copy every program to its sorted place
+    for (int le = warp; le < p.n_eq; le += nwarps) {
+        const int k = s_key[le];
+        int cnt = 0;
+        for (int j = lane; j < p.n_eq; j += 32) {
+            const int kj = s_key[j];
+            cnt += (kj > k || (kj == k && j < le)) ? 1 : 0;
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+        const int4* src = (const int4*)(tmp + le);
+        int4* dst = (int4*)(p.progs + cnt);
+        for (int q = lane; q < (int)(sizeof(ResidProg) / 16); q += 32) dst[q] = src[q];
+    }
+}
+
+// main kernel.  Persistent CTAs (one per SM) own a fixed set of tiles (tile b, b + grid, ...), taken in batches of
+// `batch_tiles`.  For every batch the CTA walks the sorted program list segment by segment (`seg_eqs` programs,
+// copied from global memory into shared memory), and for every segment over the tiles of the batch (double
+// buffered cp.async; the re-reads of a batch come from L2): all warps of the CTA therefore execute one code
+// variant on tasks of similar length for batch_tiles tiles in a row -- measured 1.5x faster per task than mixing
+// all variants on every tile (instruction cache, tail of the slowest warp).  Per equation the tiles are still
+// accumulated in increasing order into the CTA's shared table, so the sums do not depend on the segmenting.
+template <int NW, bool L2>
+__global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p) {
+    extern __shared__ __align__(16) double smem[];
+    __shared__ const double* s_tok[MAXU];
+    __shared__ int s_next;
+    __shared__ __align__(16) double s_ones[128];     // 4 rows x 256 bytes of 1.0 (fast_terms_r)
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int q = tid; q < 128; q += blockDim.x) s_ones[q] = 1.0;
+    const int nwarps = blockDim.x >> 5;
+    const int TP = p.tile_pts;
+    const size_t buf_doubles = (size_t)p.U * TP;
+    double* buf0 = smem;                                                       // [nbuf][U][tile_pts]
+    ResidProg* progs = (ResidProg*)(smem + (size_t)p.nbuf * buf_doubles);      // [seg_eqs]
+    double* table = (double*)(progs + p.seg_eqs);                              // [n_eq][TMAX][3]
+    if (tid < MAXU) s_tok[tid] = p.tok[tid];
+    for (int q = tid; q < p.n_eq * TMAX * 3; q += blockDim.x) table[q] = 0.0;
     __syncthreads();
 
-    // ---- walk over the tiles.  One buffer: the fill of a tile (a few microseconds from L2 / HBM) is short next to
-    //      the ~100 equation tasks computed on it, and the larger tile halves the per-task overheads.
-    for (int tI = blockIdx.x; tI < p.n_tiles; tI += gridDim.x) {
-        double* cur = buf0;
+    auto issue = [&](int tI, double* dst_buf) {
         const long long start = (long long)tI * TP;
         const int npts = (int)((p.N - start) < TP ? (p.N - start) : TP);
-        {
-            const int half = TP / 2;
-            const int total = p.U * half;
-            for (int q = tid; q < total; q += blockDim.x) {
-                const int us = q / half, part = q - us * half;
-                const int c0 = part * 2;
-                const double* src = s_tok[us] + start + c0;
-                double* dst = cur + (size_t)us * TP + c0;
-                if (c0 + 2 <= npts) cp_async16(dst, src);
-                else if (c0 < npts) cp_async8(dst, src);
-            }
-            cp_async_wait_all();
+        const int half = TP / 2;
+        const int total = p.U * half;
+        for (int q = tid; q < total; q += blockDim.x) {
+            const int us = q / half, part = q - us * half;
+            const int c0 = part * 2;
+            const double* src = s_tok[us] + start + c0;
+            double* dst = dst_buf + (size_t)us * TP + c0;
+            if (c0 + 2 <= npts) cp_async16(dst, src);
+            else if (c0 < npts) cp_async8(dst, src);
         }
-        if (tid == 0) s_next = nwarps;
-        __syncthreads();
-        const unsigned cur_s = smem_addr(cur);
-        int ti = warp;
-        while (ti < p.n_eq) {
-            const int le = order[ti];
-            const ResidProg* rp = progs + le;
-            if (rp->NV > 0) {
-                const unsigned prog_s = smem_addr(rp);
-                double* row = table + (size_t)le * TMAX * 3;
-#define RT(UU) residual_task<UU>(cur_s, cur, TP, prog_s, smem_addr(s_ones), rp, p.factors, npts, lane, row)
-                switch (rp->NU) {
-                    case 1: RT(1); break;
-                    case 2: RT(2); break;
-                    case 3: RT(3); break;
-                    case 4: RT(4); break;
-                    case 5: RT(5); break;
-                    case 6: RT(6); break;
-                    case 7: RT(7); break;
-                    default: RT(8); break;
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+
+    const int n_seg = (p.n_eq + p.seg_eqs - 1) / p.seg_eqs;
+    const int my_tiles = (p.n_tiles > (int)blockIdx.x) ? (p.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    int k_buf = 0;                      // buffer that receives / holds the current tile
+    for (int t0 = 0; t0 < my_tiles; t0 += p.batch_tiles) {
+        const int nb = (my_tiles - t0) < p.batch_tiles ? (my_tiles - t0) : p.batch_tiles;
+        for (int sg = 0; sg < n_seg; ++sg) {
+            const int e0 = sg * p.seg_eqs;
+            const int ne = (p.n_eq - e0) < p.seg_eqs ? (p.n_eq - e0) : p.seg_eqs;
+            // ---- the segment's programs: global (sorted) -> shared; with one buffer the first tile goes along
+            {
+                const int4* src = (const int4*)(p.progs + e0);
+                int4* dst = (int4*)progs;
+                const int n16 = ne * (int)(sizeof(ResidProg) / 16);
+                for (int q = tid; q < n16; q += blockDim.x) cp_async16(dst + q, src + q);
+                // first tile of the (batch, segment) walk; with two buffers the previous walk may have prefetched it
+                if (p.nbuf == 1 || (t0 == 0 && sg == 0)) issue((int)blockIdx.x + t0 * (int)gridDim.x, buf0 + (size_t)k_buf * buf_doubles);
+                else asm volatile("cp.async.commit_group;\n" ::: "memory");
+            }
+            for (int k = 0; k < nb; ++k) {
+                double* cur = buf0 + (size_t)k_buf * buf_doubles;
+                const int tI = (int)blockIdx.x + (t0 + k) * (int)gridDim.x;
+                // ---- prefetch the next tile of the walk into the other buffer
+                int nxt = -1;
+                if (k + 1 < nb) nxt = tI + (int)gridDim.x;
+                else if (sg + 1 < n_seg) nxt = (int)blockIdx.x + t0 * (int)gridDim.x;
+                else if (t0 + nb < my_tiles) nxt = (int)blockIdx.x + (t0 + nb) * (int)gridDim.x;
+                if (p.nbuf == 2 && nxt >= 0) {
+                    issue(nxt, buf0 + (size_t)(k_buf ^ 1) * buf_doubles);
+                    asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+                } else {
+                    if (p.nbuf == 1 && k > 0) issue(tI, cur);
+                    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
                 }
+                if (tid == 0) s_next = nwarps;
+                __syncthreads();
+                const long long start = (long long)tI * TP;
+                const int npts = (int)((p.N - start) < TP ? (p.N - start) : TP);
+                const unsigned cur_s = smem_addr(cur);
+                int ti = warp;
+                while (ti < ne) {
+                    const ResidProg* rp = progs + ti;
+                    if (rp->NV > 0) {
+                        const unsigned prog_s = smem_addr(rp);
+                        double* row = table + (size_t)rp->le * TMAX * 3;
+#define RT(UU) residual_task<UU, L2>(cur_s, cur, TP, prog_s, smem_addr(s_ones), rp, p.factors, npts, lane, row)
+                        switch (rp->NU) {
+                            case 1: RT(1); break;
+                            case 2: RT(2); break;
+                            case 3: RT(3); break;
+                            case 4: RT(4); break;
+                            case 5: RT(5); break;
+                            case 6: RT(6); break;
+                            case 7: RT(7); break;
+                            default: RT(8); break;
+                        }
 #undef RT
+                    }
+                    if (lane == 0) ti = atomicAdd(&s_next, 1);
+                    ti = __shfl_sync(0xffffffffu, ti, 0);
+                }
+                __syncthreads();            // everyone is done with `cur` (and, at k = nb - 1, with the programs)
+                if (p.nbuf == 2) k_buf ^= 1;
             }
-            if (lane == 0) ti = atomicAdd(&s_next, 1);
-            ti = __shfl_sync(0xffffffffu, ti, 0);
         }
-        __syncthreads();            // everyone is done with `cur` before it is refilled
     }
     double* out = p.partial + (size_t)blockIdx.x * p.n_eq * TMAX * 3;
     for (int q = tid; q < p.n_eq * TMAX * 3; q += blockDim.x) out[q] = table[q];
@@ -1393,7 +1459,7 @@ struct epde_ctx {
     Geom geom;
     int n_cells = 0;             // nA * nB * npieces
     DevBuf d_geom;               // packed geometry tables
-    DevBuf d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given;
+    DevBuf d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given, d_progs;
     void* h_pinned = nullptr; size_t h_pinned_cap = 0;
     epde_batch* live = nullptr;
     long long launches = 0;
@@ -1623,6 +1689,7 @@ struct epde_batch {
     long long seg_doubles = 0, win_doubles = 0;
     int* d_mode = nullptr; double* d_given_w = nullptr; double* d_given_b = nullptr;
     bool solved = false;
+    bool want_l2 = true;       // epde_batch_set_norms
 };
 
 static size_t gram_smem_bytes(const epde_ctx* c, int U, int nwarps, int n_eq) {
@@ -1664,29 +1731,38 @@ static int launch_gram_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, d
 
 static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double* sums) {
     const int U = (int)g.token_ids.size();
-    // tile = 1024 points, one buffer (measured at 512^3, population 128: 1024 single-buffered 127 ms, 1024
-    // double-buffered 136 ms, 2048 single-buffered 205 ms); EPDE_RES_TILE overrides for experiments
-    const size_t per_eq = sizeof(ResidProg) + sizeof(double) * TMAX * 3 + sizeof(int);
+    // tile = 1024 points (measured at 512^3, population 128: 2048-point tiles are slower); two buffers when they
+    // fit next to one segment of programs and the sum table
     int tile_pts = RES_TILE_MIN;
     if (const char* ev = getenv("EPDE_RES_TILE")) { const int v = atoi(ev); if (v == 1024 || v == 2048 || v == 4096) tile_pts = v; }
+    int seg_eqs = 64, batch_tiles = 4;      // measured at 512^3 / 128 equations: (64, 4) 117 ms, (16, 8) 129, (8, 8) 143
+    if (const char* ev = getenv("EPDE_RES_SEG")) seg_eqs = std::max(1, atoi(ev));
+    if (const char* ev = getenv("EPDE_RES_BATCH")) batch_tiles = std::max(1, atoi(ev));
     const long long n_tiles = (c->N + tile_pts - 1) / tile_pts;
     const int ne_all = (int)g.eqs.size();
-    // equations per launch: their programs and sum table live in shared memory next to the two tile buffers
     const size_t tile_bytes = sizeof(double) * (size_t)U * tile_pts;
-    if (tile_bytes + per_eq > (size_t)c->max_smem) return fail("pass B tiles need %zu bytes of shared memory", tile_bytes + per_eq);
-    const int cap = (int)(((size_t)c->max_smem - tile_bytes) / per_eq);
+    const size_t table_eq = sizeof(double) * TMAX * 3;
+    // equations per launch: the sum table of all of them stays in shared memory
+    const size_t fixed1 = tile_bytes + (size_t)seg_eqs * sizeof(ResidProg);
+    if (fixed1 + table_eq > (size_t)c->max_smem) return fail("pass B tiles need %zu bytes of shared memory", fixed1 + table_eq);
+    const int cap = (int)(((size_t)c->max_smem - fixed1) / table_eq);
     const int n_launch = (ne_all + cap - 1) / cap;
     const int per_launch = (ne_all + n_launch - 1) / n_launch;
     for (int e0 = 0; e0 < ne_all; e0 += per_launch) {
         const int ne = std::min(per_launch, ne_all - e0);
-        const int nwarps = std::max(1, std::min(c->resid_warps, ne));
+        const int nwarps = std::max(1, std::min(c->resid_warps, std::min(ne, seg_eqs)));
         ResidParams p;
         memset(&p, 0, sizeof p);
         p.N = c->N; p.eqs = b->d_eqs; p.factors = b->d_factors;
         p.eq_list = b->d_lists + g.list_off + e0; p.n_eq = ne; p.U = U; p.n_tiles = (int)n_tiles; p.tile_pts = tile_pts;
         for (int u = 0; u < U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
         p.slot_eval = b->d_slot_eval; p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.intercept_l1 = b->d_b1;
-        const size_t smem = tile_bytes + (size_t)ne * per_eq;
+        p.seg_eqs = std::min(seg_eqs, ne); p.batch_tiles = batch_tiles;
+        const size_t rest = (size_t)p.seg_eqs * sizeof(ResidProg) + (size_t)ne * table_eq;
+        p.nbuf = (2 * tile_bytes + rest <= (size_t)c->max_smem) ? 2 : 1;
+        const size_t smem = p.nbuf * tile_bytes + rest;
+        if (c->d_progs.ensure(2 * (size_t)ne * sizeof(ResidProg))) return 1;
+        p.progs = (ResidProg*)c->d_progs.ptr;
         // one persistent CTA per SM: the tile -> CTA assignment (and with it the summation order) depends only on
         // the grid size, never on what else is in the batch
         const int grid = (int)std::min<long long>(n_tiles, (long long)c->sm_count);
@@ -1694,7 +1770,13 @@ static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, 
         p.partial = (double*)c->d_partial.ptr;
         {
             KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
-            residual_tile_kernel<RES_WARPS><<<grid, nwarps * 32, smem, c->stream>>>(p);
+            residual_prog_kernel<<<1, 256, sizeof(int) * (size_t)ne, c->stream>>>(p);
+        }
+        CK(cudaGetLastError());
+        {
+            KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
+            if (b->want_l2) residual_tile_kernel<RES_WARPS, true><<<grid, nwarps * 32, smem, c->stream>>>(p);
+            else residual_tile_kernel<RES_WARPS, false><<<grid, nwarps * 32, smem, c->stream>>>(p);
         }
         CK(cudaGetLastError());
         ResidFinalParams fp;
@@ -1732,9 +1814,10 @@ int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx**
     c->max_smem = (int)prop.sharedMemPerBlockOptin;
     {
         // dynamic shared memory limit = opt-in maximum minus the kernels' static shared memory
-        const void* fns[2] = {(const void*)gram_tile_kernel<GRAM_WARPS>, (const void*)residual_tile_kernel<RES_WARPS>};
+        const void* fns[3] = {(const void*)gram_tile_kernel<GRAM_WARPS>, (const void*)residual_tile_kernel<RES_WARPS, true>,
+                              (const void*)residual_tile_kernel<RES_WARPS, false>};
         int dyn_max = c->max_smem;
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < 3; ++k) {
             cudaFuncAttributes fa;
             cudaError_t fe = cudaFuncGetAttributes(&fa, fns[k]);
             if (fe == cudaSuccess) {
@@ -1768,7 +1851,7 @@ int epde_ctx_destroy(epde_ctx* c) {
     cudaDeviceSynchronize();
     for (auto& kv : c->tokens) cudaFree(kv.second);
     c->d_geom.release(); c->d_cells.release(); c->d_seg.release(); c->d_win.release(); c->d_enc.release();
-    c->d_out.release(); c->d_partial.release(); c->d_given.release();
+    c->d_out.release(); c->d_partial.release(); c->d_given.release(); c->d_progs.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto& sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto& ev : c->free_events) cudaEventDestroy(ev);
@@ -2136,6 +2219,12 @@ int epde_batch_set_given(epde_batch* b, const int32_t* mode, const double* wterm
     return 0;
 }
 
+int epde_batch_set_norms(epde_batch* b, int want_l2) {
+    if (!b || !b->ctx) return fail("epde_batch_set_norms: null batch");
+    b->want_l2 = want_l2 != 0;
+    return 0;
+}
+
 int epde_batch_gram_size(epde_batch* b, int64_t* n) {
     if (!b || !n) return fail("null argument");
     *n = b->seg_doubles;
@@ -2246,7 +2335,7 @@ int epde_batch_fetch(epde_batch* b, const double* dev_sums, double* coef, double
     const double* sums = (const double*)hp(b->d_sums);
     for (int v = 0; v < ne; ++v) {
         if (fitness_l1) fitness_l1[v] = sums[3 * v] / sums[3 * v + 1];
-        if (fitness_l2) fitness_l2[v] = std::sqrt(sums[3 * v + 2]);
+        if (fitness_l2) fitness_l2[v] = b->want_l2 ? std::sqrt(sums[3 * v + 2]) : std::nan("");
     }
     return 0;
 }

@@ -228,8 +228,14 @@ class Engine:
         return out
 
     # ---- evaluation
-    def evaluate(self, enc: Encoding, want_sw=True) -> BatchResult:
-        """Whole path, host buffers in/out, synchronous."""
+    def evaluate(self, enc: Encoding, want_sw=True, want_l2=True) -> BatchResult:
+        """Whole path, host buffers in/out, synchronous.  want_l2=False: pass B accumulates the L1 sums
+        only (what L2LRFitness needs, fitness.py:142); ``fitness_l2`` is then NaN."""
+        if not want_l2:
+            with self.batch(enc) as b:
+                b.set_norms(want_l2=False)
+                b.gram(); b.solve(); b.residual()
+                return b.fetch(want_sw=want_sw)
         o = _alloc_out(enc.n_eval, self.n_windows, want_sw)
         _lib.check(self._lib.epde_evaluate_batch(self._h, *enc.c_args(), *_out_args(o)))
         return _trim(o, enc.n_eval)
@@ -273,6 +279,10 @@ class Batch:
         b = np.ascontiguousarray(intercept, np.float64)
         assert w.shape == (self.enc.n_eval, MAX_TERMS) and b.shape == (self.enc.n_eval,)
         _lib.check(self._lib.epde_batch_set_given(self._h, _p(m, _lib.c_i32p), _p(w, _lib.c_f64p), _p(b, _lib.c_f64p)))
+
+    def set_norms(self, want_l2=True):
+        """which residual norms pass B accumulates (include/epde_b200.h epde_batch_set_norms)."""
+        _lib.check(self._lib.epde_batch_set_norms(self._h, int(bool(want_l2))))
 
     @property
     def gram_size(self):

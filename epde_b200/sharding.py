@@ -44,7 +44,7 @@ def grid_slab(shape, rank: int, world: int):
 # ------------------------------------------------------------------------------------------
 # grid-point sharding: the staged path with its two all-reduces
 # ------------------------------------------------------------------------------------------
-def evaluate_grid_sharded(engine, enc, seg, sums, group=None, want_sw=True):
+def evaluate_grid_sharded(engine, enc, seg, sums, group=None, want_sw=True, want_l2=True):
     """One evaluation of `enc` on an engine that holds a slab of the grid.
 
     seg, sums: float64 tensors of ``batch.gram_size`` / ``batch.residual_size`` elements on the
@@ -56,6 +56,8 @@ def evaluate_grid_sharded(engine, enc, seg, sums, group=None, want_sw=True):
             raise ValueError(f'scratch too small: seg {seg.numel()} < {b.gram_size} or '
                              f'sums {sums.numel()} < {b.residual_size}')
         seg_v, sums_v = seg[:b.gram_size], sums[:b.residual_size]
+        if not want_l2:
+            b.set_norms(want_l2=False)
         b.gram(seg_v.data_ptr())
         dist.all_reduce(seg_v, op=dist.ReduceOp.SUM, group=group)
         b.solve(seg_v.data_ptr())

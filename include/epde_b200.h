@@ -145,6 +145,11 @@ int epde_batch_destroy(epde_batch* b);
  * terms 0); intercept[n_eval]. */
 int epde_batch_set_given(epde_batch* b, const int32_t* mode, const double* wterm,
                          const double* intercept);
+/* Which residual norms pass B accumulates.  want_l2 = 1 (default): sum|r|, sum|t| and sum r^2, i.e. both
+ * L2LRFitness (fitness.py:142) and L2Fitness (fitness.py:78-83) values.  want_l2 = 0: the L1 sums only -- what
+ * the MOEADD path needs (L2LRFitness is its fitness operator, moeadd/strategy.py:60); fitness_l2 then comes back
+ * as NaN.  Call before epde_batch_residual. */
+int epde_batch_set_norms(epde_batch* b, int want_l2);
 int epde_batch_gram_size(epde_batch* b, int64_t* n_doubles);
 int epde_batch_residual_size(epde_batch* b, int64_t* n_doubles);
 int epde_batch_gram(epde_batch* b, double* dev_seg);

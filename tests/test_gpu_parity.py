@@ -221,6 +221,22 @@ def test_staged_equals_oneshot_and_is_deterministic():
         assert np.array_equal(getattr(a, k), getattr(d, k)), k
 
 
+def test_l1_only_mode_equals_default():
+    """epde_batch_set_norms(0): pass B skips the sum of squares; every other output is bit-identical to the
+    default run and fitness_l2 comes back as NaN."""
+    for cfg, pop, seed in [('wave61', 12, 6), ('heat64', 8, 7)]:
+        shape, _, kind = syn.CONFIGS[cfg]
+        tokens = syn.make_tokens(shape, kind, seed=seed)
+        eqs = syn.make_population(len(tokens), pop, seed=seed)
+        enc = epde_b200.encode(eqs, syn.make_evals(eqs))
+        with make_engine(shape, tokens) as eng:
+            a = eng.evaluate(enc)
+            b = eng.evaluate(enc, want_l2=False)
+        for k in ('coef', 'intercept', 'fitness_l1', 'stability', 'sw_weights', 'n_active', 'all_zero', 'iters'):
+            assert np.array_equal(getattr(a, k), getattr(b, k)), (cfg, k)
+        assert np.all(np.isnan(b.fitness_l2)) and np.all(np.isfinite(a.fitness_l2))
+
+
 def test_given_weights_modes():
     """in-place fitness with known weights (fitness.py:70-96,130-174)."""
     shape, _, kind = syn.CONFIGS['wave61']
