@@ -338,7 +338,7 @@ __device__ __forceinline__ void fast_terms_r(const TermOffsets<T, N2, DEEP>& o, 
 // misses when the warps of a CTA run different equations, at the price of a few more multiplies by 1.0
 // (measured at 512^3: pass B 128 -> 122 ms; pass A, which is shared-memory-bandwidth bound, 53 -> 58 ms, so
 // pass A keeps the fine classes)
-#define COARSE_CLASSES_B 1
+#define COARSE_CLASSES_B 0
 __device__ __forceinline__ int n2_class(int n2, bool coarse) {
     if (coarse) return n2 == 0 ? 0 : (n2 <= 2 ? 2 : 3);
     return n2 <= 2 ? n2 : 3;
