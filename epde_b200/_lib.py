@@ -43,6 +43,9 @@ SIGNATURES = {
     'epde_batch_solve': (C.c_int, [vp, vp]),
     'epde_batch_residual': (C.c_int, [vp, vp]),
     'epde_batch_fetch': (C.c_int, [vp, vp] + _OUT),
+    'epde_ctx_synchronize': (C.c_int, [vp]),
+    'epde_fd_gradient': (C.c_int, [vp, vp, vp, C.c_int, c_i64p, C.c_int, c_f64p]),
+    'epde_cache_upload_interior': (C.c_int, [vp, C.c_int, vp, C.c_int, c_i64p, c_i64p]),
     'epde_ctx_launch_count': (C.c_int, [vp, c_i64p]),
     'epde_ctx_set_timing': (C.c_int, [vp, C.c_int]),
     'epde_ctx_kernel_time': (C.c_int, [vp, C.c_int, c_f64p, c_i64p]),

@@ -1459,7 +1459,7 @@ struct epde_ctx {
     Geom geom;
     int n_cells = 0;             // nA * nB * npieces
     DevBuf d_geom;               // packed geometry tables
-    DevBuf d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given, d_progs;
+    DevBuf d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given, d_progs, d_fd;
     void* h_pinned = nullptr; size_t h_pinned_cap = 0;
     epde_batch* live = nullptr;
     long long launches = 0;
@@ -1788,6 +1788,69 @@ static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, 
     return 0;
 }
 // ------------------------------------------------------------------------------------------
+// token producer on the device: finite-difference derivatives exactly as
+// AdaptiveFiniteDeriv does them (preprocessing/deriv_calculators.py:46-102 = repeated numpy.gradient with the
+// coordinate array of the axis, edge_order 1), on the FULL grid, then the interior crop that the boundary mask
+// applies before a tensor enters the cache (cache.py:250-270, interface.py:133-155).
+// numpy.gradient: constant spacing -> (f[i+1] - f[i-1]) / (2 dx); otherwise a f[i-1] + b f[i] + c f[i+1] with
+// a = -dx2 / (dx1 (dx1 + dx2)), b = (dx2 - dx1) / (dx1 dx2), c = dx1 / (dx2 (dx1 + dx2)); first-order one-sided
+// differences at the two ends.  Products and sums are rounded separately (no FMA) and in numpy's order, so the
+// result is bit-identical to the reference's.
+// ------------------------------------------------------------------------------------------
+struct FdParams {
+    const double* in;
+    double* out;
+    long long total, stride;     // elements, element stride of the axis
+    int n;                       // points along the axis
+    int uniform;
+    double dx;                   // uniform spacing
+    const double* a; const double* b; const double* c;   // [n] interior coefficients (non-uniform)
+    double dx_first, dx_last;    // end spacings
+};
+
+__global__ void __launch_bounds__(256) fd_gradient_kernel(FdParams p) {
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < p.total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)((idx / p.stride) % p.n);
+        double v;
+        if (i == 0) {
+            v = __ddiv_rn(__dsub_rn(p.in[idx + p.stride], p.in[idx]), p.dx_first);
+        } else if (i == p.n - 1) {
+            v = __ddiv_rn(__dsub_rn(p.in[idx], p.in[idx - p.stride]), p.dx_last);
+        } else if (p.uniform) {
+            v = __ddiv_rn(__dsub_rn(p.in[idx + p.stride], p.in[idx - p.stride]), __dmul_rn(2.0, p.dx));
+        } else {
+            const double t0 = __dmul_rn(p.a[i], p.in[idx - p.stride]);
+            const double t1 = __dmul_rn(p.b[i], p.in[idx]);
+            const double t2 = __dmul_rn(p.c[i], p.in[idx + p.stride]);
+            v = __dadd_rn(__dadd_rn(t0, t1), t2);
+        }
+        p.out[idx] = v;
+    }
+}
+
+struct CropParams {
+    const double* in;
+    double* out;
+    long long n_inner;
+    int ndim;
+    long long inner[EPDE_MAX_NDIM], full_stride[EPDE_MAX_NDIM], off[EPDE_MAX_NDIM];
+};
+
+__global__ void __launch_bounds__(256) crop_interior_kernel(CropParams p) {
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < p.n_inner;
+         idx += (long long)gridDim.x * blockDim.x) {
+        long long rem = idx, src = 0;
+        for (int d = p.ndim - 1; d >= 0; --d) {
+            const long long q = rem % p.inner[d];
+            rem /= p.inner[d];
+            src += (q + p.off[d]) * p.full_stride[d];
+        }
+        p.out[idx] = p.in[src];
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // C ABI
 // ------------------------------------------------------------------------------------------
 extern "C" {
@@ -1851,7 +1914,7 @@ int epde_ctx_destroy(epde_ctx* c) {
     cudaDeviceSynchronize();
     for (auto& kv : c->tokens) cudaFree(kv.second);
     c->d_geom.release(); c->d_cells.release(); c->d_seg.release(); c->d_win.release(); c->d_enc.release();
-    c->d_out.release(); c->d_partial.release(); c->d_given.release(); c->d_progs.release();
+    c->d_out.release(); c->d_partial.release(); c->d_given.release(); c->d_progs.release(); c->d_fd.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto& sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto& ev : c->free_events) cudaEventDestroy(ev);
@@ -2358,6 +2421,84 @@ int epde_evaluate_batch(epde_ctx* c, int n_eq, const int32_t* term_off, const in
     epde_batch_destroy(b);
     if (rc) g_err = keep;
     return rc;
+}
+
+int epde_ctx_synchronize(epde_ctx* c) {
+    if (!c) return fail("null context");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int epde_fd_gradient(epde_ctx* c, const double* dev_in, double* dev_out, int ndim, const int64_t* shape, int axis,
+                     const double* coords) {
+    if (!c || !dev_in || !dev_out || !shape || !coords) return fail("epde_fd_gradient: null argument");
+    if (ndim < 1 || ndim > EPDE_MAX_NDIM || axis < 0 || axis >= ndim) return fail("epde_fd_gradient: bad ndim / axis");
+    if (dev_in == dev_out) return fail("epde_fd_gradient: in-place differentiation is not supported");
+    const int n = (int)shape[axis];
+    if (n < 2) return fail("epde_fd_gradient: axis %d has %d points (numpy.gradient needs >= 2)", axis, n);
+    CK(cudaSetDevice(c->device));
+    FdParams p;
+    memset(&p, 0, sizeof p);
+    p.in = dev_in; p.out = dev_out; p.n = n;
+    p.total = 1; p.stride = 1;
+    for (int d = 0; d < ndim; ++d) { p.total *= shape[d]; if (d > axis) p.stride *= shape[d]; }
+    std::vector<double> dx(n - 1);
+    for (int i = 0; i + 1 < n; ++i) dx[i] = coords[i + 1] - coords[i];
+    bool uniform = true;
+    for (int i = 1; i + 1 < n; ++i) uniform = uniform && (dx[i] == dx[0]);
+    p.uniform = uniform ? 1 : 0;
+    p.dx = dx[0]; p.dx_first = dx[0]; p.dx_last = dx[n - 2];
+    if (!uniform) {
+        // numpy: a = -(dx2) / (dx1 * (dx1 + dx2)); b = (dx2 - dx1) / (dx1 * dx2); c = dx1 / (dx2 * (dx1 + dx2))
+        std::vector<double> co(3 * (size_t)n, 0.0);
+        for (int i = 1; i + 1 < n; ++i) {
+            const volatile double dx1 = dx[i - 1], dx2 = dx[i];
+            const volatile double s12 = dx1 + dx2;
+            const volatile double d1 = dx1 * s12, d2 = dx1 * dx2, d3 = dx2 * s12;
+            const volatile double diff = dx2 - dx1;
+            co[i] = -(dx2) / d1; co[n + i] = diff / d2; co[2 * (size_t)n + i] = dx1 / d3;
+        }
+        if (c->d_fd.ensure(sizeof(double) * co.size())) return 1;
+        CK(cudaMemcpyAsync(c->d_fd.ptr, co.data(), sizeof(double) * co.size(), cudaMemcpyHostToDevice, c->stream));
+        CK(cudaStreamSynchronize(c->stream));      // `co` is a pageable temporary
+        p.a = (const double*)c->d_fd.ptr; p.b = p.a + n; p.c = p.a + 2 * (size_t)n;
+    }
+    const int grid = (int)std::min<long long>((p.total + 255) / 256, (long long)c->sm_count * 16);
+    c->launches++;
+    fd_gradient_kernel<<<grid, 256, 0, c->stream>>>(p);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int epde_cache_upload_interior(epde_ctx* c, int id, const double* dev_full, int ndim, const int64_t* full_shape,
+                               const int64_t* boundary) {
+    if (!c || !dev_full || !full_shape || !boundary) return fail("epde_cache_upload_interior: null argument");
+    if (ndim != c->ndim) return fail("epde_cache_upload_interior: ndim %d, context has %d", ndim, c->ndim);
+    if (id < 0 || id >= EPDE_MAX_TOKENS) return fail("epde_cache_upload_interior: token id %d out of range", id);
+    CropParams p;
+    memset(&p, 0, sizeof p);
+    p.in = dev_full; p.ndim = ndim; p.n_inner = c->N;
+    long long stride = 1;
+    for (int d = ndim - 1; d >= 0; --d) {
+        if (boundary[d] < 0 || full_shape[d] - 2 * boundary[d] != c->shape[d])
+            return fail("epde_cache_upload_interior: axis %d: full %lld - 2 x boundary %lld != inner %lld", d,
+                        (long long)full_shape[d], (long long)boundary[d], c->shape[d]);
+        p.inner[d] = c->shape[d]; p.off[d] = boundary[d]; p.full_stride[d] = stride;
+        stride *= full_shape[d];
+    }
+    CK(cudaSetDevice(c->device));
+    double*& tok = c->tokens[id];
+    if (!tok) {
+        cudaError_t e = cudaMalloc((void**)&tok, sizeof(double) * (size_t)c->N);
+        if (e != cudaSuccess) { c->tokens.erase(id); return fail("epde_cache_upload_interior: out of device memory (%s)", cudaGetErrorString(e)); }
+    }
+    p.out = tok;
+    const int grid = (int)std::min<long long>((c->N + 255) / 256, (long long)c->sm_count * 16);
+    c->launches++;
+    crop_interior_kernel<<<grid, 256, 0, c->stream>>>(p);
+    CK(cudaGetLastError());
+    return 0;
 }
 
 }  // extern "C"

@@ -158,6 +158,9 @@ class Engine:
     def __exit__(self, *exc):
         self.close()
 
+    def synchronize(self):
+        _lib.check(self._lib.epde_ctx_synchronize(self._h))
+
     def set_stream(self, cuda_stream):
         """cuda_stream: integer cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream)."""
         _lib.check(self._lib.epde_ctx_set_stream(self._h, C.c_void_p(int(cuda_stream))))

@@ -159,6 +159,22 @@ int epde_batch_fetch(epde_batch* b, const double* dev_sums,
                      double* coef, double* intercept, double* fitness_l1, double* fitness_l2,
                      double* stability, double* sw_weights, int32_t* n_active,
                      int32_t* all_zero, int32_t* iters);
+/* ---- token producers on the device ---------------------------------------
+ * epde_fd_gradient = numpy.gradient(data, coords, axis=axis) (edge_order 1) as AdaptiveFiniteDeriv applies it
+ * (epde/preprocessing/deriv_calculators.py:46-102; higher orders = repeated calls), on a FULL-grid device
+ * tensor of `shape` (C order), result to dev_out (same shape, must differ from dev_in); coords = the host
+ * coordinate vector of the axis (shape[axis] values).  Arithmetic is rounded like numpy's (bit-identical).
+ * epde_cache_upload_interior = the boundary crop of Cache.set_boundaries / BoundaryExclusion
+ * (cache.py:250-270, decorators.py:103-134) + Cache.add: rows [boundary[d], full_shape[d] - boundary[d]) of
+ * every axis of a full-grid device tensor become token `token_id` (full - 2 * boundary must equal the
+ * context's inner shape). */
+/* wait for everything queued on the context stream (the producers above are asynchronous). */
+int epde_ctx_synchronize(epde_ctx* ctx);
+int epde_fd_gradient(epde_ctx* ctx, const double* dev_in, double* dev_out, int ndim, const int64_t* shape,
+                     int axis, const double* coords);
+int epde_cache_upload_interior(epde_ctx* ctx, int token_id, const double* dev_full, int ndim,
+                               const int64_t* full_shape, const int64_t* boundary);
+
 /* number of kernel launches issued by the library on this context since creation. */
 int epde_ctx_launch_count(epde_ctx* ctx, int64_t* launches);
 

@@ -1,0 +1,77 @@
+"""GPU tests of the device token producer (epde_b200.producers.fd_derivatives) against numpy.gradient --
+the arithmetic the reference's AdaptiveFiniteDeriv runs (preprocessing/deriv_calculators.py:46-102) -- followed
+by the boundary crop.  Bar: bit-exact (the kernel rounds products and sums like numpy)."""
+import numpy as np
+import pytest
+
+import epde_b200
+from epde_b200 import producers
+
+pytestmark = pytest.mark.gpu
+
+
+def numpy_chain(data, coords, max_order, boundary):
+    """AdaptiveFiniteDeriv.differentiate, non-mixed (deriv_calculators.py:50-88), then the interior crop."""
+    crop = tuple(slice(b, n - b) for b, n in zip(boundary, data.shape))
+    out = []
+    for dim in range(data.ndim):
+        cur = data
+        for _ in range(max_order[dim]):
+            cur = np.gradient(cur, coords[dim], axis=dim)
+            out.append(np.ascontiguousarray(cur[crop]).reshape(-1))
+    return out
+
+
+@pytest.mark.parametrize('shape,boundary,max_order,uniform', [
+    ((81, 81), (10, 10), (2, 2), False), ((64, 48), (0, 0), (1, 2), True), ((33, 20, 27), (4, 4, 4), (1, 2, 2), False),
+    ((40, 36, 30), (0, 3, 5), (2, 0, 3), True), ((2, 5), (0, 0), (1, 1), False)])
+def test_fd_derivatives_bit_exact(shape, boundary, max_order, uniform):
+    rng = np.random.default_rng(sum(shape))
+    if uniform:
+        coords = [np.arange(n, dtype=np.float64) * 0.125 for n in shape]          # exactly constant spacing
+    else:
+        coords = [np.linspace(0.0, 1.0 + d, n) if d % 2 == 0 else np.sort(rng.random(n)) * 3 for d, n in enumerate(shape)]
+    grids = np.meshgrid(*coords, indexing='ij')
+    data = np.sin(2.0 * grids[0]) * np.cos(grids[-1]) + 0.05 * rng.standard_normal(shape)
+    inner = tuple(n - 2 * b for n, b in zip(shape, boundary))
+    ref = numpy_chain(data, coords, max_order, boundary)
+    with epde_b200.Engine(inner, device=0) as eng:
+        ids = producers.fd_derivatives(eng, data, coords, max_order, boundary, first_token_id=1, field_token_id=0)
+        assert ids == list(range(1, 1 + len(ref)))
+        crop = tuple(slice(b, n - b) for b, n in zip(boundary, shape))
+        assert np.array_equal(eng.download(0), data[crop].reshape(-1))
+        for i, r in zip(ids, ref):
+            got = eng.download(i)
+            assert np.array_equal(got, r), f'token {i}: max abs diff {np.abs(got - r).max()}'
+        assert eng.launch_count >= 2 * len(ref)
+
+
+def test_fd_labels_and_errors():
+    assert producers.deriv_labels('u', (2, 2)) == ['du/dx0', 'd^2u/dx0^2', 'du/dx1', 'd^2u/dx1^2']
+    with epde_b200.Engine((6, 6), device=0) as eng:
+        with pytest.raises(ValueError):
+            producers.fd_derivatives(eng, np.zeros((8, 8)), [np.arange(8.0)], 1, 1)
+        with pytest.raises(epde_b200.EpdeB200Error):       # 8 - 2*2 != 6
+            producers.fd_derivatives(eng, np.zeros((8, 8)), [np.arange(8.0), np.arange(8.0)], 1, 2)
+
+
+def test_produced_tokens_feed_the_evaluator():
+    """end to end: field -> device derivatives -> cache -> evaluate == upload of numpy derivatives -> evaluate."""
+    shape, b = (60, 50), 5
+    t, x = np.linspace(0, 1, shape[0]), np.linspace(0, 2, shape[1])
+    T, X = np.meshgrid(t, x, indexing='ij')
+    u = np.exp(-T) * np.sin(3 * X) + 1e-3 * np.random.default_rng(0).standard_normal(shape)
+    inner = (shape[0] - 2 * b, shape[1] - 2 * b)
+    eqs = [[[(1, 1.0, 0, 0.0)], [(4, 1.0, 0, 0.0)], [(0, 1.0, 0, 0.0), (3, 1.0, 0, 0.0)], [(2, 1.0, 0, 0.0)]]]
+    enc = epde_b200.encode(eqs, [(0, 0), (0, 3)])
+    with epde_b200.Engine(inner, device=0) as eng:
+        producers.fd_derivatives(eng, u, [t, x], (2, 2), b, first_token_id=1, field_token_id=0)
+        a = eng.evaluate(enc)
+    ref = numpy_chain(u, [t, x], (2, 2), (b, b))
+    with epde_b200.Engine(inner, device=0) as eng:
+        eng.upload(0, u[b:-b, b:-b])
+        for i, r in enumerate(ref):
+            eng.upload(i + 1, r)
+        c = eng.evaluate(enc)
+    for k in ('coef', 'intercept', 'fitness_l1', 'fitness_l2', 'stability'):
+        assert np.array_equal(getattr(a, k), getattr(c, k)), k
