@@ -14,7 +14,8 @@ HDR = os.path.join(os.path.dirname(PKG), 'include', 'epde_b200.h')
 LIB = os.path.join(PKG, 'libepde_b200.so')
 
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
-              '-Xcompiler', '-fPIC', '-shared']
+              '-Xcompiler', '-fPIC', '-shared',
+              '--split-compile=0']      # ptxas works on the ~200 template instantiations in parallel (build 2.7 -> 1.5 min)
 
 
 def find_nvcc():

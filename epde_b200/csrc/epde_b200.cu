@@ -53,9 +53,8 @@
 #define TILE_ROWS 64           // rows (leading-axes index pairs) of a pass-A tile
 #define TILE_COLS 32           // columns (last axis) of a pass-A tile = warp width
 #define GRAM_WARPS 8           // warps per pass-A CTA
-#define RED_CHUNK 8            // Gram entries reduced per shared-memory round of the cell flush
 #define MAXU 12                // distinct tokens per launch group (tile = MAXU x 64 x 32 doubles = 192 KB)
-#define RES_WARPS 8            // warps per pass-B CTA (8 x <= 255 registers)
+#define RES_WARPS 8            // warps per pass-B CTA (8 x <= 255 registers; 12 and 16 warps measured slower)
 #define RES_TILE_MIN 1024      // points of a pass-B tile
 
 static thread_local std::string g_err;
@@ -344,58 +343,53 @@ __device__ __forceinline__ int n2_class(int n2, bool coarse) {
     return n2 <= 2 ? n2 : 3;
 }
 
-// flush: sum the lanes (columns) of every piece, RED_CHUNK Gram entries per round
+// flush: sum the lanes (columns) of every last-axis piece of the unit with warp shuffles (fixed tree order, no
+// shared memory) and let the first lane of each piece store its NACC sums, un-permuted through accmap.
+//   wlog >= 0: every piece is 2^wlog lanes wide and starts on a multiple of it -> xor butterfly in the lane groups;
+//   otherwise: segmented reduction by doubling; lane_piece = piece of this lane's column (-1 beyond the unit).
 template <int T>
-__device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2], int lane, unsigned red, double* out,
-                                            int piece_lo, int npieces, int col_lo, const int* __restrict__ piece_start,
-                                            const unsigned char* accmap, int wlog) {
+__device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2], int lane, double* out, int npieces,
+                                            const unsigned char* accmap, int wlog, int lane_piece) {
     constexpr int NACC = T * (T + 3) / 2;
-    constexpr int RS = TILE_COLS + 1;
-    if (wlog >= 0) {
-        // every piece is 2^wlog lanes wide and starts on a multiple of it: butterfly inside the lane groups
-        // (NACC independent chains per step), then the first lane of each group stores its piece
-        double v[NACC];
+    double v[NACC];
 #pragma unroll
-        for (int k = 0; k < NACC; ++k) v[k] = acc[k];
+    for (int k = 0; k < NACC; ++k) v[k] = acc[k];
+    bool head;
+    int pp;
+    if (wlog >= 0) {
         for (int off = 1; off < (1 << wlog); off <<= 1) {
 #pragma unroll
             for (int k = 0; k < NACC; ++k) v[k] += __shfl_xor_sync(0xffffffffu, v[k], off);
         }
-        const int pp = lane >> wlog;
-        if ((lane & ((1 << wlog) - 1)) == 0 && pp < npieces) {
-            double* o = out + (long long)pp * NACC;
+        pp = lane >> wlog;
+        head = (lane & ((1 << wlog) - 1)) == 0 && pp < npieces;
+    } else {
+        for (int off = 1; off < 32; off <<= 1) {
+            const int other = __shfl_down_sync(0xffffffffu, lane_piece, off);
+            const bool take = (lane + off < 32) && (other == lane_piece);
 #pragma unroll
-            for (int k = 0; k < NACC; ++k) o[accmap[k]] = v[k];
+            for (int k = 0; k < NACC; ++k) {
+                const double t = __shfl_down_sync(0xffffffffu, v[k], off);
+                if (take) v[k] += t;
+            }
         }
-        __syncwarp();
-        return;
+        const int prev = __shfl_up_sync(0xffffffffu, lane_piece, 1);
+        pp = lane_piece;
+        head = pp >= 0 && (lane == 0 || prev != lane_piece);
     }
+    if (head) {
+        double* o = out + (long long)pp * NACC;
 #pragma unroll
-    for (int b0 = 0; b0 < NACC; b0 += RED_CHUNK) {
-        const int cnt = (NACC - b0) < RED_CHUNK ? (NACC - b0) : RED_CHUNK;
-        __syncwarp();
-#pragma unroll
-        for (int k = 0; k < RED_CHUNK; ++k)
-            if (b0 + k < NACC) sts_f64_volatile(red + (k * RS + lane) * 8, acc[b0 + k]);
-        __syncwarp();
-        const int nout = npieces * cnt;
-        for (int o = lane; o < nout; o += 32) {
-            const int pp = o / cnt, k = o - pp * cnt;
-            const int lo = piece_start[piece_lo + pp] - col_lo;
-            const int hi = piece_start[piece_lo + pp + 1] - col_lo;
-            double s = 0.0;
-            for (int cidx = lo; cidx < hi; ++cidx) s += lds_f64_volatile(red + (k * RS + cidx) * 8);
-            out[(long long)pp * NACC + accmap[b0 + k]] = s;
-        }
+        for (int k = 0; k < NACC; ++k) o[accmap[k]] = v[k];
     }
     __syncwarp();
 }
 
 // fast path: every term = x^p [* y^q], p, q in {1, 2, 3}; R tile rows per iteration
 template <int T, int N2, int DEEP, int R>
-__device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, unsigned ops2, unsigned ones, int nrows, int lane, unsigned red,
-                                            double* out, int piece_lo, int npieces, int col_lo,
-                                            const int* __restrict__ piece_start, const unsigned char* accmap, int wlog) {
+__device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, unsigned ops2, unsigned ones, int nrows, int lane,
+                                            double* out, int npieces, const unsigned char* accmap, int wlog,
+                                            int lane_piece) {
     constexpr int NACC = T * (T + 3) / 2;
     constexpr int ROWB = TILE_COLS * 8;
     double acc[NACC];
@@ -418,15 +412,14 @@ __device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, unsigne
         fast_terms_r<T, N2, DEEP, 1, ROWB>(off, base + row * ROWB, ones, c);
         gram_accumulate<T>(acc, c[0]);
     }
-    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start, accmap, wlog);
+    flush_cells<T>(acc, lane, out, npieces, accmap, wlog, lane_piece);
 }
 
 // generic path: any factor kind / power / factor count
 template <int T>
 __device__ __noinline__ void gram_warp_generic(const double* tile, int tstride, const WarpProg* wp,
-                                               const FactorDesc* fac, int nrows, int lane, unsigned red, double* out,
-                                               int piece_lo, int npieces, int col_lo,
-                                               const int* __restrict__ piece_start, int wlog) {
+                                               const FactorDesc* fac, int nrows, int lane, double* out, int npieces,
+                                               int wlog, int lane_piece) {
     constexpr int NACC = T * (T + 3) / 2;
     double acc[NACC];
 #pragma unroll
@@ -439,18 +432,18 @@ __device__ __noinline__ void gram_warp_generic(const double* tile, int tstride, 
             c[t] = eval_term_generic(fac, wp->foff[t], wp->foff[t + 1], base + row * TILE_COLS, tstride);
         gram_accumulate<T>(acc, c);
     }
-    flush_cells<T>(acc, lane, red, out, piece_lo, npieces, col_lo, piece_start, wp->accmap, wlog);
+    flush_cells<T>(acc, lane, out, npieces, wp->accmap, wlog, lane_piece);
 }
 
 template <int T>
 __device__ __forceinline__ void gram_warp(const double* tile, int tstride, const WarpProg* wp, const FactorDesc* fac,
-                                          unsigned ones, int nrows, int lane, double* red, double* out, int piece_lo,
-                                          int npieces, int col_lo, const int* __restrict__ piece_start, int wlog) {
+                                          unsigned ones, int nrows, int lane, double* out, int npieces, int wlog,
+                                          int lane_piece) {
     // 8-warp CTAs may use 255 registers per thread: four rows per iteration (two for the widest equations)
     constexpr int R = T <= 6 ? 4 : 2;
     if (wp->fast) {
 #define GWF(NN, DD) gram_warp_fast<T, (NN), (DD), R>(smem_addr(tile), smem_addr(wp->op), smem_addr(wp->op2), ones, nrows, \
-                                                     lane, smem_addr(red), out, piece_lo, npieces, col_lo, piece_start, wp->accmap, wlog)
+                                                     lane, out, npieces, wp->accmap, wlog, lane_piece)
 #define GWD(NN) do { if (wp->n3 == 0) GWF(NN, 0); else if (wp->n3 == 1) GWF(NN, 1); else GWF(NN, 2); } while (0)
         switch (n2_class(wp->n2, false)) {
             case 0: GWF(0, 0); break;
@@ -461,8 +454,7 @@ __device__ __forceinline__ void gram_warp(const double* tile, int tstride, const
 #undef GWD
 #undef GWF
     } else {
-        gram_warp_generic<T>(tile, tstride, wp, fac, nrows, lane, smem_addr(red), out, piece_lo, npieces, col_lo,
-                             piece_start, wlog);
+        gram_warp_generic<T>(tile, tstride, wp, fac, nrows, lane, out, npieces, wlog, lane_piece);
     }
 }
 
@@ -472,14 +464,14 @@ __global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
     __shared__ int s_next;
     __shared__ const double* s_tok[MAXU];
     __shared__ __align__(16) double s_ones[128];     // 4 rows x 256 bytes of 1.0 (fast_terms_r)
+    __shared__ int s_lane_piece[TILE_COLS];
     const int tid = threadIdx.x;
     const int nwarps = blockDim.x >> 5;
     const int warp = tid >> 5, lane = tid & 31;
     for (int q = tid; q < 128; q += blockDim.x) s_ones[q] = 1.0;
     const int tstride = p.g.max_rows * TILE_COLS;
     double* tile = smem;                                              // [U][max_rows][32]
-    double* red_all = tile + (size_t)p.U * tstride;                   // [nwarps][RED_CHUNK][33]
-    WarpProg* progs = (WarpProg*)(red_all + nwarps * RED_CHUNK * (TILE_COLS + 1));   // [n_eq]
+    WarpProg* progs = (WarpProg*)(tile + (size_t)p.U * tstride);      // [n_eq]
     if (tid < MAXU) s_tok[tid] = p.tok[tid];
 
     // ---- per-equation programs, built once per (persistent) CTA: a task then starts from shared memory only
@@ -504,7 +496,6 @@ __global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
     }
     __syncthreads();
 
-    double* red = red_all + warp * RED_CHUNK * (TILE_COLS + 1);
     for (int ui = blockIdx.x; ui < p.g.n_units; ui += gridDim.x) {
         const UnitDesc u = p.g.units[ui];
         const int wb = u.b_hi - u.b_lo;
@@ -528,16 +519,26 @@ __global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
                     if (c0 + 1 < u.ncols) cp_async8(dst + 1, src + 1); else dst[1] = 0.0;
                 }
             }
+            // piece of every tile column (general flush path)
+            if (tid < TILE_COLS) {
+                int pc = -1;
+                for (int q = 0; q < u.npieces; ++q) {
+                    const int lo = p.g.piece_start[u.piece_lo + q] - u.col_lo, hi = p.g.piece_start[u.piece_lo + q + 1] - u.col_lo;
+                    if (tid >= lo && tid < hi) pc = q;
+                }
+                s_lane_piece[tid] = pc;
+            }
             cp_async_wait_all();
             if (tid == 0) s_next = nwarps;
             __syncthreads();
         }
+        const int lane_piece = s_lane_piece[lane];
         int le = warp;
         while (le < p.n_eq) {
             const WarpProg* wp = progs + le;
             const int T = wp->T;
             double* out = p.cells + wp->c_off + ((long long)u.cell * p.g.npieces + u.piece_lo) * nacc_of(T);
-#define GW(TT) gram_warp<TT>(tile, tstride, wp, p.factors, smem_addr(s_ones), nrows, lane, red, out, u.piece_lo, u.npieces, u.col_lo, p.g.piece_start, u.wlog)
+#define GW(TT) gram_warp<TT>(tile, tstride, wp, p.factors, smem_addr(s_ones), nrows, lane, out, u.npieces, u.wlog, lane_piece)
             switch (T) {
                 case 1: GW(1); break;
                 case 2: GW(2); break;
@@ -1693,8 +1694,8 @@ struct epde_batch {
 };
 
 static size_t gram_smem_bytes(const epde_ctx* c, int U, int nwarps, int n_eq) {
-    return sizeof(double) * ((size_t)U * c->geom.max_rows * TILE_COLS + (size_t)nwarps * RED_CHUNK * (TILE_COLS + 1)) +
-           (size_t)n_eq * sizeof(WarpProg);
+    (void)nwarps;
+    return sizeof(double) * ((size_t)U * c->geom.max_rows * TILE_COLS) + (size_t)n_eq * sizeof(WarpProg);
 }
 
 static int launch_gram_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double* cells) {
