@@ -207,12 +207,13 @@ struct WarpProg {
 
 // ------------------------------------------------------------------------------------------
 // pass A: fused term assembly + cell Gram.
-// CTA <-> unit (a (sub-)cell of the leading axes x <= 32 columns of the last axis): the tile of
-// every token of the launch group is staged in shared memory once, then each warp takes equations
-// from the group's list (longest first, dynamic) and accumulates that equation's cell Gram in
-// registers, lane <-> column, looping over the tile rows.  The per-lane accumulators are reduced
-// over the columns of each last-axis piece through a small per-warp shared buffer and written to the
-// cell table (no atomics: fixed summation order).
+// Persistent CTAs (one per SM) walk the units (a (sub-)cell of the leading axes x <= 32 columns of the
+// last axis): the tile of every token of the launch group is staged in shared memory once, then each
+// warp takes equations from the group's list (sorted by code variant, dynamic) and accumulates that
+// equation's cell Gram in registers, lane <-> column, looping over the tile rows.  The per-lane
+// accumulators are reduced over the columns of each last-axis piece with warp shuffles only (xor
+// butterfly when the pieces have one power-of-two width, segmented shfl_down otherwise) and written
+// to the cell table (no atomics: fixed summation order).
 // ------------------------------------------------------------------------------------------
 struct GramParams {
     Geom g;
@@ -559,7 +560,9 @@ __global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
 
 // ------------------------------------------------------------------------------------------
 // marginals: segment Gram row = sum of the cell Grams of the slab, in a fixed order (deterministic)
-// grid = (n_rows, n_eq_group); block = 256 = 8 cell lanes x 32 entry lanes
+// grid = (n_rows, n_eq_group); block = 256: thread <-> (cell lane, Gram entry) with 256 / NACC cell lanes, so
+// consecutive threads read consecutive doubles of consecutive cells (the slab of a leading-axis row is one
+// contiguous range of the cell table) and four independent loads per thread are in flight.
 // ------------------------------------------------------------------------------------------
 struct MargParams {
     Geom g;
@@ -570,36 +573,41 @@ struct MargParams {
 };
 
 __global__ void __launch_bounds__(256) marginal_kernel(MargParams p) {
-    __shared__ double part[8][64];
+    __shared__ double part[256];
     const int e = p.eq_list[blockIdx.y];
     const EqDesc& eq = p.eqs[e];
     const int NACC = nacc_of(eq.T);
     const int NE = NACC + 1;
     const MargDesc m = p.g.marg[blockIdx.x];
-    const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
-    const int nb = m.b_hi - m.b_lo, np = m.p_hi - m.p_lo;
-    const int ncell = (m.a_hi - m.a_lo) * nb * np;
-    const double* C = p.cells + eq.c_off;
-    double s0 = 0.0, s1 = 0.0;
-    for (int q = grp; q < ncell; q += 8) {
-        const int ip = q % np;
-        const int r = q / np;
-        const int ibb = r % nb, iaa = r / nb;
-        const long long cell = ((long long)(m.a_lo + iaa) * p.g.nB + (m.b_lo + ibb)) * p.g.npieces + (m.p_lo + ip);
-        const double* src = C + cell * NACC;
-        if (lane < NACC) s0 += src[lane];
-        if (lane + 32 < NACC) s1 += src[lane + 32];
+    const int tid = threadIdx.x;
+    const int cpt = 256 / NACC;                    // cells per trip (>= 5: NACC <= 44)
+    const int sub = tid / NACC, k = tid - sub * NACC;
+    const unsigned nb = m.b_hi - m.b_lo, np = m.p_hi - m.p_lo;
+    const int ncell = (m.a_hi - m.a_lo) * (int)nb * (int)np;
+    const double* C = p.cells + eq.c_off + k;
+    auto at = [&](int q) -> double {
+        const unsigned r = (unsigned)q / np, ip = (unsigned)q - r * np;
+        const unsigned iaa = r / nb, ibb = r - iaa * nb;
+        const long long cell = ((long long)(m.a_lo + (int)iaa) * p.g.nB + (m.b_lo + (int)ibb)) * p.g.npieces + (m.p_lo + (int)ip);
+        return __ldcs(C + cell * NACC);             // read once: do not keep in L2 ahead of the token tiles
+    };
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    if (sub < cpt) {
+        int q = sub;
+        for (; q + 3 * cpt < ncell; q += 4 * cpt) {
+            const double v0 = at(q), v1 = at(q + cpt), v2 = at(q + 2 * cpt), v3 = at(q + 3 * cpt);
+            s0 += v0; s1 += v1; s2 += v2; s3 += v3;
+        }
+        for (; q < ncell; q += cpt) s0 += at(q);
     }
-    part[grp][lane] = s0;
-    part[grp][lane + 32] = s1;
+    part[tid] = (s0 + s1) + (s2 + s3);
     __syncthreads();
-    if (threadIdx.x < 64 && threadIdx.x < NACC) {
+    if (tid < NACC) {
         double s = 0.0;
-#pragma unroll
-        for (int gI = 0; gI < 8; ++gI) s += part[gI][threadIdx.x];
-        p.seg[eq.s_off + (long long)m.row * NE + threadIdx.x] = s;
+        for (int j = 0; j < cpt; ++j) s += part[j * NACC + tid];
+        p.seg[eq.s_off + (long long)m.row * NE + tid] = s;
     }
-    if (threadIdx.x == 64) p.seg[eq.s_off + (long long)m.row * NE + NACC] = m.count;
+    if (tid == 64) p.seg[eq.s_off + (long long)m.row * NE + NACC] = m.count;
 }
 
 // window Gram = direct sum of the segment rows of the window; row W = every point (all of axis 0).
@@ -1070,7 +1078,7 @@ __device__ __forceinline__ void residual_reduce(const double (&a1)[NU], const do
 template <int NU, int N2, int DEEP, bool L2>
 __device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, unsigned ones, const ResidProg* rp, int NV,
                                                 int npts, int lane, double* table_row) {
-    constexpr int R = (NU <= 6) ? 4 : 2;
+    constexpr int R = (NU <= 6) ? 4 : 2;      // (4 at NU 7, 8 in the L1-only build spills: measured 116 vs 99 ms)
     const unsigned m_a = prog + (unsigned)offsetof(ResidProg, m);
     const unsigned sb_a = prog + (unsigned)offsetof(ResidProg, sb);
     const unsigned sdb_a = prog + (unsigned)offsetof(ResidProg, sdb);

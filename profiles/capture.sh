@@ -6,6 +6,7 @@ tag=${1:-vX}
 out=gpurun_out
 mkdir -p $out
 timeout 400 python bench.py > $out/bench_heat512_$tag.json 2> $out/bench_heat512_$tag.err
+timeout 200 python bench.py --norms both --no-cpu-baseline > $out/bench_heat512_both_$tag.json 2>/dev/null
 timeout 200 python bench.py --workload heat256 --no-cpu-baseline > $out/bench_heat256_$tag.json 2>/dev/null
 timeout 200 python bench.py --workload wave1024 --no-cpu-baseline > $out/bench_wave1024_$tag.json 2>/dev/null
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/launches_heat512_$tag.csv \
