@@ -118,7 +118,7 @@ struct UnitDesc {            // one CTA work unit of pass A: a (sub-)cell of the
 struct MargDesc {            // one output row of the segment-Gram table
     int row;                 // row in S
     int a_lo, a_hi, b_lo, b_hi, p_lo, p_hi;   // cell ranges to sum
-    int pad;
+    int kind;                // which range is the segment's: 0 = slot A, 1 = slot B, 2 = pieces
     double count;            // number of grid points in the segment slab (local)
 };
 
@@ -608,6 +608,95 @@ __global__ void __launch_bounds__(256) marginal_kernel(MargParams p) {
         p.seg[eq.s_off + (long long)m.row * NE + tid] = s;
     }
     if (tid == 64) p.seg[eq.s_off + (long long)m.row * NE + NACC] = m.count;
+}
+
+// Three-axis grids: every cell belongs to one row of each axis, so the kernel above reads the cell table three
+// times.  Two steps read it once: step 1, one CTA per (slot-A cell index a, equation), walks the contiguous slab
+// [a][all b][all pieces] and leaves  tot[a], byB[a][b], byP[a][piece]  (byP in per-thread shared slots: thread
+// (cell lane, entry) always meets the same pieces); step 2 sums those over the ranges of each segment row.
+struct MargSlabParams {
+    Geom g;
+    const EqDesc* eqs;
+    const int* eq_list;
+    const double* cells;
+    double* part;            // per equation of the group: [nA][1 + nB + npieces][NACC]
+    long long eq_stride;
+    double* seg;
+};
+
+__global__ void __launch_bounds__(256) marginal_slab_kernel(MargSlabParams p) {
+    extern __shared__ double s_pp[];               // [npieces][NACC]
+    __shared__ double part[256];
+    const int a = blockIdx.x;
+    const EqDesc& eq = p.eqs[p.eq_list[blockIdx.y]];
+    const int NACC = nacc_of(eq.T);
+    const int tid = threadIdx.x;
+    const int cpt = 256 / NACC;
+    const int sub = tid / NACC, k = tid - sub * NACC;
+    const int nB = p.g.nB, np = p.g.npieces;
+    const bool act = sub < cpt;
+    if (act)
+        for (int q = sub; q < np; q += cpt) s_pp[q * NACC + k] = 0.0;
+    const double* C = p.cells + eq.c_off + (long long)a * nB * np * NACC + k;
+    double* out = p.part + (long long)blockIdx.y * p.eq_stride + (long long)a * (1 + nB + np) * NACC;
+    double tot = 0.0;
+    for (int b = 0; b < nB; ++b) {
+        double vb = 0.0;
+        if (act) {
+            const double* Cb = C + (long long)b * np * NACC;
+#pragma unroll 4
+            for (int q = sub; q < np; q += cpt) {
+                const double v = __ldcs(Cb + q * NACC);
+                vb += v;
+                s_pp[q * NACC + k] += v;
+            }
+        }
+        part[tid] = vb;
+        __syncthreads();
+        if (tid < NACC) {
+            double t = 0.0;
+            for (int j = 0; j < cpt; ++j) t += part[j * NACC + tid];
+            out[(1 + b) * NACC + tid] = t;
+            tot += t;
+        }
+        __syncthreads();
+    }
+    if (tid < NACC) out[tid] = tot;
+    if (act)
+        for (int q = sub; q < np; q += cpt) out[(1 + nB + q) * NACC + k] = s_pp[q * NACC + k];
+}
+
+// grid = (n_rows, n_eq_group), block = 64
+__global__ void __launch_bounds__(64) marginal_rows_kernel(MargSlabParams p) {
+    const EqDesc& eq = p.eqs[p.eq_list[blockIdx.y]];
+    const int NACC = nacc_of(eq.T);
+    const int NE = NACC + 1;
+    const MargDesc m = p.g.marg[blockIdx.x];
+    const int k = threadIdx.x;
+    const int rowlen = 1 + p.g.nB + p.g.npieces;
+    if (k < NACC) {
+        const double* P = p.part + (long long)blockIdx.y * p.eq_stride + k;
+        double s = 0.0;
+        if (m.kind == 0) {
+#pragma unroll 4
+            for (int a = m.a_lo; a < m.a_hi; ++a) s += P[(long long)a * rowlen * NACC];
+        } else {
+            const int lo = (m.kind == 1) ? 1 + m.b_lo : 1 + p.g.nB + m.p_lo;
+            const int n = (m.kind == 1) ? m.b_hi - m.b_lo : m.p_hi - m.p_lo;
+            for (int q = 0; q < n; ++q) {
+                double t0 = 0.0, t1 = 0.0;
+                int a = 0;
+                for (; a + 1 < p.g.nA; a += 2) {
+                    t0 += P[((long long)a * rowlen + lo + q) * NACC];
+                    t1 += P[((long long)(a + 1) * rowlen + lo + q) * NACC];
+                }
+                if (a < p.g.nA) t0 += P[((long long)a * rowlen + lo + q) * NACC];
+                s += t0 + t1;
+            }
+        }
+        p.seg[eq.s_off + (long long)m.row * NE + k] = s;
+    }
+    if (k == 63) p.seg[eq.s_off + (long long)m.row * NE + NACC] = m.count;
 }
 
 // window Gram = direct sum of the segment rows of the window; row W = every point (all of axis 0).
@@ -1468,7 +1557,7 @@ struct epde_ctx {
     Geom geom;
     int n_cells = 0;             // nA * nB * npieces
     DevBuf d_geom;               // packed geometry tables
-    DevBuf d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given, d_progs, d_fd;
+    DevBuf d_marg, d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given, d_progs, d_fd;
     void* h_pinned = nullptr; size_t h_pinned_cap = 0;
     epde_batch* live = nullptr;
     long long launches = 0;
@@ -1608,6 +1697,7 @@ static int build_geometry(epde_ctx* c) {
             m.row = axis_row_base[d] + s;
             m.a_lo = 0; m.a_hi = nA; m.b_lo = 0; m.b_hi = nB; m.p_lo = 0; m.p_hi = npieces;
             long long width = 0;
+            m.kind = (d == last) ? 2 : (nd == 3 && d == 0) ? 0 : 1;
             if (d == last) {
                 int lo = -1, hi = -1;
                 for (int q = 0; q < npieces; ++q)
@@ -1922,7 +2012,7 @@ int epde_ctx_destroy(epde_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     for (auto& kv : c->tokens) cudaFree(kv.second);
-    c->d_geom.release(); c->d_cells.release(); c->d_seg.release(); c->d_win.release(); c->d_enc.release();
+    c->d_geom.release(); c->d_marg.release(); c->d_cells.release(); c->d_seg.release(); c->d_win.release(); c->d_enc.release();
     c->d_out.release(); c->d_partial.release(); c->d_given.release(); c->d_progs.release(); c->d_fd.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto& sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -2326,7 +2416,21 @@ int epde_batch_gram(epde_batch* b, double* dev_seg) {
         mp.g = c->geom; mp.eqs = b->d_eqs; mp.eq_list = b->d_lists + g.list_off;
         mp.cells = (const double*)c->d_cells.ptr; mp.seg = dev_seg;
         dim3 grid(c->geom.n_rows, (unsigned)g.eqs.size());
-        { KernelSpan ks(c, EPDE_KERNEL_MARGINAL); marginal_kernel<<<grid, 256, 0, c->stream>>>(mp); }
+        const size_t slab_smem = sizeof(double) * (size_t)c->geom.npieces * nacc_of(TMAX);
+        if (c->ndim == 3 && c->geom.nA >= 4 && slab_smem <= 40 * 1024) {
+            MargSlabParams sp;
+            sp.g = c->geom; sp.eqs = mp.eqs; sp.eq_list = mp.eq_list; sp.cells = mp.cells; sp.seg = dev_seg;
+            sp.eq_stride = (long long)c->geom.nA * (1 + c->geom.nB + c->geom.npieces) * nacc_of(TMAX);
+            if (c->d_marg.ensure(sizeof(double) * (size_t)sp.eq_stride * g.eqs.size())) return 1;
+            sp.part = (double*)c->d_marg.ptr;
+            KernelSpan ks(c, EPDE_KERNEL_MARGINAL);
+            marginal_slab_kernel<<<dim3(c->geom.nA, (unsigned)g.eqs.size()), 256, slab_smem, c->stream>>>(sp);
+            marginal_rows_kernel<<<grid, 64, 0, c->stream>>>(sp);
+            c->launches++;
+        } else {
+            KernelSpan ks(c, EPDE_KERNEL_MARGINAL);
+            marginal_kernel<<<grid, 256, 0, c->stream>>>(mp);
+        }
         CK(cudaGetLastError());
     }
     return 0;

@@ -333,7 +333,9 @@ def test_grid_sharding_single_gpu():
     for k in ('coef', 'n_active', 'iters'):
         assert np.array_equal(getattr(outs[0], k), getattr(outs[1], k)), k
     assert np.array_equal(outs[0].coef != 0, full.coef != 0)
-    assert_rel(outs[0].coef, full.coef, 'sharded coef', rtol=1e-8, atol=1e-14)
+    # the slabs sum their cells in another order than the whole grid: the contract tolerance (1e-6 relative)
+    # applies, random equations of this population reach ~1e-8 through their conditioning
+    assert_rel(outs[0].coef, full.coef, 'sharded coef', rtol=1e-6, atol=1e-14)
     assert_rel(outs[0].fitness_l1, full.fitness_l1, 'sharded fitness', rtol=1e-6, atol=1e-10)
     assert_rel(outs[0].stability, full.stability, 'sharded stability', rtol=1e-6, atol=1e-14)
 
