@@ -249,7 +249,7 @@ def workload_config(args, shape, eqs, evals, world):
             'evals_per_step': len(evals), 'terms_per_equation': f'{min(T)}..{max(T)} (mean {np.mean(T):.2f})',
             'distinct_tokens_mean': float(np.mean([syn.distinct_tokens(e) for e in eqs])),
             'sharding': ('grid-points along t + NCCL all-reduce' if grid_sharded else
-                         ('population round-robin, no collective' if world > 1 else 'single GPU')),
+                         ('population (cost-balanced equation lists), no collective' if world > 1 else 'single GPU')),
             'l2_policy': 'token set larger than L2' if int(np.prod(shape)) * 8 * 3 > 126e6 else
                          'L2 flushed (256 MB write) between timed steps',
             'norms': 'L1 fitness + stability (L2LRFitness, the unit of SURVEY 8d)' if getattr(args, 'norms', 'l1') == 'l1'
@@ -284,7 +284,10 @@ def run_b200(args):
         my_eqs, my_evals = eqs, evals
     else:
         lo, hi, local_shape, shard = 0, shape[0], tuple(shape), None
-        my_eqs = [eqs[i] for i in sharding.population_slice(len(eqs), rank, world)]
+        n_ev = [0] * len(eqs)
+        for e, _ in evals:
+            n_ev[e] += 1
+        my_eqs = [eqs[i] for i in sharding.population_partition([len(q) for q in eqs], n_ev, world)[rank]]
         my_evals = syn.make_evals(my_eqs)
     n_local = int(np.prod(local_shape))
 
@@ -358,6 +361,13 @@ def run_b200(args):
     launches = eng.launch_count - l0
     ktimes = eng.kernel_times()
     eng.set_timing(False)
+    # per-rank sum of kernel time per step (the step time is the slowest rank's)
+    rank_ms = torch.tensor([sum(v[0] for v in ktimes.values()) / args.steps], dtype=torch.float64, device=dev)
+    if world > 1:
+        gathered = [torch.zeros_like(rank_ms) for _ in range(world)]
+        dist.all_gather(gathered, rank_ms)
+        rank_ms = torch.cat(gathered)
+    rank_ms = [round(float(x), 3) for x in rank_ms.tolist()]
     dev_res = batch.fetch(sums.data_ptr(), want_sw=False)
     batch.close()
     total_evals = len(evals)
@@ -428,6 +438,7 @@ def run_b200(args):
             'roofline': roof(dominant),
             'roofline_other': roof(other),
             'kernel_ms_per_step': {k: v[0] / args.steps for k, v in ktimes.items()},
+            'kernel_ms_per_step_by_rank': rank_ms,
         }
         if world == 1 and not args.no_cpu_baseline:
             host_tokens = [eng.download(i) for i in range(n_tok)]

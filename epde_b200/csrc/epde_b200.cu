@@ -1031,7 +1031,9 @@ struct ResidParams {
     const double* intercept; // [n_eval]
     const double* intercept_l1;  // [n_eval]
     double* partial;         // [gridDim.x][n_eq][TMAX][3]
-    struct ResidProg* progs; // global: [n_eq] sorted programs, then [n_eq] staging (residual_prog_kernel)
+    struct ResidProg* progs; // global: [2 n_eq] sorted programs, then [2 n_eq] staging (residual_prog_kernel)
+    int* n_live;             // number of programs with evals (they come first after the sort)
+    int split;               // 1: the heaviest programs (NU * NV >= 24) become two programs of half the evals each
     int seg_eqs;             // programs per segment (shared-memory resident)
     int batch_tiles;         // tiles a CTA walks per segment before moving to the next segment
     int nbuf;                // 1 or 2 tile buffers
@@ -1247,11 +1249,15 @@ __global__ void __launch_bounds__(256) residual_prog_kernel(ResidParams p) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int nwarps = blockDim.x >> 5;
     const int TP = p.tile_pts;
-    ResidProg* tmp = p.progs + p.n_eq;                // unsorted staging area behind the sorted programs
+    ResidProg* tmp = p.progs + 2 * p.n_eq;            // unsorted staging area behind the sorted programs
     for (int le = warp; le < p.n_eq; le += nwarps) {
         const int e = p.eq_list[le];
         const EqDesc* eq = p.eqs + e;
-        ResidProg* rp = tmp + le;
+        // two slots per equation: with few equations per launch the longest (tile, program) task sets the time of
+        // every tile, so a program with many evals is cut into two programs over the SAME columns (each eval's
+        // arithmetic is unchanged, only the scheduling differs); the second slot stays empty otherwise
+        ResidProg* rp = tmp + 2 * le;
+        ResidProg* rp2 = rp + 1;
         const int T = eq->T;
         // lane d < T holds the eval id of target d
         const int my_ev = (lane < T) ? p.slot_eval[e * TMAX + lane] : -1;
@@ -1270,6 +1276,7 @@ __global__ void __launch_bounds__(256) residual_prog_kernel(ResidParams p) {
 #pragma unroll
         for (int d = 0; d < 4; ++d) used |= ((nz[0] >> (d * 8)) & 0xffu) | ((nz[1] >> (d * 8)) & 0xffu);
         const int NU = __popc(used), NV = __popc(valid);
+        const int h0 = (p.split && NV >= 3 && NU * NV >= 24) ? (NV + 1) / 2 : NV;      // evals of the first program
         // used columns in evaluation order (most slot factors first): rank of this lane's term
         int my_u = 0;
         {
@@ -1283,10 +1290,13 @@ __global__ void __launch_bounds__(256) residual_prog_kernel(ResidParams p) {
         const unsigned two = __ballot_sync(0xffffffffu, mine && my_op.z >= 0);
         const unsigned three = __ballot_sync(0xffffffffu, mine && my_op.y >= 0);
         const unsigned five = __ballot_sync(0xffffffffu, mine && my_op2.x >= 0);
-        for (int q = lane; q < TMAX * TMAX; q += 32) rp->m[q] = 0.0;
-        if (lane < TMAX) {
-            rp->op[lane] = make_int4(0, -1, -1, -1); rp->op2[lane] = make_int2(-1, -1);
-            rp->sb[lane] = 0.0; rp->sdb[lane] = 0.0; rp->term[lane] = 0; rp->dmap[lane] = 0; rp->tcol[lane] = 0;
+        for (int h = 0; h < 2; ++h) {
+            ResidProg* r = h ? rp2 : rp;
+            for (int q = lane; q < TMAX * TMAX; q += 32) r->m[q] = 0.0;
+            if (lane < TMAX) {
+                r->op[lane] = make_int4(0, -1, -1, -1); r->op2[lane] = make_int2(-1, -1);
+                r->sb[lane] = 0.0; r->sdb[lane] = 0.0; r->term[lane] = 0; r->dmap[lane] = 0; r->tcol[lane] = 0;
+            }
         }
         __syncwarp();
         if (mine) {
@@ -1295,22 +1305,24 @@ __global__ void __launch_bounds__(256) residual_prog_kernel(ResidParams p) {
             if (d.y >= 0) d.y *= TP * 8;
             if (d.z >= 0) d.z *= TP * 8;
             if (d.w >= 0) d.w *= TP * 8;
-            rp->op[my_u] = d;
+            rp->op[my_u] = d; rp2->op[my_u] = d;
             int2 d2 = my_op2;
             if (d2.x >= 0) d2.x *= TP * 8;
             if (d2.y >= 0) d2.y *= TP * 8;
-            rp->op2[my_u] = d2;
-            rp->term[my_u] = lane;
+            rp->op2[my_u] = d2; rp2->op2[my_u] = d2;
+            rp->term[my_u] = lane; rp2->term[my_u] = lane;
         }
-        if (lane <= TMAX) rp->foff[lane] = eq->fac_off[lane];
+        if (lane <= TMAX) { rp->foff[lane] = eq->fac_off[lane]; rp2->foff[lane] = eq->fac_off[lane]; }
         if (my_ev >= 0) {
-            const int dd = __popc(valid & ((1u << lane) - 1u));
+            const int dd_all = __popc(valid & ((1u << lane) - 1u));
+            ResidProg* r = dd_all >= h0 ? rp2 : rp;
+            const int dd = dd_all >= h0 ? dd_all - h0 : dd_all;
             const double b1 = p.intercept_l1[my_ev];
-            rp->sb[dd] = b1;
-            rp->sdb[dd] = b1 - p.intercept[my_ev];
-            rp->dmap[dd] = lane;
-            rp->tcol[dd] = my_u;
-            rp->m[dd * TMAX + my_u] = 1.0;
+            r->sb[dd] = b1;
+            r->sdb[dd] = b1 - p.intercept[my_ev];
+            r->dmap[dd] = lane;
+            r->tcol[dd] = my_u;
+            r->m[dd * TMAX + my_u] = 1.0;
         }
         __syncwarp();
 #pragma unroll
@@ -1319,25 +1331,35 @@ __global__ void __launch_bounds__(256) residual_prog_kernel(ResidParams p) {
             const int d = idx >> 3, j = idx & 7;
             const int uj = __shfl_sync(0xffffffffu, my_u, j);
             if (wv[h] != 0.0) {
-                const int dd = __popc(valid & ((1u << d) - 1u));
-                rp->m[dd * TMAX + uj] = -wv[h];
+                const int dd_all = __popc(valid & ((1u << d) - 1u));
+                if (dd_all >= h0) rp2->m[(dd_all - h0) * TMAX + uj] = -wv[h];
+                else rp->m[dd_all * TMAX + uj] = -wv[h];
             }
         }
         if (lane == 0) {
             const int n2 = __popc(two), n3 = five ? 2 : (three ? 1 : 0);
-            rp->NU = NU; rp->NV = NV; rp->fast = eq->fast; rp->n2 = n2; rp->n3 = n3; rp->le = le;
-            s_key[le] = (NV == 0) ? -1
-                                  : ((NU << 12) | (n2_class(n2, COARSE_CLASSES_B) << 9) |
-                                     ((COARSE_CLASSES_B ? (n3 > 0 ? 2 : 0) : n3) << 7) | ((eq->fast ? 0 : 1) << 6) | (NV << 2));
+            for (int h = 0; h < 2; ++h) {
+                ResidProg* r = h ? rp2 : rp;
+                const int nv = h ? NV - h0 : h0;
+                r->NU = NU; r->NV = nv; r->fast = eq->fast; r->n2 = n2; r->n3 = n3; r->le = le;
+                s_key[2 * le + h] = (nv == 0) ? -1
+                                              : ((NU << 12) | (n2_class(n2, COARSE_CLASSES_B) << 9) |
+                                                 ((COARSE_CLASSES_B ? (n3 > 0 ? 2 : 0) : n3) << 7) | ((eq->fast ? 0 : 1) << 6) | (nv << 2));
+            }
         }
     }
     __syncthreads();
     __threadfence_block();
-    // rank sort (keys descending, ties by list position), then copy every program to its sorted place
-    for (int le = warp; le < p.n_eq; le += nwarps) {
+    if (tid == 0) {
+        int live = 0;
+        for (int j = 0; j < 2 * p.n_eq; ++j) live += s_key[j] >= 0 ? 1 : 0;
+        *p.n_live = live;
+    }
+    // rank sort (keys descending, ties by slot), then copy every program to its sorted place
+    for (int le = warp; le < 2 * p.n_eq; le += nwarps) {
         const int k = s_key[le];
         int cnt = 0;
-        for (int j = lane; j < p.n_eq; j += 32) {
+        for (int j = lane; j < 2 * p.n_eq; j += 32) {
             const int kj = s_key[j];
             cnt += (kj > k || (kj == k && j < le)) ? 1 : 0;
         }
@@ -1390,14 +1412,15 @@ __global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p
         asm volatile("cp.async.commit_group;\n" ::: "memory");
     };
 
-    const int n_seg = (p.n_eq + p.seg_eqs - 1) / p.seg_eqs;
+    const int n_prog = *p.n_live;
+    const int n_seg = (n_prog + p.seg_eqs - 1) / p.seg_eqs;
     const int my_tiles = (p.n_tiles > (int)blockIdx.x) ? (p.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
     int k_buf = 0;                      // buffer that receives / holds the current tile
     for (int t0 = 0; t0 < my_tiles; t0 += p.batch_tiles) {
         const int nb = (my_tiles - t0) < p.batch_tiles ? (my_tiles - t0) : p.batch_tiles;
         for (int sg = 0; sg < n_seg; ++sg) {
             const int e0 = sg * p.seg_eqs;
-            const int ne = (p.n_eq - e0) < p.seg_eqs ? (p.n_eq - e0) : p.seg_eqs;
+            const int ne = (n_prog - e0) < p.seg_eqs ? (n_prog - e0) : p.seg_eqs;
             // ---- the segment's programs: global (sorted) -> shared; with one buffer the first tile goes along
             {
                 const int4* src = (const int4*)(p.progs + e0);
@@ -1849,19 +1872,21 @@ static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, 
     const int per_launch = (ne_all + n_launch - 1) / n_launch;
     for (int e0 = 0; e0 < ne_all; e0 += per_launch) {
         const int ne = std::min(per_launch, ne_all - e0);
-        const int nwarps = std::max(1, std::min(c->resid_warps, std::min(ne, seg_eqs)));
+        const int split = ne <= 64 ? 1 : 0;      // few programs per CTA: halve the longest tasks (residual_prog_kernel)
+        const int nwarps = std::max(1, std::min(c->resid_warps, std::min(split ? 2 * ne : ne, seg_eqs)));
         ResidParams p;
         memset(&p, 0, sizeof p);
         p.N = c->N; p.eqs = b->d_eqs; p.factors = b->d_factors;
         p.eq_list = b->d_lists + g.list_off + e0; p.n_eq = ne; p.U = U; p.n_tiles = (int)n_tiles; p.tile_pts = tile_pts;
         for (int u = 0; u < U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
         p.slot_eval = b->d_slot_eval; p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.intercept_l1 = b->d_b1;
-        p.seg_eqs = std::min(seg_eqs, ne); p.batch_tiles = batch_tiles;
+        p.seg_eqs = std::min(seg_eqs, split ? 2 * ne : ne); p.batch_tiles = batch_tiles; p.split = split;
         const size_t rest = (size_t)p.seg_eqs * sizeof(ResidProg) + (size_t)ne * table_eq;
         p.nbuf = (2 * tile_bytes + rest <= (size_t)c->max_smem) ? 2 : 1;
         const size_t smem = p.nbuf * tile_bytes + rest;
-        if (c->d_progs.ensure(2 * (size_t)ne * sizeof(ResidProg))) return 1;
+        if (c->d_progs.ensure(4 * (size_t)ne * sizeof(ResidProg) + 16)) return 1;
         p.progs = (ResidProg*)c->d_progs.ptr;
+        p.n_live = (int*)(p.progs + 4 * (size_t)ne);
         // one persistent CTA per SM: the tile -> CTA assignment (and with it the summation order) depends only on
         // the grid size, never on what else is in the batch
         const int grid = (int)std::min<long long>(n_tiles, (long long)c->sm_count);
@@ -1869,7 +1894,7 @@ static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, 
         p.partial = (double*)c->d_partial.ptr;
         {
             KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
-            residual_prog_kernel<<<1, 256, sizeof(int) * (size_t)ne, c->stream>>>(p);
+            residual_prog_kernel<<<1, 256, sizeof(int) * 2 * (size_t)ne, c->stream>>>(p);
         }
         CK(cudaGetLastError());
         {

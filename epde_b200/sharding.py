@@ -29,6 +29,34 @@ def population_slice(n_eq: int, rank: int, world: int):
     return list(range(rank, n_eq, world))
 
 
+def equation_cost(n_terms: int, n_evals: int) -> float:
+    """relative streaming cost of one equation: pass A does T(T+3)/2 Gram updates + ~2T term products per
+    point, pass B ~T column products and (evals) x T residual updates at ~1.7x the cost per update
+    (DESIGN.md section 6).  Only ratios matter."""
+    T = int(n_terms)
+    return T * (T + 3) / 2 + 2 * T + 1.7 * T * (int(n_evals) + 1.5)
+
+
+def population_partition(term_counts, eval_counts, world: int):
+    """cost-balanced version of :func:`population_slice`: every rank's equation list (ascending indices) from a
+    longest-processing-time greedy on :func:`equation_cost` -- deterministic, identical on every rank.
+    Populations of a few dozen equations per rank are otherwise up to ~25 % out of balance (the step time is the
+    slowest rank's)."""
+    if world <= 0:
+        raise ValueError(f'world of {world} ranks')
+    if len(term_counts) != len(eval_counts):
+        raise ValueError('one eval count per equation expected')
+    cost = [equation_cost(t, v) for t, v in zip(term_counts, eval_counts)]
+    order = sorted(range(len(cost)), key=lambda i: (-cost[i], i))
+    load = [0.0] * world
+    parts = [[] for _ in range(world)]
+    for i in order:
+        r = min(range(world), key=lambda q: (load[q], len(parts[q]), q))
+        parts[r].append(i)
+        load[r] += cost[i]
+    return [sorted(p) for p in parts]
+
+
 def grid_slab(shape, rank: int, world: int):
     """(lo, hi) rows of the time axis held by `rank`, the local inner shape and the ``shard``
     argument of :class:`epde_b200.Engine`.  Every rank gets at least 2 rows (engine minimum)."""

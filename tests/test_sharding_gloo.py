@@ -229,6 +229,20 @@ def test_partitions():
     for n, world in [(128, 8), (7, 2), (3, 4)]:
         got = sorted(i for r in range(world) for i in sharding.population_slice(n, r, world))
         assert got == list(range(n))
+    # cost-balanced partition: a permutation of the population, identical on every rank, better than round-robin
+    rng = np.random.default_rng(4)
+    T = rng.integers(2, 9, size=256).tolist()
+    V = [int(rng.integers(1, t + 1)) for t in T]
+    parts = sharding.population_partition(T, V, 8)
+    assert sorted(i for part in parts for i in part) == list(range(256))
+    assert parts == sharding.population_partition(T, V, 8) and all(part == sorted(part) for part in parts)
+    cost = [sharding.equation_cost(t, v) for t, v in zip(T, V)]
+    load = [sum(cost[i] for i in part) for part in parts]
+    rr = [sum(cost[i] for i in sharding.population_slice(256, r, 8)) for r in range(8)]
+    assert max(load) <= max(rr) and max(load) / (sum(load) / 8) < 1.01
+    assert sharding.population_partition([3, 5], [1, 2], 4) == [[1], [0], [], []]
+    with pytest.raises(ValueError):
+        sharding.population_partition([3], [1, 2], 2)
     rows = []
     for r in range(8):
         (lo, hi), local, shard = sharding.grid_slab((512, 512, 512), r, 8)
