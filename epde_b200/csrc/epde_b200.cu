@@ -1872,7 +1872,10 @@ static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, 
     const int per_launch = (ne_all + n_launch - 1) / n_launch;
     for (int e0 = 0; e0 < ne_all; e0 += per_launch) {
         const int ne = std::min(per_launch, ne_all - e0);
-        const int split = ne <= 64 ? 1 : 0;      // few programs per CTA: halve the longest tasks (residual_prog_kernel)
+        // few programs per CTA (<= 5 per warp): halve the longest tasks (residual_prog_kernel).  Measured: 32 equations
+        // per launch, slowest of 8 population shards 8.0 -> 5.5 ms; at 64 per launch the recomputed columns cost more
+        // than the tail (512^3: 91 -> 103 ms), hence the limit
+        const int split = ne <= 40 ? 1 : 0;
         const int nwarps = std::max(1, std::min(c->resid_warps, std::min(split ? 2 * ne : ne, seg_eqs)));
         ResidParams p;
         memset(&p, 0, sizeof p);
