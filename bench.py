@@ -295,9 +295,11 @@ def run_b200(args):
     eng = epde_b200.Engine(local_shape, device=local_rank, shard=shard, stream=stream.cuda_stream)
     t_up0 = time.perf_counter()
     n_tok = len(syn.token_labels(kind))
+    data_checksum = 0.0
     for i in range(n_tok):
         tk = syn.make_tokens(shape, kind, xp=torch, device=dev, seed=args.seed, axis0_range=(lo, hi), only=[i])[i]
         eng.upload_device(i, tk.data_ptr(), tk.numel())
+        data_checksum += float(tk[::4099].sum().item())      # sampled: same data on every box <=> same number
         torch.cuda.synchronize()
         del tk
     torch.cuda.empty_cache()
@@ -428,7 +430,9 @@ def run_b200(args):
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': ms_total / args.steps, 'higher_is_better': True,
             'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-            'config': workload_config(args, shape, eqs, evals, world),
+            'config': dict(workload_config(args, shape, eqs, evals, world),
+                           data_checksum_rank0=float(f'{data_checksum:.9e}'),
+                           nonzero_coefficients_rank0=int((np.asarray(dev_res.coef) != 0).sum())),
             'clocks': clocks,
             'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
                     'note': 'Engine.evaluate (C ABI epde_evaluate_batch): host CSR encodings in, host results out; '

@@ -103,11 +103,35 @@ def make_tokens(shape, kind, xp=np, device=None, noise=1e-3, seed=0, axis0_range
                         np.random.default_rng([seed, i, r]).standard_normal(row)
                 tk = tk + scale * nz
             else:
-                g = xp.Generator(device=device)
-                g.manual_seed(seed * 1000003 + i * 7919 + lo0)
-                tk = tk + scale * xp.randn(tk.shape[0], dtype=xp.float64, device=device, generator=g)
+                tk = tk + scale * _counter_normal(xp, lo0 * row, tk.shape[0], seed, i, device)
         out.append(tk.contiguous() if xp is not np else np.ascontiguousarray(tk))
     return out
+
+
+def _s64(c):
+    """a 64-bit constant as the signed value torch's int64 arithmetic wraps to"""
+    c &= (1 << 64) - 1
+    return c - (1 << 64) if c >= (1 << 63) else c
+
+
+def _counter_normal(xp, start, n, seed, token, device):
+    """standard normal noise as a pure function of (seed, token, GLOBAL point index): splitmix64 finaliser on the
+    index, two 53-bit uniforms, Box-Muller.  Unlike a device generator the values do not depend on the launch
+    geometry torch picks on a given device, and a shard of the grid sees exactly the values of the whole grid."""
+    key = _s64(seed * 0x632BE59BD9B4E019 + token * 0xD1342543DE82EF95 + 0x2545F4914F6CDD1D)
+    idx = xp.arange(start, start + n, dtype=xp.int64, device=device)
+
+    def mix(z):
+        z = z * _s64(0x9E3779B97F4A7C15) + key
+        z = (z ^ ((z >> 30) & ((1 << 34) - 1))) * _s64(0xBF58476D1CE4E5B9)
+        z = (z ^ ((z >> 27) & ((1 << 37) - 1))) * _s64(0x94D049BB133111EB)
+        return z ^ ((z >> 31) & ((1 << 33) - 1))
+
+    m53 = (1 << 53) - 1
+    u1 = (((mix(idx * 2) >> 11) & m53).to(xp.float64) + 0.5) * 2.0 ** -53
+    u2 = ((mix(idx * 2 + 1) >> 11) & m53).to(xp.float64) * 2.0 ** -53
+    del idx
+    return xp.sqrt(-2.0 * xp.log(u1)) * xp.cos(2.0 * np.pi * u2)
 
 
 def make_population(n_tokens, pop, seed=0, t_fresh=(5, 8), t_pruned=(2, 4), pruned_fraction=0.45,
