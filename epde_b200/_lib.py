@@ -52,6 +52,7 @@ SIGNATURES = {
 }
 
 _lib = None
+ABI_VERSION = 'epde_b200 0.2.0'      # must be a prefix of epde_version() (csrc/epde_b200.cu)
 
 
 class EpdeB200Error(RuntimeError):
@@ -72,10 +73,11 @@ def load():
         try:
             _build.build()
         except Exception as exc:          # noqa: BLE001
-            if not os.path.exists(path):
-                raise EpdeB200Error(
-                    f'epde_b200: CUDA library {path} is missing and could not be built ({exc}); '
-                    'there is no CPU fallback') from exc
+            # never bind a stale binary against newer ctypes signatures: argument lists may have changed
+            state = 'missing' if not os.path.exists(path) else 'older than its sources'
+            raise EpdeB200Error(
+                f'epde_b200: CUDA library {path} is {state} and could not be built ({exc}); '
+                'there is no CPU fallback') from exc
     try:
         lib = C.CDLL(path)
     except OSError as exc:
@@ -84,6 +86,10 @@ def load():
         fn = getattr(lib, name)          # AttributeError when a declared symbol is not exported
         fn.restype = res
         fn.argtypes = args
+    got = lib.epde_version().decode('utf-8', 'replace')
+    if ABI_VERSION not in got:
+        raise EpdeB200Error(f'epde_b200: {path} reports "{got}" but this package binds ABI "{ABI_VERSION}"; '
+                            'rebuild with python -m epde_b200.build --force')
     _lib = lib
     return lib
 

@@ -79,6 +79,11 @@ def evaluate_grid_sharded(engine, enc, seg, sums, group=None, want_sw=True, want
     engine's device (scratch; reusable across calls).  Returns the BatchResult (identical on every
     rank)."""
     import torch.distributed as dist
+    if seg.is_cuda and hasattr(engine, 'set_stream'):
+        # the collectives order against torch's CURRENT stream: run the kernels on that stream too, otherwise the
+        # all-reduce could start before pass A / pass B have finished (or the solve before the all-reduce)
+        import torch
+        engine.set_stream(torch.cuda.current_stream(seg.device).cuda_stream)
     with engine.batch(enc) as b:
         if seg.numel() < b.gram_size or sums.numel() < b.residual_size:
             raise ValueError(f'scratch too small: seg {seg.numel()} < {b.gram_size} or '
