@@ -4,36 +4,48 @@
 //   token cache            epde/cache/cache.py:141-524              -> HBM-resident token table
 //   term assembly          structure/factor.py:218-269, evaluators.py:92-151,
 //                          structure/main_structures.py:207-235,588-641
-//                                                                    -> gram_tile_kernel (pass A)
-//   calculate_weights      epde/supplementary.py:394-471             -> segment Grams, window_gram_kernel,
-//                                                                       lasso_solve_kernel
+//                                                                    -> build_columns (both passes)
+//   calculate_weights      epde/supplementary.py:394-471             -> gram_dmma_kernel (pass A), marginal_*,
+//                                                                       window_gram_kernel, lasso_solve_kernel
 //   PhysicsInformedLasso   operators/common/sparsity.py:20-150       -> lasso_solve_kernel
-//   L2LRFitness/L2Fitness  operators/common/fitness.py:27-183        -> residual_tile_kernel (pass B)
+//   L2LRFitness/L2Fitness  operators/common/fitness.py:27-183        -> residual_cols_kernel (pass B)
+//
+// Design (round 2): the equations of a launch group are de-duplicated into a dictionary of DISTINCT term
+// columns (a population of 128 equations with 630 term instances holds 68 distinct terms) plus a ones column.
+// Both streaming passes first build, per tile of points, the value of every distinct column ONCE in shared
+// memory (phase 1), then
+//   pass A  accumulates the Gram of the column dictionary with the FP64 tensor-core instruction
+//           (mma.sync m8n8k4 f64 = SASS DMMA.8x8x4): 8x8 column-block pairs, fragments read straight from the
+//           column tile, accumulators in registers, one warp per (<= 2 x 3 block pairs) task.  The DMMA pipe
+//           is the FP64 pipe (measured: 37.1 TFLOP/s DMMA vs 34 DFMA, not additive), but one DMMA does the
+//           work of eight warp-wide DFMAs with two operand registers, so issue slots, register bandwidth and
+//           shared-memory traffic stop being the limit.  Only the pair entries some equation needs are
+//           written to the per-cell table.
+//   pass B  evaluates each (equation, target) residual as a sparse dot over its target + surviving columns.
+// Every equation then addresses the shared pair table through its column list, so a Gram entry is computed
+// once per launch group however many equations use it, and results do not depend on batch composition
+// beyond the grouping itself.
 //
 // Data layout in HBM
 //   token t            double[N]   N = prod(inner_shape), C order, last axis contiguous
-//   cell Grams  C      per equation: [cellA][cellB][piece][NACC]   NACC = T(T+3)/2
-//                      (upper triangle of the T x T term Gram, then the T column sums)
-//   segment Grams S    per equation: [segment row][NE], NE = NACC + 1 (last = point count);
-//                      segment rows of all axes stacked.  This is the buffer that is all-reduced
-//                      under grid sharding.
-//   window Grams  Wg   per equation: [W + 1][NE]: row w = sum of the segment rows of sliding window w
-//                      (direct summation, no prefix differences: a window that holds small values
-//                      after a region of large ones keeps full relative accuracy); row W = all points.
-//
-// Execution model of the two streaming passes: a CTA stages one tile of every token the launch
-// group references in shared memory (cp.async), then each WARP evaluates a different equation on
-// that tile (lane <-> point column), so a token tile is read from L2/HBM once per group instead of
-// once per equation and all per-point operand fetches are shared-memory loads.
+//   cell table  C      per launch group: [cellA][cellB][piece][n_ent] -- n_ent = needed (column, column) pair sums
+//   segment table S    per launch group: [segment row][n_ent] (the (ones, ones) entry = point count / weight sum);
+//                      rows of all axes stacked.  This is the buffer that is all-reduced under grid sharding.
+//   window table  Wg   per launch group: [W + 1][n_ent]: row w = sum of the segment rows of sliding window w
+//                      (direct summation, no prefix differences); row W = all points (unweighted).
 //
 // No CPU fallback exists in this file: every entry point either runs the CUDA path or fails.
 #include "../../include/epde_b200.h"
 
+#include <cuda.h>
 #include <cuda_runtime.h>
+#include <cudaTypedefs.h>
 
 #include <algorithm>
+#include <array>
 #include <cmath>
 #include <cstdarg>
+#include <cstdint>
 #include <cstdio>
 #include <cstddef>
 #include <cstdlib>
@@ -50,12 +62,19 @@
 #define LASSO_MAX_ITER 20      // sparsity.py:21
 #define LASSO_TOL 1e-4         // sparsity.py:21
 
-#define TILE_ROWS 64           // rows (leading-axes index pairs) of a pass-A tile
-#define TILE_COLS 32           // columns (last axis) of a pass-A tile = warp width
-#define GRAM_WARPS 8           // warps per pass-A CTA
-#define MAXU 12                // distinct tokens per launch group (tile = MAXU x 64 x 32 doubles = 192 KB)
-#define RES_WARPS 8            // warps per pass-B CTA (8 x <= 255 registers; 12 and 16 warps measured slower)
-#define RES_TILE_MIN 1024      // points of a pass-B tile
+#define MAXU 12                // distinct tokens per launch group
+#define NBLK_MAX 10            // 8-column blocks of the column dictionary of a launch group
+#define CMAX (NBLK_MAX * 8)    // columns per launch group, ones column included
+#define MAXSF 6                // token values multiplied by a "fast" column (integer powers expanded)
+#define TILE_ROWS 64           // rows (leading-axes index pairs) of a pass-A unit (its width is chosen per grid)
+#define PT_A 128               // points per pass-A chunk = columns of the column tile
+#define PP_A (PT_A + 4)        // its pitch: == 4 (mod 16) doubles -> conflict-free DMMA fragment loads
+#define TASK_A 2               // a pass-A task covers TASK_A x TASK_B block pairs
+#define TASK_B 3
+#define GRAM_MAX_WARPS 12
+#define PT_B 256               // points per pass-B chunk
+#define PP_B (PT_B + 4)
+#define RES_WARPS 12
 
 static thread_local std::string g_err;
 
@@ -79,7 +98,7 @@ static int fail(const char* fmt, ...) {
 // ------------------------------------------------------------------------------------------
 // device-side descriptors
 // ------------------------------------------------------------------------------------------
-struct FactorDesc {          // 32 bytes
+struct FactorDesc {          // 32 bytes; factors of the generic (non-fast) columns of a launch group
     int slot;                // token slot inside the launch group's tile
     int ipow;                // integer power if power is 1, 2 or 3, else 0
     int kind;                // 0 pow, 1 sin, 2 cos, 3 inverse
@@ -88,21 +107,25 @@ struct FactorDesc {          // 32 bytes
     double param;            // freq for trig kinds
 };
 
+struct ColDesc {             // 32 bytes; one distinct term of a launch group = one column of the dictionary
+    int off[MAXSF];          // fast column: token slots of the expanded factors (u^2 * v -> u, u, v), -1 = none; the
+                             // kernels scale them to byte offsets of the slot inside a token tile when staging
+    short nf;                // number of expanded factors (fast) / factors (generic)
+    short kind;              // 0 fast, 1 generic, 2 ones column, 3 padding (all zero)
+    int gfac_off;            // generic: first factor in the group's factor array
+};
+static_assert(sizeof(ColDesc) == 32, "ColDesc is copied as int4 pairs");
+
 struct EqDesc {
     int T;
-    int fast;                // 1: every term has <= 2 factors, all kind 0 with power in {1, 2, 3}
     int group;               // launch group
-    int fac_off[TMAX + 1];   // into the batch factor array
-    long long s_off;         // doubles, into the segment-Gram table
-    long long c_off;         // doubles, into the cell-Gram scratch of its launch group
-    long long w_off;         // doubles, into the window-Gram table
-    int4 fastop[TMAX];       // fast terms IN EVALUATION ORDER (most slot factors first): slots {A, C, B, D} of
-                             // the term's factors with integer powers expanded (u^2 * v -> u, u, v); -1 = absent
-    int2 fastop2[TMAX];      // slots {E, F} of terms with five / six slot factors
-    int n2, n3;              // terms with >= 2 slot factors; depth: 0 (<= 2 factors everywhere), 1 (<= 4), 2 (<= 6)
-    unsigned char pos[TMAX]; // term index -> evaluation position
-    unsigned char perm[TMAX];// evaluation position -> term index
-    unsigned char accmap[TMAX * (TMAX + 3) / 2];   // Gram accumulator in evaluation order -> index in term order
+    int ones_col;            // column index of the ones column in the group's dictionary
+    int n_ent;               // pair entries of the group = row length of its tables
+    long long w_off;         // doubles, into the window table (start of the group's table)
+    long long pe_off;        // ints, into the pair -> entry lookup tables (start of the group's CP x CP table)
+    int cp;                  // padded column count of the group (row length of the lookup table)
+    int pad;
+    short col[TMAX + 1];     // term index -> column of the dictionary
 };
 
 struct UnitDesc {            // one CTA work unit of pass A: a (sub-)cell of the leading axes x a column chunk
@@ -111,11 +134,10 @@ struct UnitDesc {            // one CTA work unit of pass A: a (sub-)cell of the
     int col_lo, ncols;       // columns (last axis) handled, ncols <= TILE_COLS
     int cell;                // (cellA * nB + cellB)
     int piece_lo, npieces;   // pieces (sub-segments of the last axis) covered by the chunk
-    int wlog;                // >= 0: every piece of the unit is exactly 2^wlog columns wide (shuffle flush); -1: general
-    int pad1, pad2;
+    int pad0, pad1, pad2;
 };
 
-struct MargDesc {            // one output row of the segment-Gram table
+struct MargDesc {            // one output row of the segment table
     int row;                 // row in S
     int a_lo, a_hi, b_lo, b_hi, p_lo, p_hi;   // cell ranges to sum
     int kind;                // which range is the segment's: 0 = slot A, 1 = slot B, 2 = pieces
@@ -131,7 +153,7 @@ struct Geom {                // kernel-visible geometry (by value)
     int n_windows;
     int ndim;
     int max_rows;                  // largest row count of a unit (<= TILE_ROWS)
-    int aligned16;                 // 1: every tile row starts on a 16-byte boundary
+    int aligned16;                 // 1: every tile row can be fetched with 16-byte aligned bulk copies
     long long N;
     const UnitDesc* units;
     const int* piece_start;        // [npieces + 1] column bounds
@@ -140,28 +162,43 @@ struct Geom {                // kernel-visible geometry (by value)
     const int* win_hi_row;         // [W + 1] one past the last segment row
 };
 
-__host__ __device__ __forceinline__ int nacc_of(int T) { return T * (T + 3) / 2; }
-
-// index of the (i, j) product inside a Gram row; column T is the ones column
-__host__ __device__ __forceinline__ int gidx(int i, int j, int T) {
-    if (i > j) { int t = i; i = j; j = t; }
-    if (j == T) return (i == T) ? nacc_of(T) : T * (T + 1) / 2 + i;
-    return i * T - i * (i - 1) / 2 + (j - i);
-}
-
 // ------------------------------------------------------------------------------------------
-// shared-memory staging helpers
+// shared-memory / async-copy helpers (sm_100a: bulk async copies completing on an mbarrier)
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem_src));
+__device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
 }
-__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gmem_src) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem_src));
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() {
-    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+    const unsigned a = smem_addr(bar);
+    unsigned done = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(a), "r"(parity) : "memory");
+    }
+}
+// global -> shared bulk copy (TMA engine, SASS UBLKCP); bytes multiple of 16, both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, unsigned bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_addr(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ double lds_f64(unsigned a) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+}
+
+// FP64 tensor-core MMA: D(8x8) += A(8x4, row) * B(4x8, col).  Lane l holds A[l/4][l%4], B[l%4][l/4] and
+// D[l/4][2*(l%4) + {0,1}].
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
 // ------------------------------------------------------------------------------------------
@@ -179,552 +216,370 @@ __device__ __forceinline__ double apply_factor(const FactorDesc& f, double x) {
     return pow(x, f.power);
 }
 
-__device__ __forceinline__ double ipow123(double x, int ip) {
-    if (ip >= 2) { const double s = x * x; x = (ip == 3) ? s * x : s; }
-    return x;
-}
-
-// generic term: product of its factors; `pt` = tile base + point offset, slot stride `tstride`
-__device__ __forceinline__ double eval_term_generic(const FactorDesc* fac, int f0, int f1, const double* pt,
-                                                    int tstride) {
-    double v = 1.0;
-    for (int f = f0; f < f1; ++f) {
-        const FactorDesc d = fac[f];
-        v *= apply_factor(d, pt[d.slot * tstride]);
-    }
-    return v;
-}
-
-// per-warp copy of the equation being processed (shared memory)
-struct WarpProg {
-    int4 op[TMAX];           // fast terms in evaluation order: byte offsets of slots {A, C, B, D}, -1 = absent
-    int foff[TMAX + 1];      // generic path: factor ranges
-    int2 op2[TMAX];          // byte offsets of slots {E, F}
-    int T, fast, n2, n3;
-    long long c_off;         // doubles, into the cell-Gram scratch of the launch group
-    unsigned char accmap[TMAX * (TMAX + 3) / 2 + 4];
-};
-
-// ------------------------------------------------------------------------------------------
-// pass A: fused term assembly + cell Gram.
-// Persistent CTAs (one per SM) walk the units (a (sub-)cell of the leading axes x <= 32 columns of the
-// last axis): the tile of every token of the launch group is staged in shared memory once, then each
-// warp takes equations from the group's list (sorted by code variant, dynamic) and accumulates that
-// equation's cell Gram in registers, lane <-> column, looping over the tile rows.  The per-lane
-// accumulators are reduced over the columns of each last-axis piece with warp shuffles only (xor
-// butterfly when the pieces have one power-of-two width, segmented shfl_down otherwise) and written
-// to the cell table (no atomics: fixed summation order).
-// ------------------------------------------------------------------------------------------
-struct GramParams {
-    Geom g;
-    const EqDesc* eqs;
-    const FactorDesc* factors;
-    const int* eq_list;      // equations of this launch group, most terms first
-    int n_eq;
-    int U;                   // tokens of the group
-    const double* tok[MAXU];
-    double* cells;           // cell-Gram scratch of the group
-};
-
-// explicit shared-space accesses: the per-equation worker functions are not inlined, so a generic
-// pointer would cost 64-bit address arithmetic and generic loads on every operand fetch
-__device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ double lds_f64(unsigned a) {
-    double v;
-    asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
-    return v;
-}
+// Phase 1 of both passes: the value of every column of the launch group's dictionary at the points of the
+// current chunk -> column tile ct[c][p] (shared memory, row pitch ppb bytes).  Warps walk over columns (a column
+// is uniform per warp: no divergence), lanes over points: thread handles points p = lane + 32 k, k < NPL, whose
+// token values sit at tile + (slot offset) + toffb[k]; invalid (padding) points get 0 in EVERY column, the ones
+// column included, so they add nothing to any sum.  All operands are addressed in the shared window explicitly
+// (32-bit addresses, ld.shared / st.shared): no generic-pointer arithmetic in the inner loops.
+// s_cols holds the ColDesc of the group with `off` already scaled to byte offsets of the slot inside a tile.
 __device__ __forceinline__ int4 lds_v4(unsigned a) {
     int4 v;
-    asm("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
     return v;
 }
-__device__ __forceinline__ double lds_f64_volatile(unsigned a) {
-    double v;
-    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a) : "memory");
-    return v;
-}
-__device__ __forceinline__ void sts_f64_volatile(unsigned a, double v) {
+__device__ __forceinline__ void sts_f64(unsigned a, double v) {
     asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory");
 }
 
-template <int T>
-__device__ __forceinline__ void gram_accumulate(double (&acc)[T * (T + 3) / 2], const double (&c)[T]) {
-    int k = 0;
+__device__ __forceinline__ void load_cols_to_smem(ColDesc* s_cols, const ColDesc* cols, int nbuild, int tstride_b,
+                                                  int tid, int nthreads) {
+    for (int q = tid; q < nbuild; q += nthreads) {
+        ColDesc cd = cols[q];
 #pragma unroll
-    for (int i = 0; i < T; ++i)
-#pragma unroll
-        for (int j = i; j < T; ++j) { acc[k] = fma(c[i], c[j], acc[k]); ++k; }
-#pragma unroll
-    for (int i = 0; i < T; ++i) { acc[k] += c[i]; ++k; }
+        for (int f = 0; f < MAXSF; ++f) cd.off[f] = (cd.off[f] >= 0) ? cd.off[f] * tstride_b : 0;
+        s_cols[q] = cd;
+    }
 }
 
-// fast terms for R consecutive tile rows of one lane, branch free.  A fast term is a product of 1..4 token
-// values (integer powers expanded: u^2 * v = u * u * v).  Terms come in evaluation order, most factors
-// first.  N2 = number of leading terms that get a second-factor multiply, one of {0, 1, 2, T} (the class
-// >= the equation's count); DEEP 1 / 2: those N2 terms also get factors three-four / three-six.  A term inside a
-// class without that factor multiplies by 1.0 read from a small shared region of ones, so the body is
-// straight-line code the scheduler interleaves with the Gram FMAs.  ops: shared address of the int4 op
-// table (byte offsets of slots {A, C, B, D}, -1 = absent); pr: shared address of the lane's element in
-// row `row` of slot 0; rows are ROWB bytes apart; ones: shared address of >= R * ROWB bytes of 1.0.
-template <int T, int N2, int DEEP>
-struct TermOffsets {
-    int a[T];
-    int b[N2 > 0 ? N2 : 1];
-    int c[(DEEP >= 1 && N2 > 0) ? N2 : 1], d[(DEEP >= 1 && N2 > 0) ? N2 : 1];
-    int e[(DEEP >= 2 && N2 > 0) ? N2 : 1], f[(DEEP >= 2 && N2 > 0) ? N2 : 1];
+template <int NPL>
+__device__ __forceinline__ void build_columns(unsigned ct, int ppb, unsigned cols, int nbuild, const FactorDesc* gfac,
+                                              unsigned tile, int tstride_b, const int (&toffb)[NPL],
+                                              const bool (&valid)[NPL], int warp, int nwarps, int lane) {
+    for (int c = warp; c < nbuild; c += nwarps) {
+        const int4 q0 = lds_v4(cols + c * 32), q1 = lds_v4(cols + c * 32 + 16);
+        const int nf = q1.z & 0xffff, kind = q1.z >> 16;
+        double v[NPL];
+        if (kind == 0) {
+#pragma unroll
+            for (int k = 0; k < NPL; ++k) v[k] = lds_f64(tile + q0.x + toffb[k]);
+            if (nf > 1) {
+#pragma unroll
+                for (int k = 0; k < NPL; ++k) v[k] *= lds_f64(tile + q0.y + toffb[k]);
+                if (nf > 2) {
+#pragma unroll
+                    for (int k = 0; k < NPL; ++k) v[k] *= lds_f64(tile + q0.z + toffb[k]);
+                    if (nf > 3) {
+#pragma unroll
+                        for (int k = 0; k < NPL; ++k) v[k] *= lds_f64(tile + q0.w + toffb[k]);
+                        if (nf > 4) {
+#pragma unroll
+                            for (int k = 0; k < NPL; ++k) v[k] *= lds_f64(tile + q1.x + toffb[k]);
+                            if (nf > 5) {
+#pragma unroll
+                                for (int k = 0; k < NPL; ++k) v[k] *= lds_f64(tile + q1.y + toffb[k]);
+                            }
+                        }
+                    }
+                }
+            }
+        } else if (kind == 1) {
+#pragma unroll
+            for (int k = 0; k < NPL; ++k) v[k] = 1.0;
+            for (int f = 0; f < nf; ++f) {
+                const FactorDesc fd = gfac[q1.w + f];
+#pragma unroll
+                for (int k = 0; k < NPL; ++k) v[k] *= apply_factor(fd, lds_f64(tile + fd.slot * tstride_b + toffb[k]));
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < NPL; ++k) v[k] = (kind == 2) ? 1.0 : 0.0;
+        }
+        const unsigned dst = ct + c * ppb + lane * 8;
+#pragma unroll
+        for (int k = 0; k < NPL; ++k) sts_f64(dst + k * 256, valid[k] ? v[k] : 0.0);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// pass A: Gram of the column dictionary per (cell, piece), FP64 tensor cores.
+//
+// Persistent CTAs (two per SM) walk the units (a (sub-)cell of the leading axes x a chunk of <= tile_cols
+// last-axis columns).  The token tile of a unit is fetched by the TMA engine: one tensor copy per token
+// (cp.async.bulk.tensor, box = unit rows x unit columns of the token's N-d tensor map, SASS UTMALDG) completing
+// on an mbarrier; the second CTA of the SM computes while this one waits.  Every last-axis piece of the unit is a
+// RUN of rows x piece-width points with its own Gram; a run is processed in chunks of PT_A points:
+//   phase 1  all warps build the column tile ct[column][point] (build_columns),
+//   phase 2  warp (task, kpart) accumulates its <= TASK_A x TASK_B block pairs with DMMA.8x8x4 over the 4-point
+//            k-steps s == kpart (mod ksplit) of the chunk; accumulators stay in registers across the chunks of a run.
+// At the end of a run the D fragments are scattered to the cell record through the task's flush map (pair entry
+// index per (pair slot, lane, half), -1 = not needed); with ksplit > 1 the partial fragments of the kparts are first
+// summed in shared memory in kpart order.  No atomics: every table entry has one writer and a fixed summation order.
+// ------------------------------------------------------------------------------------------
+struct TaskDesc {            // 8 bytes
+    unsigned char ablk[TASK_A], bblk[TASK_B];
+    unsigned char mask;      // bit (i * TASK_B + j): block pair (ablk[i], bblk[j]) belongs to this task
+    unsigned char pad0, pad1;
+};
+#define TASK_PAIRS (TASK_A * TASK_B)
+
+struct GramParams {
+    Geom g;
+    const ColDesc* cols;     // [nbuild]: dictionary columns, zero padding up to cp, then the weight pseudo column
+    const FactorDesc* gfac;
+    int cp;                  // 8 * number of column blocks
+    int nbuild;              // columns phase 1 builds = rows of the column tile (cp, + 1 when weighted)
+    int wcol;                // weighted mode: row of the column tile holding the sample weight of each point
+    int U;                   // token slots staged per tile (weight token included)
+    const double* tok[MAXU + 1];
+    const TaskDesc* tasks;
+    int ntasks, ksplit;
+    const int* flushmap;     // [ntasks][TASK_PAIRS][32][2]
+    double* cells;           // [n_cells][n_ent]
+    int n_ent;
+    int use_tma;             // 1: token tiles come through the tensor maps below; 0: plain loads (odd last axis)
+    int box_a, box_b, box_c; // tile extents = TMA box (slot A rows, slot B rows, last-axis columns)
+    alignas(64) CUtensorMap tmap[MAXU + 1];
 };
 
-template <int T, int N2, int DEEP>
-__device__ __forceinline__ void load_term_offsets(unsigned ops, unsigned ops2, TermOffsets<T, N2, DEEP>& o) {
-#pragma unroll
-    for (int t = 0; t < T; ++t) {
-        const int4 q = lds_v4(ops + t * 16);
-        o.a[t] = q.x;
-        if (t < N2) {
-            o.b[t] = q.z;
-            if (DEEP >= 1) { o.c[t] = q.y; o.d[t] = q.w; }
-            if (DEEP >= 2) {
-                int ex, fx;
-                asm("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(ex), "=r"(fx) : "r"(ops2 + t * 8));
-                o.e[t] = ex; o.f[t] = fx;
-            }
-        }
-    }
+__device__ __forceinline__ void tma_load_tile(double* dst, const CUtensorMap* tm, int ndim, int c0, int c1, int c2, uint64_t* bar) {
+    const unsigned d = smem_addr(dst), b = smem_addr(bar);
+    if (ndim == 3)
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                     ::"r"(d), "l"(tm), "r"(b), "r"(c0), "r"(c1), "r"(c2) : "memory");
+    else if (ndim == 2)
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                     ::"r"(d), "l"(tm), "r"(b), "r"(c0), "r"(c1) : "memory");
+    else
+        asm volatile("cp.async.bulk.tensor.1d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3}], [%2];"
+                     ::"r"(d), "l"(tm), "r"(b), "r"(c0) : "memory");
 }
 
-template <int T, int N2, int DEEP, int R, int ROWB>
-__device__ __forceinline__ void fast_terms_r(const TermOffsets<T, N2, DEEP>& o, unsigned pr, unsigned ones,
-                                             double (&c)[R][T]) {
-#pragma unroll
-    for (int t = 0; t < T; ++t) {
-#pragma unroll
-        for (int r = 0; r < R; ++r) c[r][t] = lds_f64(pr + o.a[t] + r * ROWB);
-    }
-#pragma unroll
-    for (int t = 0; t < N2; ++t) {
-        const unsigned ab = (o.b[t] >= 0) ? pr + o.b[t] : ones;
-#pragma unroll
-        for (int r = 0; r < R; ++r) c[r][t] *= lds_f64(ab + r * ROWB);
-    }
-    if (DEEP >= 1) {
-#pragma unroll
-        for (int t = 0; t < N2; ++t) {
-            const unsigned ac = (o.c[t] >= 0) ? pr + o.c[t] : ones;
-            const unsigned ad = (o.d[t] >= 0) ? pr + o.d[t] : ones;
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                c[r][t] *= lds_f64(ac + r * ROWB);
-                c[r][t] *= lds_f64(ad + r * ROWB);
-            }
-        }
-    }
-    if (DEEP >= 2) {
-#pragma unroll
-        for (int t = 0; t < N2; ++t) {
-            const unsigned ae = (o.e[t] >= 0) ? pr + o.e[t] : ones;
-            const unsigned af = (o.f[t] >= 0) ? pr + o.f[t] : ones;
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                c[r][t] *= lds_f64(ae + r * ROWB);
-                c[r][t] *= lds_f64(af + r * ROWB);
-            }
-        }
-    }
-}
-
-// class of a two-factor count: the smallest of {0, 1, 2, T} that is >= n2, as an index 0..3.
-// coarse (pass B): N2 in {0, 2, T} and DEPTH in {0, 2} only -- half the code variants, so fewer instruction-cache
-// misses when the warps of a CTA run different equations, at the price of a few more multiplies by 1.0
-// (measured at 512^3: pass B 128 -> 122 ms; pass A, which is shared-memory-bandwidth bound, 53 -> 58 ms, so
-// pass A keeps the fine classes)
-#define COARSE_CLASSES_B 0
-__device__ __forceinline__ int n2_class(int n2, bool coarse) {
-    if (coarse) return n2 == 0 ? 0 : (n2 <= 2 ? 2 : 3);
-    return n2 <= 2 ? n2 : 3;
-}
-
-// flush: sum the lanes (columns) of every last-axis piece of the unit with warp shuffles (fixed tree order, no
-// shared memory) and let the first lane of each piece store its NACC sums, un-permuted through accmap.
-//   wlog >= 0: every piece is 2^wlog lanes wide and starts on a multiple of it -> xor butterfly in the lane groups;
-//   otherwise: segmented reduction by doubling; lane_piece = piece of this lane's column (-1 beyond the unit).
-template <int T>
-__device__ __forceinline__ void flush_cells(const double (&acc)[T * (T + 3) / 2], int lane, double* out, int npieces,
-                                            const unsigned char* accmap, int wlog, int lane_piece) {
-    constexpr int NACC = T * (T + 3) / 2;
-    double v[NACC];
-#pragma unroll
-    for (int k = 0; k < NACC; ++k) v[k] = acc[k];
-    bool head;
-    int pp;
-    if (wlog >= 0) {
-        for (int off = 1; off < (1 << wlog); off <<= 1) {
-#pragma unroll
-            for (int k = 0; k < NACC; ++k) v[k] += __shfl_xor_sync(0xffffffffu, v[k], off);
-        }
-        pp = lane >> wlog;
-        head = (lane & ((1 << wlog) - 1)) == 0 && pp < npieces;
-    } else {
-        for (int off = 1; off < 32; off <<= 1) {
-            const int other = __shfl_down_sync(0xffffffffu, lane_piece, off);
-            const bool take = (lane + off < 32) && (other == lane_piece);
-#pragma unroll
-            for (int k = 0; k < NACC; ++k) {
-                const double t = __shfl_down_sync(0xffffffffu, v[k], off);
-                if (take) v[k] += t;
-            }
-        }
-        const int prev = __shfl_up_sync(0xffffffffu, lane_piece, 1);
-        pp = lane_piece;
-        head = pp >= 0 && (lane == 0 || prev != lane_piece);
-    }
-    if (head) {
-        double* o = out + (long long)pp * NACC;
-#pragma unroll
-        for (int k = 0; k < NACC; ++k) o[accmap[k]] = v[k];
-    }
-    __syncwarp();
-}
-
-// fast path: every term = x^p [* y^q], p, q in {1, 2, 3}; R tile rows per iteration
-template <int T, int N2, int DEEP, int R>
-__device__ __noinline__ void gram_warp_fast(unsigned tile, unsigned ops, unsigned ops2, unsigned ones, int nrows, int lane,
-                                            double* out, int npieces, const unsigned char* accmap, int wlog,
-                                            int lane_piece) {
-    constexpr int NACC = T * (T + 3) / 2;
-    constexpr int ROWB = TILE_COLS * 8;
-    double acc[NACC];
-#pragma unroll
-    for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
-    const unsigned base = tile + lane * 8;
-    TermOffsets<T, N2, DEEP> off;
-    load_term_offsets<T, N2, DEEP>(ops, ops2, off);
-    int row = 0;
-    if (R > 1) {
-        for (; row + R <= nrows; row += R) {
-            double c[R][T];
-            fast_terms_r<T, N2, DEEP, R, ROWB>(off, base + row * ROWB, ones, c);
-#pragma unroll
-            for (int r = 0; r < R; ++r) gram_accumulate<T>(acc, c[r]);
-        }
-    }
-    for (; row < nrows; ++row) {
-        double c[1][T];
-        fast_terms_r<T, N2, DEEP, 1, ROWB>(off, base + row * ROWB, ones, c);
-        gram_accumulate<T>(acc, c[0]);
-    }
-    flush_cells<T>(acc, lane, out, npieces, accmap, wlog, lane_piece);
-}
-
-// generic path: any factor kind / power / factor count
-template <int T>
-__device__ __noinline__ void gram_warp_generic(const double* tile, int tstride, const WarpProg* wp,
-                                               const FactorDesc* fac, int nrows, int lane, double* out, int npieces,
-                                               int wlog, int lane_piece) {
-    constexpr int NACC = T * (T + 3) / 2;
-    double acc[NACC];
-#pragma unroll
-    for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
-    const double* base = tile + lane;
-    for (int row = 0; row < nrows; ++row) {
-        double c[T];
-#pragma unroll
-        for (int t = 0; t < T; ++t)
-            c[t] = eval_term_generic(fac, wp->foff[t], wp->foff[t + 1], base + row * TILE_COLS, tstride);
-        gram_accumulate<T>(acc, c);
-    }
-    flush_cells<T>(acc, lane, out, npieces, wp->accmap, wlog, lane_piece);
-}
-
-template <int T>
-__device__ __forceinline__ void gram_warp(const double* tile, int tstride, const WarpProg* wp, const FactorDesc* fac,
-                                          unsigned ones, int nrows, int lane, double* out, int npieces, int wlog,
-                                          int lane_piece) {
-    // 8-warp CTAs may use 255 registers per thread: four rows per iteration (two for the widest equations)
-    constexpr int R = T <= 6 ? 4 : 2;
-    if (wp->fast) {
-#define GWF(NN, DD) gram_warp_fast<T, (NN), (DD), R>(smem_addr(tile), smem_addr(wp->op), smem_addr(wp->op2), ones, nrows, \
-                                                     lane, out, npieces, wp->accmap, wlog, lane_piece)
-#define GWD(NN) do { if (wp->n3 == 0) GWF(NN, 0); else if (wp->n3 == 1) GWF(NN, 1); else GWF(NN, 2); } while (0)
-        switch (n2_class(wp->n2, false)) {
-            case 0: GWF(0, 0); break;
-            case 1: GWD(1); break;
-            case 2: if (T >= 2) { GWD(T >= 2 ? 2 : T); break; }
-            default: GWD(T); break;
-        }
-#undef GWD
-#undef GWF
-    } else {
-        gram_warp_generic<T>(tile, tstride, wp, fac, nrows, lane, out, npieces, wlog, lane_piece);
-    }
-}
-
-template <int NW>
-__global__ void __launch_bounds__(NW * 32, 1) gram_tile_kernel(GramParams p) {
-    extern __shared__ __align__(16) double smem[];
-    __shared__ int s_next;
-    __shared__ const double* s_tok[MAXU];
-    __shared__ __align__(16) double s_ones[128];     // 4 rows x 256 bytes of 1.0 (fast_terms_r)
-    __shared__ int s_lane_piece[TILE_COLS];
-    const int tid = threadIdx.x;
-    const int nwarps = blockDim.x >> 5;
-    const int warp = tid >> 5, lane = tid & 31;
-    for (int q = tid; q < 128; q += blockDim.x) s_ones[q] = 1.0;
-    const int tstride = p.g.max_rows * TILE_COLS;
-    double* tile = smem;                                              // [U][max_rows][32]
-    WarpProg* progs = (WarpProg*)(tile + (size_t)p.U * tstride);      // [n_eq]
-    if (tid < MAXU) s_tok[tid] = p.tok[tid];
-
-    // ---- per-equation programs, built once per (persistent) CTA: a task then starts from shared memory only
-    for (int le = warp; le < p.n_eq; le += nwarps) {
-        const EqDesc* eq = p.eqs + p.eq_list[le];
-        WarpProg* wp = progs + le;
-        if (lane < TMAX) {
-            int4 d = eq->fastop[lane];            // slots -> byte offsets inside the tile
-            d.x *= tstride * 8;
-            if (d.y >= 0) d.y *= tstride * 8;
-            if (d.z >= 0) d.z *= tstride * 8;
-            if (d.w >= 0) d.w *= tstride * 8;
-            wp->op[lane] = d;
-            int2 d2 = eq->fastop2[lane];
-            if (d2.x >= 0) d2.x *= tstride * 8;
-            if (d2.y >= 0) d2.y *= tstride * 8;
-            wp->op2[lane] = d2;
-        }
-        if (lane <= TMAX) wp->foff[lane] = eq->fac_off[lane];
-        if (lane == 0) { wp->T = eq->T; wp->fast = eq->fast; wp->n2 = eq->n2; wp->n3 = eq->n3; wp->c_off = eq->c_off; }
-        for (int k = lane; k < TMAX * (TMAX + 3) / 2; k += 32) wp->accmap[k] = eq->accmap[k];
-    }
+template <bool WEIGHTED>
+__global__ void __launch_bounds__(GRAM_MAX_WARPS * 32, 2) gram_dmma_kernel(const __grid_constant__ GramParams p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ uint64_t s_bar;
+    const int tid = threadIdx.x, nthreads = blockDim.x;
+    const int warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
+    const int tstride = (p.box_a * p.box_b * p.box_c + 15) & ~15;           // doubles per token tile (128-byte multiple)
+    double* tile = (double*)smem_raw;                                        // [U][box_a][box_b][box_c]
+    double* ctp = tile + (size_t)p.U * tstride;                              // [nbuild][PP_A]
+    ColDesc* s_cols = (ColDesc*)(ctp + (size_t)p.nbuild * PP_A);             // [nbuild]
+    double* scratch = (double*)(s_cols + p.nbuild);                          // [ntasks][ksplit - 1][TASK_PAIRS * 2][32]
+    load_cols_to_smem(s_cols, p.cols, p.nbuild, tstride * 8, tid, nthreads);
+    if (tid == 0) mbar_init(&s_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
+    const unsigned ct = smem_addr(ctp), tile_a = smem_addr(tile), cols_a = smem_addr(s_cols);
 
+    // ---- this warp's task
+    const int ntw = p.ntasks * p.ksplit;
+    const bool worker = warp < ntw;
+    const int task = worker ? warp / p.ksplit : 0, kpart = worker ? warp % p.ksplit : 0;
+    const TaskDesc td = p.tasks[task];
+    unsigned a_off[TASK_A], b_off[TASK_B];
+    const unsigned ct_base = ct + (unsigned)(((lane >> 2) * PP_A + (lane & 3)) * 8);
+#pragma unroll
+    for (int i = 0; i < TASK_A; ++i) a_off[i] = ct_base + (unsigned)(td.ablk[i] * 8 * PP_A * 8);
+#pragma unroll
+    for (int j = 0; j < TASK_B; ++j) b_off[j] = ct_base + (unsigned)(td.bblk[j] * 8 * PP_A * 8);
+    const unsigned w_off = ct + (unsigned)((p.wcol * PP_A + (lane & 3)) * 8);
+    bool on[TASK_PAIRS];
+#pragma unroll
+    for (int m = 0; m < TASK_PAIRS; ++m) on[m] = worker && ((td.mask >> m) & 1);
+    const int* fmap = p.flushmap + ((size_t)task * TASK_PAIRS * 32 + lane) * 2;
+
+    unsigned phase = 0;
     for (int ui = blockIdx.x; ui < p.g.n_units; ui += gridDim.x) {
         const UnitDesc u = p.g.units[ui];
         const int wb = u.b_hi - u.b_lo;
         const int nrows = (u.a_hi - u.a_lo) * wb;
-        // ---- stage the tile: 16-byte cp.async where rows are aligned and full, 8-byte / zero fill otherwise
-        {
-            const bool vec = p.g.aligned16 && !(u.col_lo & 1);
-            const int total = p.U * nrows * (TILE_COLS / 2);
-            for (int q = tid; q < total; q += blockDim.x) {
-                const int part = q & (TILE_COLS / 2 - 1);
-                const int rr = q / (TILE_COLS / 2);
-                const int row = rr % nrows, us = rr / nrows;
-                const int ia = u.a_lo + row / wb, ib = u.b_lo + row % wb;
-                const int c0 = part * 2;
-                const double* src = s_tok[us] + ((long long)ia * p.g.strideA + (long long)ib * p.g.strideB + u.col_lo + c0);
-                double* dst = tile + (size_t)us * tstride + row * TILE_COLS + c0;
-                if (vec && c0 + 2 <= u.ncols) {
-                    cp_async16(dst, src);
-                } else {
-                    if (c0 < u.ncols) cp_async8(dst, src); else dst[0] = 0.0;
-                    if (c0 + 1 < u.ncols) cp_async8(dst + 1, src + 1); else dst[1] = 0.0;
+        const int shift = u.col_lo & 1;             // the tile starts on the even column at or before col_lo
+        // ---- stage the token tile of the unit (everyone finished reading the previous one: chunk barriers below)
+        if (p.use_tma) {
+            if (tid == 0) {
+                fence_proxy_async();
+                mbar_expect_tx(&s_bar, (unsigned)(p.U * p.box_a * p.box_b * p.box_c * 8));
+                for (int us = 0; us < p.U; ++us) {
+                    double* dst = tile + (size_t)us * tstride;
+                    if (p.g.ndim == 3) tma_load_tile(dst, &p.tmap[us], 3, u.col_lo - shift, u.b_lo, u.a_lo, &s_bar);
+                    else if (p.g.ndim == 2) tma_load_tile(dst, &p.tmap[us], 2, u.col_lo - shift, u.b_lo, 0, &s_bar);
+                    else tma_load_tile(dst, &p.tmap[us], 1, u.col_lo - shift, 0, 0, &s_bar);
                 }
             }
-            // piece of every tile column (general flush path)
-            if (tid < TILE_COLS) {
-                int pc = -1;
-                for (int q = 0; q < u.npieces; ++q) {
-                    const int lo = p.g.piece_start[u.piece_lo + q] - u.col_lo, hi = p.g.piece_start[u.piece_lo + q + 1] - u.col_lo;
-                    if (tid >= lo && tid < hi) pc = q;
-                }
-                s_lane_piece[tid] = pc;
+            mbar_wait(&s_bar, phase);
+            phase ^= 1;
+        } else {
+            const int total = p.U * nrows * u.ncols;
+            for (int q = tid; q < total; q += nthreads) {
+                const int cc = q % u.ncols, rr = q / u.ncols;
+                const int us = rr / nrows, row = rr - us * nrows;
+                const int ra = row / wb, rb = row - ra * wb;
+                const long long off = (long long)(u.a_lo + ra) * p.g.strideA + (long long)(u.b_lo + rb) * p.g.strideB + u.col_lo + cc;
+                tile[(size_t)us * tstride + (ra * p.box_b + rb) * p.box_c + shift + cc] = __ldg(p.tok[us] + off);
             }
-            cp_async_wait_all();
-            if (tid == 0) s_next = nwarps;
             __syncthreads();
         }
-        const int lane_piece = s_lane_piece[lane];
-        int le = warp;
-        while (le < p.n_eq) {
-            const WarpProg* wp = progs + le;
-            const int T = wp->T;
-            double* out = p.cells + wp->c_off + ((long long)u.cell * p.g.npieces + u.piece_lo) * nacc_of(T);
-#define GW(TT) gram_warp<TT>(tile, tstride, wp, p.factors, smem_addr(s_ones), nrows, lane, out, u.npieces, u.wlog, lane_piece)
-            switch (T) {
-                case 1: GW(1); break;
-                case 2: GW(2); break;
-                case 3: GW(3); break;
-                case 4: GW(4); break;
-                case 5: GW(5); break;
-                case 6: GW(6); break;
-                case 7: GW(7); break;
-                default: GW(8); break;
+
+        for (int q = 0; q < u.npieces; ++q) {
+            const int ps = p.g.piece_start[u.piece_lo + q];
+            const int pw = p.g.piece_start[u.piece_lo + q + 1] - ps;
+            const int c_lo = ps - u.col_lo + shift;
+            const int npts = nrows * pw;
+            double acc[TASK_PAIRS][2];
+#pragma unroll
+            for (int m = 0; m < TASK_PAIRS; ++m) { acc[m][0] = 0.0; acc[m][1] = 0.0; }
+            for (int c0 = 0; c0 < npts; c0 += PT_A) {
+                int toffb[PT_A / 32];
+                bool valid[PT_A / 32];
+#pragma unroll
+                for (int k = 0; k < PT_A / 32; ++k) {
+                    const int pi = c0 + lane + 32 * k;
+                    valid[k] = pi < npts;
+                    const int r = pi / pw;
+                    const int ra = r / wb;
+                    toffb[k] = valid[k] ? (((ra * p.box_b + (r - ra * wb)) * p.box_c + c_lo + (pi - r * pw)) * 8) : 0;
+                }
+                build_columns<PT_A / 32>(ct, PP_A * 8, cols_a, p.nbuild, p.gfac, tile_a, tstride * 8, toffb, valid, warp, nwarps, lane);
+                __syncthreads();
+                if (worker) {
+                    const int nks = (min(PT_A, npts - c0) + 3) >> 2;
+                    for (int s = kpart; s < nks; s += p.ksplit) {
+                        double a[TASK_A], b[TASK_B];
+#pragma unroll
+                        for (int i = 0; i < TASK_A; ++i) a[i] = lds_f64(a_off[i] + s * 32);
+#pragma unroll
+                        for (int j = 0; j < TASK_B; ++j) b[j] = lds_f64(b_off[j] + s * 32);
+                        if (WEIGHTED) {
+                            const double w = lds_f64(w_off + s * 32);
+#pragma unroll
+                            for (int j = 0; j < TASK_B; ++j) b[j] *= w;
+                        }
+#pragma unroll
+                        for (int i = 0; i < TASK_A; ++i)
+#pragma unroll
+                            for (int j = 0; j < TASK_B; ++j)
+                                if (on[i * TASK_B + j]) dmma884(acc[i * TASK_B + j][0], acc[i * TASK_B + j][1], a[i], b[j]);
+                    }
+                }
+                __syncthreads();
             }
-#undef GW
-            if (lane == 0) le = atomicAdd(&s_next, 1);
-            le = __shfl_sync(0xffffffffu, le, 0);
+            // ---- flush the run
+            double* out = p.cells + ((long long)u.cell * p.g.npieces + u.piece_lo + q) * p.n_ent;
+            if (p.ksplit > 1) {
+                if (worker && kpart > 0) {
+                    double* sc = scratch + ((size_t)(task * (p.ksplit - 1) + kpart - 1) * TASK_PAIRS * 2) * 32 + lane;
+#pragma unroll
+                    for (int m = 0; m < TASK_PAIRS; ++m) { sc[(2 * m) * 32] = acc[m][0]; sc[(2 * m + 1) * 32] = acc[m][1]; }
+                }
+                __syncthreads();
+                if (worker && kpart == 0) {
+                    for (int k = 1; k < p.ksplit; ++k) {
+                        const double* sc = scratch + ((size_t)(task * (p.ksplit - 1) + k - 1) * TASK_PAIRS * 2) * 32 + lane;
+#pragma unroll
+                        for (int m = 0; m < TASK_PAIRS; ++m) { acc[m][0] += sc[(2 * m) * 32]; acc[m][1] += sc[(2 * m + 1) * 32]; }
+                    }
+                }
+            }
+            if (worker && kpart == 0) {
+#pragma unroll
+                for (int m = 0; m < TASK_PAIRS; ++m) {
+                    if (!on[m]) continue;
+                    const int e0 = __ldg(fmap + m * 64), e1 = __ldg(fmap + m * 64 + 1);
+                    if (e0 >= 0) out[e0] = acc[m][0];
+                    if (e1 >= 0) out[e1] = acc[m][1];
+                }
+            }
+            if (p.ksplit > 1) __syncthreads();      // scratch is reused by the next run
         }
-        __syncthreads();            // everyone is done with the tile before it is refilled
     }
 }
 
 // ------------------------------------------------------------------------------------------
-// marginals: segment Gram row = sum of the cell Grams of the slab, in a fixed order (deterministic)
-// grid = (n_rows, n_eq_group); block = 256: thread <-> (cell lane, Gram entry) with 256 / NACC cell lanes, so
-// consecutive threads read consecutive doubles of consecutive cells (the slab of a leading-axis row is one
-// contiguous range of the cell table) and four independent loads per thread are in flight.
+// marginals: segment row = sum of the cell records of its slab, in a fixed order (deterministic).
+// grid = (n_rows, ceil(n_ent / 128)); thread <-> pair entry, so a warp reads 256 contiguous bytes of every cell
+// record; four independent partial sums keep loads in flight.
 // ------------------------------------------------------------------------------------------
 struct MargParams {
     Geom g;
-    const EqDesc* eqs;
-    const int* eq_list;
     const double* cells;
-    double* seg;
+    double* seg;             // [n_rows][n_ent]
+    int n_ent;
 };
 
-__global__ void __launch_bounds__(256) marginal_kernel(MargParams p) {
-    __shared__ double part[256];
-    const int e = p.eq_list[blockIdx.y];
-    const EqDesc& eq = p.eqs[e];
-    const int NACC = nacc_of(eq.T);
-    const int NE = NACC + 1;
+__global__ void __launch_bounds__(128) marginal_kernel(MargParams p) {
+    const int ent = blockIdx.y * 128 + threadIdx.x;
+    if (ent >= p.n_ent) return;
     const MargDesc m = p.g.marg[blockIdx.x];
-    const int tid = threadIdx.x;
-    const int cpt = 256 / NACC;                    // cells per trip (>= 5: NACC <= 44)
-    const int sub = tid / NACC, k = tid - sub * NACC;
-    const unsigned nb = m.b_hi - m.b_lo, np = m.p_hi - m.p_lo;
-    const int ncell = (m.a_hi - m.a_lo) * (int)nb * (int)np;
-    const double* C = p.cells + eq.c_off + k;
-    auto at = [&](int q) -> double {
-        const unsigned r = (unsigned)q / np, ip = (unsigned)q - r * np;
-        const unsigned iaa = r / nb, ibb = r - iaa * nb;
-        const long long cell = ((long long)(m.a_lo + (int)iaa) * p.g.nB + (m.b_lo + (int)ibb)) * p.g.npieces + (m.p_lo + (int)ip);
-        return __ldcs(C + cell * NACC);             // read once: do not keep in L2 ahead of the token tiles
+    const int nb = m.b_hi - m.b_lo, np = m.p_hi - m.p_lo;
+    const long long inner = (long long)nb * np;
+    const long long total = (long long)(m.a_hi - m.a_lo) * inner;
+    const double* C = p.cells + ent;
+    auto at = [&](long long q) -> double {
+        const int ia = (int)(q / inner);
+        const int r = (int)(q - (long long)ia * inner);
+        const int ib = r / np, ip = r - ib * np;
+        const long long cell = ((long long)(m.a_lo + ia) * p.g.nB + (m.b_lo + ib)) * p.g.npieces + (m.p_lo + ip);
+        return __ldcs(C + cell * p.n_ent);
     };
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    if (sub < cpt) {
-        int q = sub;
-        for (; q + 3 * cpt < ncell; q += 4 * cpt) {
-            const double v0 = at(q), v1 = at(q + cpt), v2 = at(q + 2 * cpt), v3 = at(q + 3 * cpt);
-            s0 += v0; s1 += v1; s2 += v2; s3 += v3;
-        }
-        for (; q < ncell; q += cpt) s0 += at(q);
+    long long q = 0;
+    for (; q + 3 < total; q += 4) {
+        const double v0 = at(q), v1 = at(q + 1), v2 = at(q + 2), v3 = at(q + 3);
+        s0 += v0; s1 += v1; s2 += v2; s3 += v3;
     }
-    part[tid] = (s0 + s1) + (s2 + s3);
-    __syncthreads();
-    if (tid < NACC) {
-        double s = 0.0;
-        for (int j = 0; j < cpt; ++j) s += part[j * NACC + tid];
-        p.seg[eq.s_off + (long long)m.row * NE + tid] = s;
-    }
-    if (tid == 64) p.seg[eq.s_off + (long long)m.row * NE + NACC] = m.count;
+    for (; q < total; ++q) s0 += at(q);
+    p.seg[(long long)m.row * p.n_ent + ent] = (s0 + s1) + (s2 + s3);
 }
 
-// Three-axis grids: every cell belongs to one row of each axis, so the kernel above reads the cell table three
-// times.  Two steps read it once: step 1, one CTA per (slot-A cell index a, equation), walks the contiguous slab
-// [a][all b][all pieces] and leaves  tot[a], byB[a][b], byP[a][piece]  (byP in per-thread shared slots: thread
-// (cell lane, entry) always meets the same pieces); step 2 sums those over the ranges of each segment row.
-struct MargSlabParams {
-    Geom g;
-    const EqDesc* eqs;
-    const int* eq_list;
-    const double* cells;
-    double* part;            // per equation of the group: [nA][1 + nB + npieces][NACC]
-    long long eq_stride;
-    double* seg;
-};
-
-__global__ void __launch_bounds__(256) marginal_slab_kernel(MargSlabParams p) {
-    extern __shared__ double s_pp[];               // [npieces][NACC]
-    __shared__ double part[256];
-    const int a = blockIdx.x;
-    const EqDesc& eq = p.eqs[p.eq_list[blockIdx.y]];
-    const int NACC = nacc_of(eq.T);
-    const int tid = threadIdx.x;
-    const int cpt = 256 / NACC;
-    const int sub = tid / NACC, k = tid - sub * NACC;
-    const int nB = p.g.nB, np = p.g.npieces;
-    const bool act = sub < cpt;
-    if (act)
-        for (int q = sub; q < np; q += cpt) s_pp[q * NACC + k] = 0.0;
-    const double* C = p.cells + eq.c_off + (long long)a * nB * np * NACC + k;
-    double* out = p.part + (long long)blockIdx.y * p.eq_stride + (long long)a * (1 + nB + np) * NACC;
-    double tot = 0.0;
-    for (int b = 0; b < nB; ++b) {
-        double vb = 0.0;
-        if (act) {
-            const double* Cb = C + (long long)b * np * NACC;
-#pragma unroll 4
-            for (int q = sub; q < np; q += cpt) {
-                const double v = __ldcs(Cb + q * NACC);
-                vb += v;
-                s_pp[q * NACC + k] += v;
-            }
-        }
-        part[tid] = vb;
-        __syncthreads();
-        if (tid < NACC) {
-            double t = 0.0;
-            for (int j = 0; j < cpt; ++j) t += part[j * NACC + tid];
-            out[(1 + b) * NACC + tid] = t;
-            tot += t;
-        }
-        __syncthreads();
-    }
-    if (tid < NACC) out[tid] = tot;
-    if (act)
-        for (int q = sub; q < np; q += cpt) out[(1 + nB + q) * NACC + k] = s_pp[q * NACC + k];
-}
-
-// grid = (n_rows, n_eq_group), block = 64
-__global__ void __launch_bounds__(64) marginal_rows_kernel(MargSlabParams p) {
-    const EqDesc& eq = p.eqs[p.eq_list[blockIdx.y]];
-    const int NACC = nacc_of(eq.T);
-    const int NE = NACC + 1;
-    const MargDesc m = p.g.marg[blockIdx.x];
-    const int k = threadIdx.x;
-    const int rowlen = 1 + p.g.nB + p.g.npieces;
-    if (k < NACC) {
-        const double* P = p.part + (long long)blockIdx.y * p.eq_stride + k;
-        double s = 0.0;
-        if (m.kind == 0) {
-#pragma unroll 4
-            for (int a = m.a_lo; a < m.a_hi; ++a) s += P[(long long)a * rowlen * NACC];
-        } else {
-            const int lo = (m.kind == 1) ? 1 + m.b_lo : 1 + p.g.nB + m.p_lo;
-            const int n = (m.kind == 1) ? m.b_hi - m.b_lo : m.p_hi - m.p_lo;
-            for (int q = 0; q < n; ++q) {
-                double t0 = 0.0, t1 = 0.0;
-                int a = 0;
-                for (; a + 1 < p.g.nA; a += 2) {
-                    t0 += P[((long long)a * rowlen + lo + q) * NACC];
-                    t1 += P[((long long)(a + 1) * rowlen + lo + q) * NACC];
-                }
-                if (a < p.g.nA) t0 += P[((long long)a * rowlen + lo + q) * NACC];
-                s += t0 + t1;
-            }
-        }
-        p.seg[eq.s_off + (long long)m.row * NE + k] = s;
-    }
-    if (k == 63) p.seg[eq.s_off + (long long)m.row * NE + NACC] = m.count;
-}
-
-// window Gram = direct sum of the segment rows of the window; row W = every point (all of axis 0).
-// grid = (W + 1, n_eq), block = 64
+// window row = direct sum of the segment rows of the window; row W = every point (all rows of axis 0).
+// grid = (W + 1, ceil(n_ent / 128))
 struct WindowParams {
     Geom g;
-    const EqDesc* eqs;
-    const double* seg;
-    double* win;
+    const double* seg;       // [n_rows][n_ent]
+    double* win;             // [W + 1][n_ent]
+    const double* total;     // weighted mode: unweighted totals [n_ent] for row W, else null
+    int n_ent;
 };
 
-__global__ void window_gram_kernel(WindowParams p) {
-    const EqDesc& eq = p.eqs[blockIdx.y];
-    const int NE = nacc_of(eq.T) + 1;
+__global__ void __launch_bounds__(128) window_gram_kernel(WindowParams p) {
+    const int ent = blockIdx.y * 128 + threadIdx.x;
+    if (ent >= p.n_ent) return;
     const int w = blockIdx.x;
-    const int r0 = p.g.win_lo_row[w], r1 = p.g.win_hi_row[w];
-    const double* S = p.seg + eq.s_off;
-    for (int a = threadIdx.x; a < NE; a += blockDim.x) {
-        double s = 0.0;
-        for (int r = r0; r < r1; ++r) s += S[(long long)r * NE + a];
-        p.win[eq.w_off + (long long)w * NE + a] = s;
+    double s = 0.0;
+    if (w == p.g.n_windows && p.total) {
+        s = p.total[ent];
+    } else {
+        const int r0 = p.g.win_lo_row[w], r1 = p.g.win_hi_row[w];
+        for (int r = r0; r < r1; ++r) s += p.seg[(long long)r * p.n_ent + ent];
     }
+    p.win[(long long)w * p.n_ent + ent] = s;
 }
+
+// sum of ALL cell records (weighted mode: the unweighted total Gram of the LASSO sums, sparsity.py:54-55,73-76)
+// in two fixed-order steps: grid = (parts, ceil(n_ent / 128)) -> part sums, then one CTA row sums the parts.
+struct TotalParams {
+    const double* cells;     // [n_cells][n_ent]
+    double* part;            // [parts][n_ent]
+    double* total;           // [n_ent]
+    int n_cells, n_ent, parts;
+};
+
+__global__ void __launch_bounds__(128) total_part_kernel(TotalParams p) {
+    const int ent = blockIdx.y * 128 + threadIdx.x;
+    if (ent >= p.n_ent) return;
+    const long long per = ((long long)p.n_cells + p.parts - 1) / p.parts;
+    const long long lo = (long long)blockIdx.x * per, hi = min((long long)p.n_cells, lo + per);
+    double s0 = 0.0, s1 = 0.0;
+    long long q = lo;
+    for (; q + 1 < hi; q += 2) { s0 += __ldcs(p.cells + q * p.n_ent + ent); s1 += __ldcs(p.cells + (q + 1) * p.n_ent + ent); }
+    if (q < hi) s0 += __ldcs(p.cells + q * p.n_ent + ent);
+    p.part[(long long)blockIdx.x * p.n_ent + ent] = s0 + s1;
+}
+
+__global__ void __launch_bounds__(128) total_final_kernel(TotalParams p) {
+    const int ent = blockIdx.x * 128 + threadIdx.x;
+    if (ent >= p.n_ent) return;
+    double s = 0.0;
+    for (int q = 0; q < p.parts; ++q) s += p.part[(long long)q * p.n_ent + ent];
+    p.total[ent] = s;
+}
+
 // ------------------------------------------------------------------------------------------
 // solve: one CTA per eval.  calculate_weights (supplementary.py:455-469) = every window's ridge
 // system solved by a GS-lane group (Gaussian elimination with partial pivoting, as LAPACK gesv);
 // PhysicsInformedLasso.fit (sparsity.py:42-150) on the total Gram by thread 0 with the reference's
-// exact control flow.
+// exact control flow.  The equation reads the launch group's pair table through its column list.
 // ------------------------------------------------------------------------------------------
 struct SolveParams {
     Geom g;
@@ -732,7 +587,8 @@ struct SolveParams {
     const int* eval_list;
     const int* eval_eq;
     const int* eval_tgt;
-    const double* win;       // window Grams [W + 1][NE] per equation (row W = all points)
+    const double* win;       // window tables [W + 1][n_ent] per launch group (row W = all points)
+    const int* pairent;      // (column, column) -> entry lookup tables per launch group
     const int* mode;         // per eval: 0 LASSO, 1 given weights + window solves, 2 given weights only (may be null)
     const double* given_wterm;   // [n_eval][TMAX] coefficient per term index (modes 1, 2)
     const double* given_b;       // [n_eval]
@@ -762,6 +618,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
     constexpr int NG = SOLVE_THREADS / GS;
     __shared__ double Gt[KS * KS];             // total Gram of all points, symmetric K x K
     __shared__ double M[NG][GS][GS + 1];       // augmented systems
+    __shared__ int s_ent[KS * KS];             // (term | ones, term | ones) -> entry of the group's pair table
     __shared__ int cols[KS];                   // columns of the current system: active terms, then T (ones)
     __shared__ double s_coef[TMAX], s_cv[TMAX], s_mu[KS], s_cvraw[KS];
     __shared__ int s_n, s_state, s_iter, s_sweeps;
@@ -774,14 +631,16 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
     const int tgt = p.eval_tgt[ev];
     const EqDesc& eq = p.eqs[e];
     const int T = eq.T, F = T - 1;
-    const int NE = nacc_of(T) + 1;
+    const int NE = eq.n_ent;
     const int W = p.g.n_windows;
     const double* P = p.win + eq.w_off;
+    const int* pe = p.pairent + eq.pe_off;
 
-    // total Gram
     for (int q = tid; q < (T + 1) * (T + 1); q += SOLVE_THREADS) {
         const int i = q / (T + 1), j = q % (T + 1);
-        Gt[i * KS + j] = P[(long long)W * NE + gidx(i, j, T)];
+        const int en = pe[(int)eq.col[i] * eq.cp + (int)eq.col[j]];
+        s_ent[i * KS + j] = en;
+        Gt[i * KS + j] = P[(long long)W * NE + en];
     }
     if (tid == 0) {
         int n = 0;
@@ -814,13 +673,11 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
             if (lr < n) {
                 const int i = cols[lr];
                 for (int c = 0; c < n; ++c) {
-                    const int gi = gidx(i, cols[c], T);
-                    double v = Phi[gi];
+                    double v = Phi[s_ent[i * KS + cols[c]]];
                     if (c == lr) v += RIDGE;
                     Mg[lr][c] = v;
                 }
-                const int gi = gidx(i, tgt, T);
-                Mg[lr][n] = Phi[gi];
+                Mg[lr][n] = Phi[s_ent[i * KS + tgt]];
             }
             __syncwarp();
             for (int k = 0; k < n; ++k) {
@@ -833,10 +690,11 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
                     const int oi = __shfl_xor_sync(0xffffffffu, idx, off, GS);
                     if (ov > val || (ov == val && oi < idx)) { val = ov; idx = oi; }
                 }
-                if (idx != k && lr >= k && lr <= n) {
+                if (idx != k && lr >= k && lr < n) {           // lane <-> column; lane k also swaps the right-hand side
                     const double t0 = Mg[k][lr];
                     Mg[k][lr] = Mg[idx][lr];
                     Mg[idx][lr] = t0;
+                    if (lr == k) { const double t1 = Mg[k][n]; Mg[k][n] = Mg[idx][n]; Mg[idx][n] = t1; }
                 }
                 __syncwarp();
                 if (lr > k && lr < n) {
@@ -1006,503 +864,367 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
     }
 }
 
-
 // ------------------------------------------------------------------------------------------
 // pass B: residual sums per eval: sum|r|, sum|t|, sum r2^2 with r = t - (F w + b1), r2 = t - (F w + b)
-// (fitness.py:135-142 and 70-83).  Persistent CTAs walk over tiles of tile_pts consecutive points
-// (double-buffered in shared memory with cp.async).  Each CTA first builds the "residual program" of
-// every equation of the launch in shared memory (term ops, weights of every eval, masks); then, per
-// tile, its warps take equations from the list dynamically (longest first) and evaluate all evals of
-// that equation on the tile, lane <-> point, two points per decode.  Tile sums are added to a per-CTA
-// shared table in tile order (fixed order), written once per CTA and reduced by residual_final_kernel.
+// (fitness.py:135-142 and 70-83).  Persistent CTAs (one per SM) walk over chunks of PT_B consecutive points
+// (token rows of the chunk fetched with one bulk async copy per token, two stages).  Phase 1 builds the column tile
+// of the launch group's dictionary once per chunk; phase 2: warps take jobs from a shared counter:
+//   dense job   one equation of <= 8 terms with all its evals: the equation's columns are loaded into registers
+//               once per 128 points (lane <-> 4 points) and every eval is a predicated dot over them (only the
+//               non-zero coefficients issue FMAs); the <= 8 per-eval sums of the job are reduced over the warp
+//               together (reduce-scatter butterfly: 9 shuffle steps instead of 40);
+//   sparse job  one eval of a longer equation: sparse dot of its target and surviving columns read from the tile;
+//   target job  sum|t| of one distinct target column.
+// Chunk sums go to a per-CTA shared table in chunk order, written once per CTA and reduced over CTAs in CTA order by
+// residual_final_kernel: fixed summation order, no atomics on data.
 // ------------------------------------------------------------------------------------------
+#define DJ_T 8               // terms / evals of a dense job
+
+struct DenseJob {            // built on the device from the solve outputs (residual_prog_kernel)
+    short col[DJ_T];         // columns of the equation's terms
+    int T, D;                // terms, evals
+    int slot0;               // sum slot of eval 0 (the evals of a job occupy consecutive slots)
+    int pad;
+    unsigned char mask[DJ_T];// per eval: bit k set <-> w[v][k] != 0
+    unsigned char pad8[8];   // keeps the double rows 16-byte aligned
+    double b1[DJ_T];         // offset of the L1 residual
+    double delta[DJ_T];      // r2 = r + delta (b1 - intercept: non-zero only when no feature survives)
+    double w[DJ_T][DJ_T];    // w[v][k]: +1 at the target column, -coefficient at the surviving features
+};
+static_assert(sizeof(DenseJob) % 16 == 0, "DenseJob rows are read as 16-byte pieces");
+
+struct EvalJob {             // 32 bytes
+    int tcol, nnz, slot, pad;
+    double b1;
+    double delta;
+};
+
+struct ResidProgParams {
+    const EqDesc* eqs;
+    const int* eval_eq;
+    const int* eval_tgt;
+    const int* dj_eq;        // [n_dense] equation of every dense job
+    const int* dj_slot0;     // [n_dense]
+    const int* slot_ev;      // [n_slots] eval id of every sum slot (dense jobs first, then sparse evals)
+    const double* wterm;     // [n_eval][TMAX]
+    const double* intercept;
+    const double* intercept_l1;
+    DenseJob* djobs;         // [n_dense]
+    EvalJob* jobs;           // [n_sparse]
+    short* job_col;          // [n_sparse][TMAX]
+    double* job_w;           // [n_sparse][TMAX]
+    int n_dense, n_sparse, n_slots;
+};
+
+__global__ void residual_prog_kernel(ResidProgParams p) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < p.n_dense) {
+        const EqDesc& eq = p.eqs[p.dj_eq[q]];
+        DenseJob dj;
+        memset(&dj, 0, sizeof dj);
+        dj.T = eq.T; dj.slot0 = p.dj_slot0[q];
+        for (int k = 0; k < eq.T; ++k) dj.col[k] = eq.col[k];
+        int D = 0;
+        for (int s = dj.slot0; s < p.n_slots && D < DJ_T; ++s) {
+            const int ev = p.slot_ev[s];
+            if (p.eval_eq[ev] != p.dj_eq[q]) break;
+            const int tgt = p.eval_tgt[ev];
+            unsigned m = 0;
+            for (int k = 0; k < eq.T; ++k) {
+                double w = (k == tgt) ? 1.0 : -p.wterm[(long long)ev * TMAX + k];
+                if (w != 0.0) m |= 1u << k;
+                dj.w[D][k] = w;
+            }
+            dj.mask[D] = (unsigned char)m;
+            dj.b1[D] = p.intercept_l1[ev];
+            dj.delta[D] = p.intercept_l1[ev] - p.intercept[ev];
+            ++D;
+        }
+        dj.D = D;
+        p.djobs[q] = dj;
+    } else if (q < p.n_dense + p.n_sparse) {
+        const int jj = q - p.n_dense;
+        const int slot = p.n_slots - p.n_sparse + jj;
+        const int ev = p.slot_ev[slot];
+        const EqDesc& eq = p.eqs[p.eval_eq[ev]];
+        const int tgt = p.eval_tgt[ev];
+        int nnz = 0;
+        for (int t = 0; t < eq.T; ++t) {
+            const double w = p.wterm[(long long)ev * TMAX + t];
+            if (t != tgt && w != 0.0) {
+                p.job_col[(long long)jj * TMAX + nnz] = eq.col[t];
+                p.job_w[(long long)jj * TMAX + nnz] = w;
+                ++nnz;
+            }
+        }
+        EvalJob j;
+        j.tcol = eq.col[tgt]; j.nnz = nnz; j.slot = slot; j.pad = 0;
+        j.b1 = p.intercept_l1[ev];
+        j.delta = p.intercept_l1[ev] - p.intercept[ev];
+        p.jobs[jj] = j;
+    }
+}
+
 struct ResidParams {
     long long N;
-    const EqDesc* eqs;
-    const FactorDesc* factors;
-    const int* eq_list;      // equations of this launch (most terms first)
-    int n_eq;
     int U;
-    int n_tiles;
-    int tile_pts;            // points per tile (multiple of 1024)
-    const double* tok[MAXU];
-    const int* slot_eval;    // [n_eq_total][TMAX] eval id of (equation, target term) or -1
-    const double* wterm;     // [n_eval][TMAX]
-    const double* intercept; // [n_eval]
-    const double* intercept_l1;  // [n_eval]
-    double* partial;         // [gridDim.x][n_eq][TMAX][3]
-    struct ResidProg* progs; // global: [2 n_eq] sorted programs, then [2 n_eq] staging (residual_prog_kernel)
-    int* n_live;             // number of programs with evals (they come first after the sort)
-    int split;               // 1: the heaviest programs (NU * NV >= 24) become two programs of half the evals each
-    int seg_eqs;             // programs per segment (shared-memory resident)
-    int batch_tiles;         // tiles a CTA walks per segment before moving to the next segment
-    int nbuf;                // 1 or 2 tile buffers
+    const double* tok[MAXU + 1];
+    const ColDesc* cols;
+    const FactorDesc* gfac;
+    int nbuild;              // columns of the tile (cp)
+    const DenseJob* djobs;
+    int n_dense;
+    const EvalJob* jobs;
+    const short* job_col;
+    const double* job_w;
+    int n_sparse;
+    int n_slots;             // evals of the group = sum slots
+    const int* tcols;        // distinct target columns
+    int n_tcols;
+    double* partial;         // [gridDim.x][2 * n_slots + n_tcols]
+    int n_chunks;
+    int nstages;
+    int aligned;             // token vectors may be fetched with bulk copies
 };
 
-// Per-equation residual program in shared memory (16-byte aligned), COMPACTED: only the NU terms
-// some eval needs ("used": targets and surviving features) and only the NV evals that exist.
-// The residual of eval dd at a point is  r = sum_u m[dd][u] * c[u] - b1[dd]  with m = +1 at the target
-// column and -coefficient at the feature columns, so the inner loop has no data-dependent tests.
-struct ResidProg {
-    int4 op[TMAX];           // fast terms of the used columns (byte offsets of the slots inside a tile buffer)
-    double m[TMAX * TMAX];   // [dd][u]
-    double sb[TMAX], sdb[TMAX];
-    int term[TMAX];          // used column u -> term index (generic path)
-    int foff[TMAX + 1];      // factor ranges by TERM index (generic path)
-    int dmap[TMAX];          // compact eval dd -> target term d (row of the sum table)
-    int tcol[TMAX];          // compact eval dd -> used column of its target
-    int NU, NV, fast, n2;    // n2: used columns with >= 2 slot factors (they come first)
-    int n3, le, pad1, pad2;    // n3: depth over the used columns: 0 (<= 2 slot factors), 1 (<= 4), 2 (<= 6); le: list position
-    int2 op2[TMAX];            // byte offsets of slots {E, F}
-};
+#define RES_NPL (PT_B / 32)
 
-static_assert(sizeof(ResidProg) % 16 == 0, "ResidProg is copied in 16-byte pieces");
-
-template <int NU>
-__device__ __forceinline__ void residual_point_block(const double (&c)[NU], int NV, unsigned m_a, unsigned sb_a,
-                                                     unsigned sdb_a, double (&a1)[NU], double (&a3)[NU], double (&sabs)[NU]) {
+__device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
-    for (int u = 0; u < NU; ++u) sabs[u] += fabs(c[u]);
-#pragma unroll
-    for (int dd = 0; dd < NU; ++dd) {
-        if (dd < NV) {
-            double r = -lds_f64(sb_a + dd * 8);
-#pragma unroll
-            for (int u = 0; u < NU; ++u) r = fma(lds_f64(m_a + (dd * TMAX + u) * 8), c[u], r);
-            const double q = r + lds_f64(sdb_a + dd * 8);     // L2Fitness keeps the LASSO intercept (fitness.py:80)
-            a1[dd] += fabs(r);
-            a3[dd] = fma(q, q, a3[dd]);
-        }
-    }
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    return v;
 }
 
-// R points per decode: same arithmetic, weights fetched once for the R points
-template <int NU, int R, bool L2>
-__device__ __forceinline__ void residual_points(const double (&c)[R][NU], int NV, unsigned m_a, unsigned sb_a,
-                                                unsigned sdb_a, double (&a1)[NU], double (&a3)[NU], double (&sabs)[NU]) {
+// sums of 8 per-lane values over the warp, all at once: after the three exchange steps lane l holds value
+// ((l >> 4) & 1) * 4 + ((l >> 3) & 1) * 2 + ((l >> 2) & 1) summed over the 8 lanes that share its low two bits; two more
+// butterfly steps finish it.  Returns that value's warp total (the same in the 4 lanes of a group).
+__device__ __forceinline__ double warp_sum8(const double (&a)[DJ_T], int lane) {
+    double b[4], c[2];
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
 #pragma unroll
-    for (int u = 0; u < NU; ++u) {
-        if (R == 4) {
-            sabs[u] += (fabs(c[0][u]) + fabs(c[1][u])) + (fabs(c[2][u]) + fabs(c[3][u]));
-        } else {
-            double t = 0.0;
-#pragma unroll
-            for (int r = 0; r < R; ++r) t += fabs(c[r][u]);
-            sabs[u] += t;
-        }
+    for (int i = 0; i < 4; ++i) {
+        const double keep = h16 ? a[i + 4] : a[i], give = h16 ? a[i] : a[i + 4];
+        b[i] = keep + __shfl_xor_sync(0xffffffffu, give, 16);
     }
 #pragma unroll
-    for (int dd = 0; dd < NU; ++dd) {
-        if (dd < NV) {
-            const double nb = -lds_f64(sb_a + dd * 8);
-            double rr[R];
-#pragma unroll
-            for (int r = 0; r < R; ++r) rr[r] = nb;
-#pragma unroll
-            for (int u = 0; u < NU; ++u) {
-                const double w = lds_f64(m_a + (dd * TMAX + u) * 8);
-#pragma unroll
-                for (int r = 0; r < R; ++r) rr[r] = fma(w, c[r][u], rr[r]);
-            }
-            if (!L2) {      // L1 norms only (L2LRFitness, fitness.py:142): no sum of squares
-                if (R == 4) a1[dd] += (fabs(rr[0]) + fabs(rr[1])) + (fabs(rr[2]) + fabs(rr[3]));
-                else if (R == 2) a1[dd] += fabs(rr[0]) + fabs(rr[1]);
-                else a1[dd] += fabs(rr[0]);
-                continue;
-            }
-            const double db = lds_f64(sdb_a + dd * 8);        // L2Fitness keeps the LASSO intercept (fitness.py:80)
-            // pairwise (fixed order) instead of a serial chain: the R points are independent
-            double q[R];
-#pragma unroll
-            for (int r = 0; r < R; ++r) q[r] = rr[r] + db;
-            if (R == 4) {
-                a1[dd] += (fabs(rr[0]) + fabs(rr[1])) + (fabs(rr[2]) + fabs(rr[3]));
-                a3[dd] += fma(q[0], q[0], q[1] * q[1]) + fma(q[2], q[2], q[3] * q[3]);
-            } else if (R == 2) {
-                a1[dd] += fabs(rr[0]) + fabs(rr[1]);
-                a3[dd] += fma(q[0], q[0], q[1] * q[1]);
-            } else {
-                double s1 = 0.0, s3 = a3[dd];
-#pragma unroll
-                for (int r = 0; r < R; ++r) { s1 += fabs(rr[r]); s3 = fma(q[r], q[r], s3); }
-                a1[dd] += s1;
-                a3[dd] = s3;
-            }
-        }
+    for (int i = 0; i < 2; ++i) {
+        const double keep = h8 ? b[i + 2] : b[i], give = h8 ? b[i] : b[i + 2];
+        c[i] = keep + __shfl_xor_sync(0xffffffffu, give, 8);
     }
+    const double keep = h4 ? c[1] : c[0], give = h4 ? c[0] : c[1];
+    double d = keep + __shfl_xor_sync(0xffffffffu, give, 4);
+    d += __shfl_xor_sync(0xffffffffu, d, 2);
+    d += __shfl_xor_sync(0xffffffffu, d, 1);
+    return d;
 }
 
-template <int NU, bool L2>
-__device__ __forceinline__ void residual_reduce(const double (&a1)[NU], const double (&a3)[NU], const double (&sabs)[NU],
-                                                const ResidProg* rp, int NV, int lane, double* table_row) {
-    double t_abs[NU];
-#pragma unroll
-    for (int u = 0; u < NU; ++u) {
-        double v = sabs[u];
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
-        t_abs[u] = v;
-    }
-#pragma unroll
-    for (int dd = 0; dd < NU; ++dd) {
-        if (dd < NV) {
-            double v1 = a1[dd], v3 = a3[dd];
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                v1 += __shfl_xor_sync(0xffffffffu, v1, off);
-                if (L2) v3 += __shfl_xor_sync(0xffffffffu, v3, off);
-            }
-            if (lane == 0) {
-                const int d = rp->dmap[dd], tc = rp->tcol[dd];
-                double ta = 0.0;
-#pragma unroll
-                for (int u = 0; u < NU; ++u) if (u == tc) ta = t_abs[u];
-                table_row[d * 3 + 0] += v1;
-                table_row[d * 3 + 1] += ta;
-                table_row[d * 3 + 2] += v3;
-            }
+__device__ __forceinline__ void resid_stage_issue(const ResidParams& p, long long chunk, double* tile, uint64_t* bar,
+                                                  int tid, int nthreads) {
+    const long long lo = chunk * PT_B;
+    const int npts = (int)min((long long)PT_B, p.N - lo);
+    if (p.aligned) {
+        const unsigned bytes = (unsigned)(((npts + 1) & ~1) * 8);
+        if (tid < 32) {
+            if (tid == 0) mbar_expect_tx(bar, bytes * (unsigned)p.U);
+            __syncwarp();
+            if (tid < p.U) bulk_g2s(tile + (size_t)tid * PT_B, p.tok[tid] + lo, bytes, bar);
         }
-    }
-}
-
-// one (tile, equation) task, fast terms; returns through the shared table row
-template <int NU, int N2, int DEEP, bool L2>
-__device__ __noinline__ void residual_task_fast(unsigned tile, unsigned prog, unsigned ones, const ResidProg* rp, int NV,
-                                                int npts, int lane, double* table_row) {
-    constexpr int R = (NU <= 6) ? 4 : 2;      // (4 at NU 7, 8 in the L1-only build spills: measured 116 vs 99 ms)
-    const unsigned m_a = prog + (unsigned)offsetof(ResidProg, m);
-    const unsigned sb_a = prog + (unsigned)offsetof(ResidProg, sb);
-    const unsigned sdb_a = prog + (unsigned)offsetof(ResidProg, sdb);
-    double a1[NU], a3[NU], sabs[NU];
-#pragma unroll
-    for (int k = 0; k < NU; ++k) { a1[k] = 0.0; a3[k] = 0.0; sabs[k] = 0.0; }
-    TermOffsets<NU, N2, DEEP> off;
-    load_term_offsets<NU, N2, DEEP>(prog, prog + (unsigned)offsetof(ResidProg, op2), off);
-    const int nfull = npts - npts % (32 * R);
-    int i = lane;
-    for (; i < nfull; i += 32 * R) {
-        double c[R][NU];
-        fast_terms_r<NU, N2, DEEP, R, 256>(off, tile + i * 8, ones, c);
-        residual_points<NU, R, L2>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
-    }
-    for (; i < npts; i += 32) {
-        double c[1][NU];
-        fast_terms_r<NU, N2, DEEP, 1, 256>(off, tile + i * 8, ones, c);
-        residual_points<NU, 1, L2>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
-    }
-    residual_reduce<NU, L2>(a1, a3, sabs, rp, NV, lane, table_row);
-}
-
-// same, generic terms (any kind / power / factor count)
-template <int NU, bool L2>
-__device__ __noinline__ void residual_task_generic(const double* tile_g, int tile_pts, unsigned prog, const ResidProg* rp,
-                                                   const FactorDesc* fac, int NV, int npts, int lane, double* table_row) {
-    const unsigned m_a = prog + (unsigned)offsetof(ResidProg, m);
-    const unsigned sb_a = prog + (unsigned)offsetof(ResidProg, sb);
-    const unsigned sdb_a = prog + (unsigned)offsetof(ResidProg, sdb);
-    double a1[NU], a3[NU], sabs[NU];
-#pragma unroll
-    for (int k = 0; k < NU; ++k) { a1[k] = 0.0; a3[k] = 0.0; sabs[k] = 0.0; }
-    for (int i = lane; i < npts; i += 32) {
-        double c[1][NU];
-#pragma unroll
-        for (int u = 0; u < NU; ++u) {
-            const int t = rp->term[u];
-            c[0][u] = eval_term_generic(fac, rp->foff[t], rp->foff[t + 1], tile_g + i, tile_pts);
-        }
-        residual_points<NU, 1, L2>(c, NV, m_a, sb_a, sdb_a, a1, a3, sabs);
-    }
-    residual_reduce<NU, L2>(a1, a3, sabs, rp, NV, lane, table_row);
-}
-
-template <int NU, bool L2>
-__device__ __forceinline__ void residual_task(unsigned tile, const double* tile_g, int tile_pts, unsigned prog, unsigned ones,
-                                              const ResidProg* rp, const FactorDesc* fac, int npts, int lane,
-                                              double* table_row) {
-    if (rp->fast) {
-#define RTF(NN, DD) residual_task_fast<NU, (NN), (DD), L2>(tile, prog, ones, rp, rp->NV, npts, lane, table_row)
-#if COARSE_CLASSES_B
-#define RTD(NN) do { if (rp->n3 == 0) RTF(NN, 0); else RTF(NN, 2); } while (0)
-#else
-#define RTD(NN) do { if (rp->n3 == 0) RTF(NN, 0); else if (rp->n3 == 1) RTF(NN, 1); else RTF(NN, 2); } while (0)
-#endif
-        switch (n2_class(rp->n2, COARSE_CLASSES_B)) {
-            case 0: RTF(0, 0); break;
-#if !COARSE_CLASSES_B
-            case 1: RTD(1); break;
-#endif
-            case 2: if (NU >= 2) { RTD(NU >= 2 ? 2 : NU); break; }
-            default: RTD(NU); break;
-        }
-#undef RTD
-#undef RTF
     } else {
-        residual_task_generic<NU, L2>(tile_g, tile_pts, prog, rp, fac, rp->NV, npts, lane, table_row);
+        for (int q = tid; q < p.U * npts; q += nthreads) {
+            const int us = q / npts, i = q - us * npts;
+            tile[(size_t)us * PT_B + i] = __ldg(p.tok[us] + lo + i);
+        }
     }
 }
 
-// program kernel (one CTA): builds the residual program of every equation of the launch from the solve outputs and
-// stores them in global memory SORTED by code variant (heaviest first), so that a segment of consecutive programs
-// runs (almost) one code variant with tasks of similar length.
-__global__ void __launch_bounds__(256) residual_prog_kernel(ResidParams p) {
-    extern __shared__ int s_key[];                    // [n_eq]
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nwarps = blockDim.x >> 5;
-    const int TP = p.tile_pts;
-    ResidProg* tmp = p.progs + 2 * p.n_eq;            // unsorted staging area behind the sorted programs
-    for (int le = warp; le < p.n_eq; le += nwarps) {
-        const int e = p.eq_list[le];
-        const EqDesc* eq = p.eqs + e;
-        // two slots per equation: with few equations per launch the longest (tile, program) task sets the time of
-        // every tile, so a program with many evals is cut into two programs over the SAME columns (each eval's
-        // arithmetic is unchanged, only the scheduling differs); the second slot stays empty otherwise
-        ResidProg* rp = tmp + 2 * le;
-        ResidProg* rp2 = rp + 1;
-        const int T = eq->T;
-        // lane d < T holds the eval id of target d
-        const int my_ev = (lane < T) ? p.slot_eval[e * TMAX + lane] : -1;
-        const unsigned valid = __ballot_sync(0xffffffffu, my_ev >= 0);
-        double wv[2];
-        unsigned nz[2];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const int idx = lane + 32 * h;
-            const int d = idx >> 3, j = idx & 7;
-            const int evd = __shfl_sync(0xffffffffu, my_ev, d);
-            wv[h] = (evd >= 0 && j < T) ? p.wterm[(long long)evd * TMAX + j] : 0.0;
-            nz[h] = __ballot_sync(0xffffffffu, wv[h] != 0.0);
-        }
-        unsigned used = valid;
-#pragma unroll
-        for (int d = 0; d < 4; ++d) used |= ((nz[0] >> (d * 8)) & 0xffu) | ((nz[1] >> (d * 8)) & 0xffu);
-        const int NU = __popc(used), NV = __popc(valid);
-        const int h0 = (p.split && NV >= 3 && NU * NV >= 24) ? (NV + 1) / 2 : NV;      // evals of the first program
-        // used columns in evaluation order (most slot factors first): rank of this lane's term
-        int my_u = 0;
-        {
-            const int my_pos = (lane < T) ? eq->pos[lane] : 0;
-            for (int t2 = 0; t2 < T; ++t2)
-                if ((used >> t2 & 1u) && eq->pos[t2] < my_pos) ++my_u;
-        }
-        const int4 my_op = (lane < T) ? eq->fastop[eq->pos[lane]] : make_int4(0, -1, -1, -1);
-        const int2 my_op2 = (lane < T) ? eq->fastop2[eq->pos[lane]] : make_int2(-1, -1);
-        const bool mine = lane < T && (used >> lane & 1u);
-        const unsigned two = __ballot_sync(0xffffffffu, mine && my_op.z >= 0);
-        const unsigned three = __ballot_sync(0xffffffffu, mine && my_op.y >= 0);
-        const unsigned five = __ballot_sync(0xffffffffu, mine && my_op2.x >= 0);
-        for (int h = 0; h < 2; ++h) {
-            ResidProg* r = h ? rp2 : rp;
-            for (int q = lane; q < TMAX * TMAX; q += 32) r->m[q] = 0.0;
-            if (lane < TMAX) {
-                r->op[lane] = make_int4(0, -1, -1, -1); r->op2[lane] = make_int2(-1, -1);
-                r->sb[lane] = 0.0; r->sdb[lane] = 0.0; r->term[lane] = 0; r->dmap[lane] = 0; r->tcol[lane] = 0;
-            }
-        }
-        __syncwarp();
-        if (mine) {
-            int4 d = my_op;
-            d.x *= TP * 8;
-            if (d.y >= 0) d.y *= TP * 8;
-            if (d.z >= 0) d.z *= TP * 8;
-            if (d.w >= 0) d.w *= TP * 8;
-            rp->op[my_u] = d; rp2->op[my_u] = d;
-            int2 d2 = my_op2;
-            if (d2.x >= 0) d2.x *= TP * 8;
-            if (d2.y >= 0) d2.y *= TP * 8;
-            rp->op2[my_u] = d2; rp2->op2[my_u] = d2;
-            rp->term[my_u] = lane; rp2->term[my_u] = lane;
-        }
-        if (lane <= TMAX) { rp->foff[lane] = eq->fac_off[lane]; rp2->foff[lane] = eq->fac_off[lane]; }
-        if (my_ev >= 0) {
-            const int dd_all = __popc(valid & ((1u << lane) - 1u));
-            ResidProg* r = dd_all >= h0 ? rp2 : rp;
-            const int dd = dd_all >= h0 ? dd_all - h0 : dd_all;
-            const double b1 = p.intercept_l1[my_ev];
-            r->sb[dd] = b1;
-            r->sdb[dd] = b1 - p.intercept[my_ev];
-            r->dmap[dd] = lane;
-            r->tcol[dd] = my_u;
-            r->m[dd * TMAX + my_u] = 1.0;
-        }
-        __syncwarp();
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const int idx = lane + 32 * h;
-            const int d = idx >> 3, j = idx & 7;
-            const int uj = __shfl_sync(0xffffffffu, my_u, j);
-            if (wv[h] != 0.0) {
-                const int dd_all = __popc(valid & ((1u << d) - 1u));
-                if (dd_all >= h0) rp2->m[(dd_all - h0) * TMAX + uj] = -wv[h];
-                else rp->m[dd_all * TMAX + uj] = -wv[h];
-            }
-        }
-        if (lane == 0) {
-            const int n2 = __popc(two), n3 = five ? 2 : (three ? 1 : 0);
-            for (int h = 0; h < 2; ++h) {
-                ResidProg* r = h ? rp2 : rp;
-                const int nv = h ? NV - h0 : h0;
-                r->NU = NU; r->NV = nv; r->fast = eq->fast; r->n2 = n2; r->n3 = n3; r->le = le;
-                s_key[2 * le + h] = (nv == 0) ? -1
-                                              : ((NU << 12) | (n2_class(n2, COARSE_CLASSES_B) << 9) |
-                                                 ((COARSE_CLASSES_B ? (n3 > 0 ? 2 : 0) : n3) << 7) | ((eq->fast ? 0 : 1) << 6) | (nv << 2));
-            }
-        }
-    }
-    __syncthreads();
-    __threadfence_block();
-    if (tid == 0) {
-        int live = 0;
-        for (int j = 0; j < 2 * p.n_eq; ++j) live += s_key[j] >= 0 ? 1 : 0;
-        *p.n_live = live;
-    }
-    // rank sort (keys descending, ties by slot), then copy every program to its sorted place
-    for (int le = warp; le < 2 * p.n_eq; le += nwarps) {
-        const int k = s_key[le];
-        int cnt = 0;
-        for (int j = lane; j < 2 * p.n_eq; j += 32) {
-            const int kj = s_key[j];
-            cnt += (kj > k || (kj == k && j < le)) ? 1 : 0;
-        }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
-        const int4* src = (const int4*)(tmp + le);
-        int4* dst = (int4*)(p.progs + cnt);
-        for (int q = lane; q < (int)(sizeof(ResidProg) / 16); q += 32) dst[q] = src[q];
-    }
-}
-
-// main kernel.  Persistent CTAs (one per SM) own a fixed set of tiles (tile b, b + grid, ...), taken in batches of
-// `batch_tiles`.  For every batch the CTA walks the sorted program list segment by segment (`seg_eqs` programs,
-// copied from global memory into shared memory), and for every segment over the tiles of the batch (double
-// buffered cp.async; the re-reads of a batch come from L2): all warps of the CTA therefore execute one code
-// variant on tasks of similar length for batch_tiles tiles in a row -- measured 1.5x faster per task than mixing
-// all variants on every tile (instruction cache, tail of the slowest warp).  Per equation the tiles are still
-// accumulated in increasing order into the CTA's shared table, so the sums do not depend on the segmenting.
-template <int NW, bool L2>
-__global__ void __launch_bounds__(NW * 32, 1) residual_tile_kernel(ResidParams p) {
-    extern __shared__ __align__(16) double smem[];
-    __shared__ const double* s_tok[MAXU];
+template <bool L2>
+__global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidParams p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ uint64_t s_bar[2];
     __shared__ int s_next;
-    __shared__ __align__(16) double s_ones[128];     // 4 rows x 256 bytes of 1.0 (fast_terms_r)
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    for (int q = tid; q < 128; q += blockDim.x) s_ones[q] = 1.0;
-    const int nwarps = blockDim.x >> 5;
-    const int TP = p.tile_pts;
-    const size_t buf_doubles = (size_t)p.U * TP;
-    double* buf0 = smem;                                                       // [nbuf][U][tile_pts]
-    ResidProg* progs = (ResidProg*)(smem + (size_t)p.nbuf * buf_doubles);      // [seg_eqs]
-    double* table = (double*)(progs + p.seg_eqs);                              // [n_eq][TMAX][3]
-    if (tid < MAXU) s_tok[tid] = p.tok[tid];
-    for (int q = tid; q < p.n_eq * TMAX * 3; q += blockDim.x) table[q] = 0.0;
+    const int tid = threadIdx.x, nthreads = blockDim.x;
+    const int warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
+    double* tiles = (double*)smem_raw;                                        // [nstages][U][PT_B]
+    double* ctp = tiles + (size_t)p.nstages * p.U * PT_B;                     // [nbuild][PP_B]
+    ColDesc* s_cols = (ColDesc*)(ctp + (size_t)p.nbuild * PP_B);              // [nbuild]
+    double* s_sum = (double*)(s_cols + p.nbuild);                             // [2 n_slots + n_tcols]
+    const int nsum = 2 * p.n_slots + p.n_tcols;
+    load_cols_to_smem(s_cols, p.cols, p.nbuild, PT_B * 8, tid, nthreads);
+    for (int q = tid; q < nsum; q += nthreads) s_sum[q] = 0.0;
+    if (tid == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
+    const unsigned ct = smem_addr(ctp), cols_a = smem_addr(s_cols);
 
-    auto issue = [&](int tI, double* dst_buf) {
-        const long long start = (long long)tI * TP;
-        const int npts = (int)((p.N - start) < TP ? (p.N - start) : TP);
-        const int half = TP / 2;
-        const int total = p.U * half;
-        for (int q = tid; q < total; q += blockDim.x) {
-            const int us = q / half, part = q - us * half;
-            const int c0 = part * 2;
-            const double* src = s_tok[us] + start + c0;
-            double* dst = dst_buf + (size_t)us * TP + c0;
-            if (c0 + 2 <= npts) cp_async16(dst, src);
-            else if (c0 < npts) cp_async8(dst, src);
-        }
-        asm volatile("cp.async.commit_group;\n" ::: "memory");
-    };
-
-    const int n_prog = *p.n_live;
-    const int n_seg = (n_prog + p.seg_eqs - 1) / p.seg_eqs;
-    const int my_tiles = (p.n_tiles > (int)blockIdx.x) ? (p.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-    int k_buf = 0;                      // buffer that receives / holds the current tile
-    for (int t0 = 0; t0 < my_tiles; t0 += p.batch_tiles) {
-        const int nb = (my_tiles - t0) < p.batch_tiles ? (my_tiles - t0) : p.batch_tiles;
-        for (int sg = 0; sg < n_seg; ++sg) {
-            const int e0 = sg * p.seg_eqs;
-            const int ne = (n_prog - e0) < p.seg_eqs ? (n_prog - e0) : p.seg_eqs;
-            // ---- the segment's programs: global (sorted) -> shared; with one buffer the first tile goes along
-            {
-                const int4* src = (const int4*)(p.progs + e0);
-                int4* dst = (int4*)progs;
-                const int n16 = ne * (int)(sizeof(ResidProg) / 16);
-                for (int q = tid; q < n16; q += blockDim.x) cp_async16(dst + q, src + q);
-                // first tile of the (batch, segment) walk; with two buffers the previous walk may have prefetched it
-                if (p.nbuf == 1 || (t0 == 0 && sg == 0)) issue((int)blockIdx.x + t0 * (int)gridDim.x, buf0 + (size_t)k_buf * buf_doubles);
-                else asm volatile("cp.async.commit_group;\n" ::: "memory");
+    const bool async = p.aligned != 0;
+    unsigned phase[2] = {0, 0};
+    int it = 0;
+    if (p.nstages == 2 && (long long)blockIdx.x < p.n_chunks) resid_stage_issue(p, blockIdx.x, tiles, &s_bar[0], tid, nthreads);
+    const int njobs_all = p.n_dense + p.n_sparse + p.n_tcols;
+    for (long long ci = blockIdx.x; ci < p.n_chunks; ci += gridDim.x, ++it) {
+        const int st = (p.nstages == 2) ? (it & 1) : 0;
+        double* tile = tiles + (size_t)st * p.U * PT_B;
+        if (p.nstages == 2) {
+            const long long cn = ci + gridDim.x;
+            if (cn < p.n_chunks) {
+                if (async) fence_proxy_async();
+                resid_stage_issue(p, cn, tiles + (size_t)(st ^ 1) * p.U * PT_B, &s_bar[st ^ 1], tid, nthreads);
             }
-            for (int k = 0; k < nb; ++k) {
-                double* cur = buf0 + (size_t)k_buf * buf_doubles;
-                const int tI = (int)blockIdx.x + (t0 + k) * (int)gridDim.x;
-                // ---- prefetch the next tile of the walk into the other buffer
-                int nxt = -1;
-                if (k + 1 < nb) nxt = tI + (int)gridDim.x;
-                else if (sg + 1 < n_seg) nxt = (int)blockIdx.x + t0 * (int)gridDim.x;
-                else if (t0 + nb < my_tiles) nxt = (int)blockIdx.x + (t0 + nb) * (int)gridDim.x;
-                if (p.nbuf == 2 && nxt >= 0) {
-                    issue(nxt, buf0 + (size_t)(k_buf ^ 1) * buf_doubles);
-                    asm volatile("cp.async.wait_group 1;\n" ::: "memory");
-                } else {
-                    if (p.nbuf == 1 && k > 0) issue(tI, cur);
-                    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-                }
-                if (tid == 0) s_next = nwarps;
-                __syncthreads();
-                const long long start = (long long)tI * TP;
-                const int npts = (int)((p.N - start) < TP ? (p.N - start) : TP);
-                const unsigned cur_s = smem_addr(cur);
-                int ti = warp;
-                while (ti < ne) {
-                    const ResidProg* rp = progs + ti;
-                    if (rp->NV > 0) {
-                        const unsigned prog_s = smem_addr(rp);
-                        double* row = table + (size_t)rp->le * TMAX * 3;
-#define RT(UU) residual_task<UU, L2>(cur_s, cur, TP, prog_s, smem_addr(s_ones), rp, p.factors, npts, lane, row)
-                        switch (rp->NU) {
-                            case 1: RT(1); break;
-                            case 2: RT(2); break;
-                            case 3: RT(3); break;
-                            case 4: RT(4); break;
-                            case 5: RT(5); break;
-                            case 6: RT(6); break;
-                            case 7: RT(7); break;
-                            default: RT(8); break;
+        } else {
+            if (async) fence_proxy_async();
+            resid_stage_issue(p, ci, tile, &s_bar[0], tid, nthreads);
+        }
+        if (async) { mbar_wait(&s_bar[st], phase[st]); phase[st] ^= 1; }
+        else __syncthreads();
+
+        const int npts = (int)min((long long)PT_B, p.N - ci * PT_B);
+        {
+            int toffb[RES_NPL];
+            bool valid[RES_NPL];
+#pragma unroll
+            for (int k = 0; k < RES_NPL; ++k) { valid[k] = lane + 32 * k < npts; toffb[k] = valid[k] ? (lane + 32 * k) * 8 : 0; }
+            build_columns<RES_NPL>(ct, PP_B * 8, cols_a, p.nbuild, p.gfac, smem_addr(tile), PT_B * 8, toffb, valid, warp, nwarps, lane);
+        }
+        if (tid == 0) s_next = 0;
+        __syncthreads();
+
+        const unsigned cl = ct + lane * 8;
+        for (;;) {
+            int jj = 0;
+            if (lane == 0) jj = atomicAdd(&s_next, 1);
+            jj = __shfl_sync(0xffffffffu, jj, 0);
+            if (jj >= njobs_all) break;
+            if (jj < p.n_dense) {
+                // ---------------- dense job: one equation, all its evals
+                const DenseJob* dj = p.djobs + jj;
+                const int4 cq = *(const int4*)dj->col;
+                const int T = dj->T, D = dj->D;
+                unsigned coff[DJ_T];
+                coff[0] = (cq.x & 0xffff) * (PP_B * 8); coff[1] = ((unsigned)cq.x >> 16) * (PP_B * 8);
+                coff[2] = (cq.y & 0xffff) * (PP_B * 8); coff[3] = ((unsigned)cq.y >> 16) * (PP_B * 8);
+                coff[4] = (cq.z & 0xffff) * (PP_B * 8); coff[5] = ((unsigned)cq.z >> 16) * (PP_B * 8);
+                coff[6] = (cq.w & 0xffff) * (PP_B * 8); coff[7] = ((unsigned)cq.w >> 16) * (PP_B * 8);
+                const uint2 mq = *(const uint2*)dj->mask;
+                double a1[DJ_T], a2[DJ_T];
+#pragma unroll
+                for (int v = 0; v < DJ_T; ++v) { a1[v] = 0.0; a2[v] = 0.0; }
+#pragma unroll 1
+                for (int sub = 0; sub < PT_B / 128; ++sub) {
+                    const unsigned base = cl + sub * 1024;
+                    double c[DJ_T][4];
+#pragma unroll
+                    for (int k = 0; k < DJ_T; ++k) {
+                        if (k < T) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) c[k][i] = lds_f64(base + coff[k] + i * 256);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) c[k][i] = 0.0;
                         }
-#undef RT
                     }
-                    if (lane == 0) ti = atomicAdd(&s_next, 1);
-                    ti = __shfl_sync(0xffffffffu, ti, 0);
+                    bool ok[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) ok[i] = sub * 128 + lane + 32 * i < npts;
+#pragma unroll
+                    for (int v = 0; v < DJ_T; ++v) {
+                        if (v < D) {
+                            const unsigned m = ((v < 4 ? mq.x : mq.y) >> (8 * (v & 3))) & 0xffu;
+                            const double2* wr = (const double2*)dj->w[v];
+                            const double2 w01 = __ldg(wr), w23 = __ldg(wr + 1), w45 = __ldg(wr + 2), w67 = __ldg(wr + 3);
+                            const double wk[DJ_T] = {w01.x, w01.y, w23.x, w23.y, w45.x, w45.y, w67.x, w67.y};
+                            const double b1 = __ldg(&dj->b1[v]);
+                            double r[4];
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) r[i] = -b1;
+#pragma unroll
+                            for (int k = 0; k < DJ_T; ++k) {
+                                if ((m >> k) & 1u) {
+#pragma unroll
+                                    for (int i = 0; i < 4; ++i) r[i] = fma(wk[k], c[k][i], r[i]);
+                                }
+                            }
+                            if (L2) {
+                                const double dl = __ldg(&dj->delta[v]);
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) if (ok[i]) { const double r2 = r[i] + dl; a2[v] = fma(r2, r2, a2[v]); }
+                            }
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) if (ok[i]) a1[v] += fabs(r[i]);
+                        }
+                    }
                 }
-                __syncthreads();            // everyone is done with `cur` (and, at k = nb - 1, with the programs)
-                if (p.nbuf == 2) k_buf ^= 1;
+                const int vi = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+                const double t1 = warp_sum8(a1, lane);
+                if ((lane & 3) == 0 && vi < D) s_sum[dj->slot0 + vi] += t1;
+                if (L2) {
+                    const double t2 = warp_sum8(a2, lane);
+                    if ((lane & 3) == 0 && vi < D) s_sum[p.n_slots + dj->slot0 + vi] += t2;
+                }
+            } else if (jj < p.n_dense + p.n_sparse) {
+                // ---------------- sparse job: one eval of an equation with more than DJ_T terms
+                const int js = jj - p.n_dense;
+                const EvalJob job = p.jobs[js];
+                double r[RES_NPL];
+#pragma unroll
+                for (int k = 0; k < RES_NPL; ++k) r[k] = lds_f64(cl + job.tcol * (PP_B * 8) + k * 256) - job.b1;
+                for (int z = 0; z < job.nnz; ++z) {
+                    const int c = p.job_col[(long long)js * TMAX + z];
+                    const double w = p.job_w[(long long)js * TMAX + z];
+#pragma unroll
+                    for (int k = 0; k < RES_NPL; ++k) r[k] = fma(-w, lds_f64(cl + c * (PP_B * 8) + k * 256), r[k]);
+                }
+                double a1 = 0.0, a2 = 0.0;
+#pragma unroll
+                for (int k = 0; k < RES_NPL; ++k) {
+                    if (lane + 32 * k < npts) {
+                        a1 += fabs(r[k]);
+                        if (L2) { const double r2 = r[k] + job.delta; a2 = fma(r2, r2, a2); }
+                    }
+                }
+                a1 = warp_sum(a1);
+                if (L2) a2 = warp_sum(a2);
+                if (lane == 0) { s_sum[job.slot] += a1; if (L2) s_sum[p.n_slots + job.slot] += a2; }
+            } else {
+                // ---------------- target job: sum|t| of one target column (padding points hold 0)
+                const int tc = jj - p.n_dense - p.n_sparse;
+                const int c = p.tcols[tc];
+                double a = 0.0;
+#pragma unroll
+                for (int k = 0; k < RES_NPL; ++k) a += fabs(lds_f64(cl + c * (PP_B * 8) + k * 256));
+                a = warp_sum(a);
+                if (lane == 0) s_sum[2 * p.n_slots + tc] += a;
             }
         }
+        __syncthreads();
     }
-    double* out = p.partial + (size_t)blockIdx.x * p.n_eq * TMAX * 3;
-    for (int q = tid; q < p.n_eq * TMAX * 3; q += blockDim.x) out[q] = table[q];
+    double* out = p.partial + (size_t)blockIdx.x * nsum;
+    for (int q = tid; q < nsum; q += nthreads) out[q] = s_sum[q];
 }
 
-// fixed-order reduction of the per-CTA partial sums -> sums[eval][3]
 struct ResidFinalParams {
-    const int* eq_list;
-    const int* slot_eval;
-    const double* partial;
-    double* sums;
-    int n_eq;
-    int n_cta;
+    const int* slot_ev;      // [n_slots]
+    const int* slot_tci;     // [n_slots] index of the eval's target column in the target-column list
+    const double* partial;   // [n_cta][2 n_slots + n_tcols]
+    double* sums;            // [n_eval][3]
+    int n_slots, n_tcols, n_cta, want_l2;
 };
 
 __global__ void residual_final_kernel(ResidFinalParams p) {
-    const int le = blockIdx.x;
-    const int e = p.eq_list[le];
-    const int tid = threadIdx.x;          // TMAX*3 threads
-    if (tid >= TMAX * 3) return;
-    const int d = tid / 3;
-    const int ev = p.slot_eval[e * TMAX + d];
-    if (ev < 0) return;
-    double s = 0.0;
-    for (int b = 0; b < p.n_cta; ++b) s += p.partial[((size_t)b * p.n_eq + le) * TMAX * 3 + tid];
-    p.sums[(long long)ev * 3 + (tid - d * 3)] = s;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= p.n_slots) return;
+    const int nsum = 2 * p.n_slots + p.n_tcols;
+    const int tci = p.slot_tci[s];
+    double s1 = 0.0, s2 = 0.0, st = 0.0;
+    for (int b = 0; b < p.n_cta; ++b) {
+        const double* q = p.partial + (size_t)b * nsum;
+        s1 += q[s];
+        s2 += q[p.n_slots + s];
+        st += q[2 * p.n_slots + tci];
+    }
+    const int ev = p.slot_ev[s];
+    p.sums[(long long)ev * 3 + 0] = s1;
+    p.sums[(long long)ev * 3 + 1] = st;
+    p.sums[(long long)ev * 3 + 2] = p.want_l2 ? s2 : nan("");
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1575,20 +1297,23 @@ struct epde_ctx {
     long long N = 0;
     cudaStream_t stream = 0;
     std::map<int, double*> tokens;
+    double* weights = nullptr;   // sample weights g (device), null = all ones
     AxisPlan axes[EPDE_MAX_NDIM];
     bool geom_ready = false;
     Geom geom;
     int n_cells = 0;             // nA * nB * npieces
+    int tile_cols = 32;          // pass-A unit width limit = last-axis extent of the token tile / TMA box
+    int box_a = 1, box_b = 1;    // leading extents of the token tile / TMA box (largest cell of slot A / slot B)
+    int box_c = 32;              // its last-axis extent: tile_cols, or tile_cols + 2 when units may start on odd columns
     DevBuf d_geom;               // packed geometry tables
-    DevBuf d_marg, d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given, d_progs, d_fd;
+    DevBuf d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given, d_jobs, d_fd, d_total;
     void* h_pinned = nullptr; size_t h_pinned_cap = 0;
     epde_batch* live = nullptr;
     long long launches = 0;
-    size_t cell_budget_bytes = (size_t)12 << 30;   // scratch cap for the cell Grams of one launch group
+    size_t cell_budget_bytes = (size_t)16 << 30;   // scratch cap for the cell table of one launch group
     int sm_count = 148;
-    int max_smem = 227 * 1024;
-    int resid_warps = RES_WARPS;
-    int gram_warps = GRAM_WARPS;
+    int max_smem = 227 * 1024;   // opt-in shared memory per block of the device
+    int smem_gram = 0, smem_resid = 0, smem_solve = 0;   // dynamic shared memory available to each kernel
     // optional per-kernel-class device timing (epde_ctx_set_timing)
     bool timing = false;
     struct Span { int cls; cudaEvent_t a, b; };
@@ -1660,30 +1385,37 @@ static int build_geometry(epde_ctx* c) {
     } else {
         cellsA = {{0, 0, 1}}; cellsB = {{0, 0, 1}};
     }
-    const AxisPlan& lastp = c->axes[last];
-    const long long nl = c->shape[last];
-    // pieces: sub-segments of the last axis no wider than a tile
-    std::vector<int> piece_start, piece_seg;
-    for (auto& cl : lastp.cells)
-        for (int lo = cl.lo; lo < cl.hi; lo += TILE_COLS) { piece_start.push_back(lo); piece_seg.push_back(cl.seg); }
-    piece_start.push_back((int)nl);
-    const int npieces = (int)piece_seg.size();
-    // chunks: runs of pieces with total width <= TILE_COLS
-    struct Chunk { int p_lo, np, col_lo, ncols; };
-    std::vector<Chunk> chunks;
-    for (int pI = 0; pI < npieces;) {
-        int q = pI;
-        while (q < npieces && piece_start[q + 1] - piece_start[pI] <= TILE_COLS) ++q;
-        chunks.push_back({pI, q - pI, piece_start[pI], piece_start[q] - piece_start[pI]});
-        pI = q;
-    }
     const int nA = (int)cellsA.size(), nB = (int)cellsB.size();
-    std::vector<UnitDesc> units;
-    units.reserve((size_t)nA * nB * chunks.size());
     int max_rows = 1;
     for (int a = 0; a < nA; ++a)
-        for (int b = 0; b < nB; ++b) {
+        for (int b = 0; b < nB; ++b)
             max_rows = std::max(max_rows, (cellsA[a].hi - cellsA[a].lo) * (cellsB[b].hi - cellsB[b].lo));
+    // unit width: about 512 points per unit (the token tile of a unit is max_rows x tile_cols doubles per token)
+    int tile_cols = 32;
+    while (tile_cols > 8 && max_rows * tile_cols > 512) tile_cols /= 2;
+    const AxisPlan& lastp = c->axes[last];
+    const long long nl = c->shape[last];
+    // pieces: sub-segments of the last axis no wider than a unit
+    std::vector<int> piece_start, piece_seg;
+    for (auto& cl : lastp.cells)
+        for (int lo = cl.lo; lo < cl.hi; lo += tile_cols) { piece_start.push_back(lo); piece_seg.push_back(cl.seg); }
+    piece_start.push_back((int)nl);
+    const int npieces = (int)piece_seg.size();
+    // chunks: runs of pieces with total width <= tile_cols
+    struct Chunk { int p_lo, np, col_lo, ncols; };
+    std::vector<Chunk> chunks;
+    bool odd = false;
+    for (int pI = 0; pI < npieces;) {
+        int q = pI;
+        while (q < npieces && piece_start[q + 1] - piece_start[pI] <= tile_cols) ++q;
+        chunks.push_back({pI, q - pI, piece_start[pI], piece_start[q] - piece_start[pI]});
+        if (piece_start[pI] & 1) odd = true;
+        pI = q;
+    }
+    std::vector<UnitDesc> units;
+    units.reserve((size_t)nA * nB * chunks.size());
+    for (int a = 0; a < nA; ++a)
+        for (int b = 0; b < nB; ++b)
             for (auto& ch : chunks) {
                 UnitDesc u;
                 memset(&u, 0, sizeof u);
@@ -1692,16 +1424,8 @@ static int build_geometry(epde_ctx* c) {
                 u.col_lo = ch.col_lo; u.ncols = ch.ncols;
                 u.cell = a * nB + b;
                 u.piece_lo = ch.p_lo; u.npieces = ch.np;
-                u.wlog = -1;
-                for (int wl = 0; wl <= 5 && u.wlog < 0; ++wl) {
-                    bool ok = true;
-                    for (int q = 0; q < ch.np && ok; ++q)
-                        ok = (piece_start[ch.p_lo + q + 1] - piece_start[ch.p_lo + q]) == (1 << wl);
-                    if (ok) u.wlog = wl;
-                }
                 units.push_back(u);
             }
-        }
     // segment rows: axes stacked; marginal descriptors (cells of one segment are contiguous)
     std::vector<int> axis_row_base(nd + 1, 0);
     for (int d = 0; d < nd; ++d) axis_row_base[d + 1] = axis_row_base[d] + c->axes[d].nseg;
@@ -1772,7 +1496,7 @@ static int build_geometry(epde_ctx* c) {
     g.n_windows = W;
     g.ndim = nd;
     g.max_rows = max_rows;
-    g.aligned16 = (nd == 1 || (nl % 2 == 0)) ? 1 : 0;
+    g.aligned16 = (nd == 1 || nl % 2 == 0) ? 1 : 0;
     g.N = c->N;
     g.units = (const UnitDesc*)(base + o_units);
     g.piece_start = (const int*)(base + o_piece);
@@ -1780,29 +1504,44 @@ static int build_geometry(epde_ctx* c) {
     g.win_lo_row = (const int*)(base + o_wlo);
     g.win_hi_row = (const int*)(base + o_whi);
     c->n_cells = nA * nB * npieces;
+    // the TMA box starts on an even column (16-byte aligned global address): a unit that starts on an odd column
+    // fetches one column more on the left, so the box is two columns wider when such units exist
+    c->tile_cols = tile_cols;
+    c->box_c = odd ? tile_cols + 2 : tile_cols;
+    c->box_a = 1; c->box_b = 1;
+    for (auto& cl : cellsA) c->box_a = std::max(c->box_a, cl.hi - cl.lo);
+    for (auto& cl : cellsB) c->box_b = std::max(c->box_b, cl.hi - cl.lo);
     c->geom_ready = true;
     return 0;
 }
 
-struct LaunchGroup {             // equations evaluated together: <= MAXU distinct tokens, cell table within budget
-    std::vector<int> eqs;        // most terms first
+struct LaunchGroup {             // equations evaluated together over ONE dictionary of distinct term columns
+    std::vector<int> eqs;
     std::vector<int> token_ids;  // slot -> token id
-    int list_off = 0;            // offset of the group's equation list inside d_lists
-    long long cell_doubles = 0;
+    std::vector<int> col_term;   // column -> global distinct-term id (the ones column is appended after these)
+    int ncols = 0, cp = 0, n_ent = 0;
+    int ntasks = 0, ksplit = 1;
+    int n_slots = 0, n_dense = 0, n_sparse = 0, n_tcols = 0;   // pass-B jobs: evals, dense-equation jobs, sparse evals, target columns
+    int n_gfac = 0;
+    long long seg_off = 0, win_off = 0, pe_off = 0;     // doubles / doubles / ints into the batch-wide tables
+    // device pointers into ctx->d_enc
+    ColDesc* d_cols = nullptr; FactorDesc* d_gfac = nullptr; TaskDesc* d_tasks = nullptr;
+    int* d_flush = nullptr; int* d_slot_ev = nullptr; int* d_slot_tci = nullptr; int* d_tcols = nullptr;
+    int* d_dj_eq = nullptr; int* d_dj_slot0 = nullptr;
 };
 
 struct epde_batch {
     epde_ctx* ctx = nullptr;
-    int n_eq = 0, n_eval = 0, n_fac = 0;
+    int n_eq = 0, n_eval = 0;
     std::vector<EqDesc> eqs;
     std::vector<LaunchGroup> groups;
-    std::vector<int> evals_gs8, evals_gs16;
+    std::vector<int> evals_gs8, evals_gs16, evals_gs32;
     // device pointers into ctx->d_enc
     EqDesc* d_eqs = nullptr;
-    FactorDesc* d_factors = nullptr;
-    int* d_eval_eq = nullptr; int* d_eval_tgt = nullptr; int* d_slot_eval = nullptr;
-    int* d_lists = nullptr;                      // equation lists by group, eval lists by GS
-    int off_gs8 = 0, off_gs16 = 0;
+    int* d_eval_eq = nullptr; int* d_eval_tgt = nullptr;
+    int* d_lists = nullptr;                      // eval lists by GS
+    int* d_pairent = nullptr;
+    int off_gs8 = 0, off_gs16 = 0, off_gs32 = 0;
     // outputs in ctx->d_out
     double* d_coef = nullptr; double* d_intercept = nullptr; double* d_stab = nullptr;
     double* d_sw = nullptr; double* d_wterm = nullptr; double* d_sums = nullptr; double* d_b1 = nullptr;
@@ -1812,108 +1551,56 @@ struct epde_batch {
     int* d_mode = nullptr; double* d_given_w = nullptr; double* d_given_b = nullptr;
     bool solved = false;
     bool want_l2 = true;       // epde_batch_set_norms
+    bool weighted = false;     // the context held non-trivial sample weights when the batch was created
 };
 
-static size_t gram_smem_bytes(const epde_ctx* c, int U, int nwarps, int n_eq) {
-    (void)nwarps;
-    return sizeof(double) * ((size_t)U * c->geom.max_rows * TILE_COLS) + (size_t)n_eq * sizeof(WarpProg);
+// ---- pass-A tasks of a launch group: TASK_A x TASK_B rectangles of 8x8 column-block pairs covering the needed part
+//      of the upper block triangle; ordered so that the four warp schedulers of an SM get equal DMMA counts
+static void build_tasks(int nblk, const std::vector<char>& need /* [nblk * nblk], I <= J */, std::vector<TaskDesc>& tasks) {
+    tasks.clear();
+    for (int i0 = 0; i0 < nblk; i0 += TASK_A) {
+        std::vector<int> js;
+        for (int j = i0; j < nblk; ++j) {
+            bool any = false;
+            for (int i = i0; i < std::min(nblk, i0 + TASK_A); ++i)
+                if (i <= j && need[i * nblk + j]) any = true;
+            if (any) js.push_back(j);
+        }
+        for (size_t q = 0; q < js.size(); q += TASK_B) {
+            TaskDesc t;
+            memset(&t, 0, sizeof t);
+            int pairs = 0;
+            for (int a = 0; a < TASK_A; ++a) t.ablk[a] = (unsigned char)std::min(nblk - 1, i0 + a);
+            for (int b = 0; b < TASK_B; ++b) t.bblk[b] = (unsigned char)js[std::min(js.size() - 1, q + b)];
+            for (int a = 0; a < TASK_A; ++a)
+                for (int b = 0; b < TASK_B; ++b) {
+                    const int i = i0 + a, j = (q + b < js.size()) ? js[q + b] : -1;
+                    if (i < nblk && j >= 0 && i <= j && need[i * nblk + j]) { t.mask |= (unsigned char)(1u << (a * TASK_B + b)); ++pairs; }
+                }
+            t.pad0 = (unsigned char)pairs;
+            if (pairs) tasks.push_back(t);
+        }
+    }
+    // longest-processing-time deal into the 4 scheduler bins (warp w runs on scheduler w % 4)
+    std::stable_sort(tasks.begin(), tasks.end(), [](const TaskDesc& a, const TaskDesc& b) { return a.pad0 > b.pad0; });
+    std::vector<TaskDesc> bins[4];
+    int load[4] = {0, 0, 0, 0};
+    for (auto& t : tasks) {
+        int k = 0;
+        for (int q = 1; q < 4; ++q) if (load[q] < load[k]) k = q;
+        bins[k].push_back(t); load[k] += t.pad0;
+    }
+    std::vector<TaskDesc> out;
+    for (size_t r = 0; out.size() < tasks.size(); ++r)
+        for (int k = 0; k < 4; ++k) if (r < bins[k].size()) out.push_back(bins[k][r]);
+    tasks.swap(out);
 }
 
-static int launch_gram_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double* cells) {
-    GramParams p;
-    memset(&p, 0, sizeof p);
-    p.g = c->geom; p.eqs = b->d_eqs; p.factors = b->d_factors;
-    p.eq_list = b->d_lists + g.list_off; p.n_eq = (int)g.eqs.size();
-    p.U = (int)g.token_ids.size();
-    for (int u = 0; u < p.U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
-    p.cells = cells;
-    // persistent CTAs (one per SM) walk over the units; the programs of the launch's equations live in shared
-    // memory next to the tile, so a group whose programs do not fit is split into several launches
-    const int ne_all = (int)g.eqs.size();
-    const size_t fixed = gram_smem_bytes(c, p.U, c->gram_warps, 0);
-    if (fixed + sizeof(WarpProg) > (size_t)c->max_smem)
-        return fail("pass A tile needs %zu bytes of shared memory (> %d)", fixed + sizeof(WarpProg), c->max_smem);
-    const int cap = (int)(((size_t)c->max_smem - fixed) / sizeof(WarpProg));
-    const int n_launch = (ne_all + cap - 1) / cap;
-    const int per_launch = (ne_all + n_launch - 1) / n_launch;
-    for (int e0 = 0; e0 < ne_all; e0 += per_launch) {
-        p.eq_list = b->d_lists + g.list_off + e0;
-        p.n_eq = std::min(per_launch, ne_all - e0);
-        const int nwarps = std::max(1, std::min(c->gram_warps, p.n_eq));
-        const size_t smem = gram_smem_bytes(c, p.U, nwarps, p.n_eq);
-        const unsigned grid = (unsigned)std::min(c->geom.n_units, c->sm_count);
-        {
-            KernelSpan ks(c, EPDE_KERNEL_GRAM);
-            gram_tile_kernel<GRAM_WARPS><<<grid, nwarps * 32, smem, c->stream>>>(p);
-        }
-        CK(cudaGetLastError());
-    }
-    return 0;
-}
+struct TermKey {
+    std::vector<double> v;       // sorted (token, kind, power, param) tuples, flattened
+    bool operator<(const TermKey& o) const { return v < o.v; }
+};
 
-static int launch_resid_group(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double* sums) {
-    const int U = (int)g.token_ids.size();
-    // tile = 1024 points (measured at 512^3, population 128: 2048-point tiles are slower); two buffers when they
-    // fit next to one segment of programs and the sum table
-    int tile_pts = RES_TILE_MIN;
-    if (const char* ev = getenv("EPDE_RES_TILE")) { const int v = atoi(ev); if (v == 1024 || v == 2048 || v == 4096) tile_pts = v; }
-    int seg_eqs = 64, batch_tiles = 4;      // measured at 512^3 / 128 equations: (64, 4) 117 ms, (16, 8) 129, (8, 8) 143
-    if (const char* ev = getenv("EPDE_RES_SEG")) seg_eqs = std::max(1, atoi(ev));
-    if (const char* ev = getenv("EPDE_RES_BATCH")) batch_tiles = std::max(1, atoi(ev));
-    const long long n_tiles = (c->N + tile_pts - 1) / tile_pts;
-    const int ne_all = (int)g.eqs.size();
-    const size_t tile_bytes = sizeof(double) * (size_t)U * tile_pts;
-    const size_t table_eq = sizeof(double) * TMAX * 3;
-    // equations per launch: the sum table of all of them stays in shared memory
-    const size_t fixed1 = tile_bytes + (size_t)seg_eqs * sizeof(ResidProg);
-    if (fixed1 + table_eq > (size_t)c->max_smem) return fail("pass B tiles need %zu bytes of shared memory", fixed1 + table_eq);
-    const int cap = (int)(((size_t)c->max_smem - fixed1) / table_eq);
-    const int n_launch = (ne_all + cap - 1) / cap;
-    const int per_launch = (ne_all + n_launch - 1) / n_launch;
-    for (int e0 = 0; e0 < ne_all; e0 += per_launch) {
-        const int ne = std::min(per_launch, ne_all - e0);
-        // few programs per CTA (<= 5 per warp): halve the longest tasks (residual_prog_kernel).  Measured: 32 equations
-        // per launch, slowest of 8 population shards 8.0 -> 5.5 ms; at 64 per launch the recomputed columns cost more
-        // than the tail (512^3: 91 -> 103 ms), hence the limit
-        const int split = ne <= 40 ? 1 : 0;
-        const int nwarps = std::max(1, std::min(c->resid_warps, std::min(split ? 2 * ne : ne, seg_eqs)));
-        ResidParams p;
-        memset(&p, 0, sizeof p);
-        p.N = c->N; p.eqs = b->d_eqs; p.factors = b->d_factors;
-        p.eq_list = b->d_lists + g.list_off + e0; p.n_eq = ne; p.U = U; p.n_tiles = (int)n_tiles; p.tile_pts = tile_pts;
-        for (int u = 0; u < U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
-        p.slot_eval = b->d_slot_eval; p.wterm = b->d_wterm; p.intercept = b->d_intercept; p.intercept_l1 = b->d_b1;
-        p.seg_eqs = std::min(seg_eqs, split ? 2 * ne : ne); p.batch_tiles = batch_tiles; p.split = split;
-        const size_t rest = (size_t)p.seg_eqs * sizeof(ResidProg) + (size_t)ne * table_eq;
-        p.nbuf = (2 * tile_bytes + rest <= (size_t)c->max_smem) ? 2 : 1;
-        const size_t smem = p.nbuf * tile_bytes + rest;
-        if (c->d_progs.ensure(4 * (size_t)ne * sizeof(ResidProg) + 16)) return 1;
-        p.progs = (ResidProg*)c->d_progs.ptr;
-        p.n_live = (int*)(p.progs + 4 * (size_t)ne);
-        // one persistent CTA per SM: the tile -> CTA assignment (and with it the summation order) depends only on
-        // the grid size, never on what else is in the batch
-        const int grid = (int)std::min<long long>(n_tiles, (long long)c->sm_count);
-        if (c->d_partial.ensure(sizeof(double) * (size_t)grid * ne * TMAX * 3)) return 1;
-        p.partial = (double*)c->d_partial.ptr;
-        {
-            KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
-            residual_prog_kernel<<<1, 256, sizeof(int) * 2 * (size_t)ne, c->stream>>>(p);
-        }
-        CK(cudaGetLastError());
-        {
-            KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
-            if (b->want_l2) residual_tile_kernel<RES_WARPS, true><<<grid, nwarps * 32, smem, c->stream>>>(p);
-            else residual_tile_kernel<RES_WARPS, false><<<grid, nwarps * 32, smem, c->stream>>>(p);
-        }
-        CK(cudaGetLastError());
-        ResidFinalParams fp;
-        fp.eq_list = p.eq_list; fp.slot_eval = b->d_slot_eval; fp.partial = p.partial; fp.sums = sums;
-        fp.n_eq = ne; fp.n_cta = grid;
-        { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_final_kernel<<<ne, 32, 0, c->stream>>>(fp); }
-        CK(cudaGetLastError());
-    }
-    return 0;
-}
 // ------------------------------------------------------------------------------------------
 // token producer on the device: finite-difference derivatives exactly as
 // AdaptiveFiniteDeriv does them (preprocessing/deriv_calculators.py:46-102 = repeated numpy.gradient with the
@@ -1980,10 +1667,60 @@ __global__ void __launch_bounds__(256) crop_interior_kernel(CropParams p) {
 // ------------------------------------------------------------------------------------------
 // C ABI
 // ------------------------------------------------------------------------------------------
+
+// sustained FP64 rate measurement (epde_measure_fp64_peak): independent FMA chains / DMMA chains, no memory traffic
+template <int CHAINS>
+__global__ void __launch_bounds__(256) fp64_dfma_kernel(double* out, int iters, double a, double b) {
+    double acc[CHAINS];
+#pragma unroll
+    for (int k = 0; k < CHAINS; ++k) acc[k] = threadIdx.x * 1e-3 + k;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < CHAINS; ++k) acc[k] = fma(acc[k], a, b);
+    }
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < CHAINS; ++k) s += acc[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+template <int CHAINS>
+__global__ void __launch_bounds__(256) fp64_dmma_kernel(double* out, int iters, double a, double b) {
+    double d0[CHAINS], d1[CHAINS];
+#pragma unroll
+    for (int k = 0; k < CHAINS; ++k) { d0[k] = threadIdx.x * 1e-3 + k; d1[k] = k; }
+    const double av = a + threadIdx.x * 1e-9;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < CHAINS; ++k) dmma884(d0[k], d1[k], av, b);
+    }
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < CHAINS; ++k) s += d0[k] + d1[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// ------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------
 extern "C" {
 
 const char* epde_last_error(void) { return g_err.c_str(); }
-const char* epde_version(void) { return "epde_b200 0.2.0 sm_100a"; }
+const char* epde_version(void) { return "epde_b200 0.3.0 sm_100a"; }
+
+static int set_dyn_smem(const void* fn, int max_smem, int* dyn_out) {
+    cudaFuncAttributes fa;
+    cudaError_t fe = cudaFuncGetAttributes(&fa, fn);
+    int dyn = max_smem;
+    if (fe == cudaSuccess) {
+        dyn = max_smem - (int)fa.sharedSizeBytes;
+        fe = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+    }
+    if (fe != cudaSuccess)
+        return fail("epde_ctx_create: cannot configure shared memory (%s); is this an sm_100 device?", cudaGetErrorString(fe));
+    if (dyn_out) *dyn_out = std::min(*dyn_out, dyn);
+    return 0;
+}
 
 int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx** out) {
     if (!out || !inner_shape) return fail("epde_ctx_create: null argument");
@@ -2003,25 +1740,14 @@ int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx**
     c->sm_count = prop.multiProcessorCount;
     c->max_smem = (int)prop.sharedMemPerBlockOptin;
     {
-        // dynamic shared memory limit = opt-in maximum minus the kernels' static shared memory
-        const void* fns[3] = {(const void*)gram_tile_kernel<GRAM_WARPS>, (const void*)residual_tile_kernel<RES_WARPS, true>,
-                              (const void*)residual_tile_kernel<RES_WARPS, false>};
-        int dyn_max = c->max_smem;
-        for (int k = 0; k < 3; ++k) {
-            cudaFuncAttributes fa;
-            cudaError_t fe = cudaFuncGetAttributes(&fa, fns[k]);
-            if (fe == cudaSuccess) {
-                const int dyn = c->max_smem - (int)fa.sharedSizeBytes;
-                fe = cudaFuncSetAttribute(fns[k], cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
-                dyn_max = std::min(dyn_max, dyn);
-            }
-            if (fe != cudaSuccess) {
-                delete c;
-                return fail("epde_ctx_create: cannot configure shared memory (%s); is this an sm_100 device?",
-                            cudaGetErrorString(fe));
-            }
-        }
-        c->max_smem = dyn_max;
+        // dynamic shared memory limit of a kernel = opt-in maximum minus its static shared memory
+        c->smem_gram = c->smem_resid = c->smem_solve = c->max_smem;
+        const void* gram[] = {(const void*)gram_dmma_kernel<false>, (const void*)gram_dmma_kernel<true>};
+        const void* resid[] = {(const void*)residual_cols_kernel<false>, (const void*)residual_cols_kernel<true>};
+        const void* solve[] = {(const void*)lasso_solve_kernel<8>, (const void*)lasso_solve_kernel<16>, (const void*)lasso_solve_kernel<32>};
+        for (const void* fn : gram) if (set_dyn_smem(fn, c->max_smem, &c->smem_gram)) { delete c; return 1; }
+        for (const void* fn : resid) if (set_dyn_smem(fn, c->max_smem, &c->smem_resid)) { delete c; return 1; }
+        for (const void* fn : solve) if (set_dyn_smem(fn, c->max_smem, &c->smem_solve)) { delete c; return 1; }
     }
     c->N = 1;
     for (int d = 0; d < ndim; ++d) {
@@ -2040,8 +1766,10 @@ int epde_ctx_destroy(epde_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     for (auto& kv : c->tokens) cudaFree(kv.second);
-    c->d_geom.release(); c->d_marg.release(); c->d_cells.release(); c->d_seg.release(); c->d_win.release(); c->d_enc.release();
-    c->d_out.release(); c->d_partial.release(); c->d_given.release(); c->d_progs.release(); c->d_fd.release();
+    if (c->weights) cudaFree(c->weights);
+    c->d_geom.release(); c->d_cells.release(); c->d_seg.release(); c->d_win.release(); c->d_enc.release();
+    c->d_out.release(); c->d_partial.release(); c->d_given.release(); c->d_jobs.release(); c->d_fd.release();
+    c->d_total.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto& sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto& ev : c->free_events) cudaEventDestroy(ev);
@@ -2066,16 +1794,24 @@ int epde_ctx_set_shard(epde_ctx* c, int64_t off, int64_t glob) {
     return build_geometry(c);
 }
 
+// token vectors are allocated with 16 spare doubles: the 16-byte bulk copies of the streaming passes may read one
+// element past the last point of an odd-length chunk
+static int token_alloc(epde_ctx* c, double** p, const char* who) {
+    if (*p) return 0;
+    cudaError_t e = cudaMalloc((void**)p, sizeof(double) * ((size_t)c->N + 16));
+    if (e != cudaSuccess) { *p = nullptr; return fail("%s: out of device memory (%s)", who, cudaGetErrorString(e)); }
+    e = cudaMemsetAsync(*p + c->N, 0, sizeof(double) * 16, c->stream);
+    if (e != cudaSuccess) return fail("%s: %s", who, cudaGetErrorString(e));
+    return 0;
+}
+
 int epde_cache_upload(epde_ctx* c, int id, const double* host, int64_t n) {
     if (!c || !host) return fail("epde_cache_upload: null argument");
     if (n != c->N) return fail("epde_cache_upload: token %d has %lld values, context expects %lld", id, (long long)n, c->N);
     if (id < 0 || id >= EPDE_MAX_TOKENS) return fail("epde_cache_upload: token id %d out of range", id);
     CK(cudaSetDevice(c->device));
     double*& p = c->tokens[id];
-    if (!p) {
-        cudaError_t e = cudaMalloc((void**)&p, sizeof(double) * (size_t)n);
-        if (e != cudaSuccess) { c->tokens.erase(id); return fail("epde_cache_upload: out of device memory (%s)", cudaGetErrorString(e)); }
-    }
+    if (token_alloc(c, &p, "epde_cache_upload")) { c->tokens.erase(id); return 1; }
     CK(cudaMemcpyAsync(p, host, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     return 0;
@@ -2087,10 +1823,7 @@ int epde_cache_upload_device(epde_ctx* c, int id, const double* dev, int64_t n) 
     if (id < 0 || id >= EPDE_MAX_TOKENS) return fail("epde_cache_upload_device: token id %d out of range", id);
     CK(cudaSetDevice(c->device));
     double*& p = c->tokens[id];
-    if (!p) {
-        cudaError_t e = cudaMalloc((void**)&p, sizeof(double) * (size_t)n);
-        if (e != cudaSuccess) { c->tokens.erase(id); return fail("epde_cache_upload_device: out of device memory (%s)", cudaGetErrorString(e)); }
-    }
+    if (token_alloc(c, &p, "epde_cache_upload_device")) { c->tokens.erase(id); return 1; }
     CK(cudaMemcpyAsync(p, dev, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, c->stream));
     return 0;
 }
@@ -2132,10 +1865,16 @@ int epde_cache_bytes(epde_ctx* c, int64_t* bytes) {
 int epde_ctx_set_sample_weights(epde_ctx* c, const double* host, int64_t n) {
     if (!c || !host) return fail("null argument");
     if (n != c->N) return fail("epde_ctx_set_sample_weights: size mismatch");
-    for (int64_t i = 0; i < n; ++i)
-        if (host[i] != 1.0)
-            return fail("epde_ctx_set_sample_weights: only the default all-ones g_func mask is supported "
-                        "(value %g at %lld); non-trivial sample weights are not implemented", host[i], (long long)i);
+    CK(cudaSetDevice(c->device));
+    bool ones = true;
+    for (int64_t i = 0; i < n && ones; ++i) ones = host[i] == 1.0;
+    if (ones) {                                 // the default 0/1 mask restricted to the interior (interface.py:540-545)
+        if (c->weights) { CK(cudaStreamSynchronize(c->stream)); cudaFree(c->weights); c->weights = nullptr; }
+        return 0;
+    }
+    if (token_alloc(c, &c->weights, "epde_ctx_set_sample_weights")) return 1;
+    CK(cudaMemcpyAsync(c->weights, host, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
     return 0;
 }
 
@@ -2187,188 +1926,272 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
     CK(cudaSetDevice(c->device));
     epde_batch* b = new epde_batch();
     b->ctx = c; b->n_eq = n_eq; b->n_eval = n_eval;
+    b->weighted = c->weights != nullptr;
     const int n_terms = term_off[n_eq];
-    b->n_fac = fac_off[n_terms];
-    std::vector<FactorDesc> factors(b->n_fac);
+    const int n_fac = fac_off[n_terms];
     b->eqs.resize(n_eq);
     const int W = c->geom.n_windows;
-    long long s_off = 0, w_off = 0;
+    const int max_cols = CMAX - 1;             // term columns of a group (one more for the ones column)
+    const int max_tok = b->weighted ? MAXU - 1 : MAXU;
+    for (int f = 0; f < n_fac; ++f) {
+        if (!c->tokens.count(fac_token[f])) { delete b; return fail("factor %d references token %d which is not in the cache", f, fac_token[f]); }
+        const int kind = fac_kind ? fac_kind[f] : 0;
+        if (kind < 0 || kind > 3) { delete b; return fail("factor %d has unknown kind %d", f, kind); }
+    }
+    // ---- dictionary of distinct terms: a term = the multiset of its (token, kind, power, param) factors
+    std::map<TermKey, int> term_ids;
+    std::vector<int> term_first;               // distinct term -> one (global) term index holding it
+    std::vector<int> term_of(n_terms);         // (global) term index -> distinct term
+    std::vector<std::vector<int>> term_tok;    // distinct term -> tokens
     for (int e = 0; e < n_eq; ++e) {
         const int T = term_off[e + 1] - term_off[e];
         if (T < 1 || T > TMAX) { delete b; return fail("equation %d has %d terms; supported: 1..%d", e, T, TMAX); }
-        EqDesc& q = b->eqs[e];
-        memset(&q, 0, sizeof q);
-        q.T = T;
-        for (int t = 0; t <= T; ++t) q.fac_off[t] = fac_off[term_off[e] + t];
-        for (int t = T + 1; t <= TMAX; ++t) q.fac_off[t] = q.fac_off[T];
-        for (int t = 0; t < T; ++t) {
-            const int nf = q.fac_off[t + 1] - q.fac_off[t];
-            if (nf < 1 || nf > FMAXF) { delete b; return fail("equation %d term %d has %d factors; supported: 1..%d", e, t, nf, FMAXF); }
+        for (int t = term_off[e]; t < term_off[e + 1]; ++t) {
+            const int nf = fac_off[t + 1] - fac_off[t];
+            if (nf < 1 || nf > FMAXF) { delete b; return fail("equation %d term %d has %d factors; supported: 1..%d", e, t - term_off[e], nf, FMAXF); }
+            std::vector<std::array<double, 4>> fs;
+            for (int f = fac_off[t]; f < fac_off[t + 1]; ++f)
+                fs.push_back({(double)fac_token[f], (double)(fac_kind ? fac_kind[f] : 0), fac_power[f], fac_param ? fac_param[f] : 0.0});
+            std::sort(fs.begin(), fs.end());
+            TermKey key;
+            for (auto& q : fs) key.v.insert(key.v.end(), q.begin(), q.end());
+            auto it = term_ids.find(key);
+            if (it == term_ids.end()) {
+                it = term_ids.emplace(key, (int)term_first.size()).first;
+                term_first.push_back(t);
+                std::set<int> tk;
+                for (int f = fac_off[t]; f < fac_off[t + 1]; ++f) tk.insert(fac_token[f]);
+                term_tok.push_back(std::vector<int>(tk.begin(), tk.end()));
+            }
+            term_of[t] = it->second;
         }
-        q.s_off = s_off;
-        s_off += (long long)c->geom.n_rows * (nacc_of(T) + 1);
-        q.w_off = w_off;
-        w_off += (long long)(W + 1) * (nacc_of(T) + 1);
     }
-    b->seg_doubles = s_off;
-    b->win_doubles = w_off;
-    for (int f = 0; f < b->n_fac; ++f) {
-        if (!c->tokens.count(fac_token[f])) { delete b; return fail("factor %d references token %d which is not in the cache", f, fac_token[f]); }
-        FactorDesc& d = factors[f];
-        memset(&d, 0, sizeof d);
-        d.power = fac_power[f];
-        d.kind = fac_kind ? fac_kind[f] : 0;
-        d.param = fac_param ? fac_param[f] : 0.0;
-        if (d.kind < 0 || d.kind > 3) { delete b; return fail("factor %d has unknown kind %d", f, d.kind); }
-        d.ipow = (d.power == 1.0) ? 1 : (d.power == 2.0) ? 2 : (d.power == 3.0) ? 3 : 0;
-    }
-    // ---- launch groups: a group shares one staged tile of <= MAXU distinct tokens.  Equations are taken most
-    //      terms first and placed first-fit into the open groups (token count and cell scratch permitting).
+    // ---- launch groups: equations (most terms first) go to the open group they share the most columns with,
+    //      as long as its dictionary stays within CMAX columns and MAXU tokens
     std::vector<int> order(n_eq);
     for (int e = 0; e < n_eq; ++e) order[e] = e;
-    std::stable_sort(order.begin(), order.end(), [&](int a, int bb) { return b->eqs[a].T > b->eqs[bb].T; });
-    std::vector<std::set<int>> group_tok;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int bb) {
+        return term_off[a + 1] - term_off[a] > term_off[bb + 1] - term_off[bb]; });
+    std::vector<std::set<int>> g_terms, g_tok;
     for (int e : order) {
-        const EqDesc& q = b->eqs[e];
-        std::set<int> mine;
-        for (int f = q.fac_off[0]; f < q.fac_off[q.T]; ++f) mine.insert(fac_token[f]);
-        if ((int)mine.size() > MAXU) { delete b; return fail("equation %d references %d distinct tokens; supported: %d", e, (int)mine.size(), MAXU); }
-        const long long cd = (long long)c->n_cells * nacc_of(q.T);
-        int gi = -1;
-        for (size_t k = 0; k < b->groups.size() && gi < 0; ++k) {
-            std::set<int> uni = group_tok[k];
-            uni.insert(mine.begin(), mine.end());
-            if ((int)uni.size() <= MAXU &&
-                (size_t)(b->groups[k].cell_doubles + cd) * sizeof(double) <= c->cell_budget_bytes) gi = (int)k;
+        std::set<int> mine, mtok;
+        for (int t = term_off[e]; t < term_off[e + 1]; ++t) {
+            mine.insert(term_of[t]);
+            mtok.insert(term_tok[term_of[t]].begin(), term_tok[term_of[t]].end());
         }
-        if (gi < 0) { b->groups.push_back(LaunchGroup()); group_tok.push_back(std::set<int>()); gi = (int)b->groups.size() - 1; }
-        group_tok[gi].insert(mine.begin(), mine.end());
-        b->groups[gi].eqs.push_back(e);
-        b->groups[gi].cell_doubles += cd;
+        if ((int)mtok.size() > max_tok) { delete b; return fail("equation %d references %d distinct tokens; supported: %d", e, (int)mtok.size(), max_tok); }
+        int gi = -1, best_new = 1 << 30;
+        for (size_t k = 0; k < b->groups.size(); ++k) {
+            int fresh = 0;
+            for (int t : mine) fresh += g_terms[k].count(t) ? 0 : 1;
+            std::set<int> uni = g_tok[k];
+            uni.insert(mtok.begin(), mtok.end());
+            if ((int)g_terms[k].size() + fresh <= max_cols && (int)uni.size() <= max_tok && fresh < best_new) { gi = (int)k; best_new = fresh; }
+        }
+        if (gi < 0) { b->groups.push_back(LaunchGroup()); g_terms.push_back({}); g_tok.push_back({}); gi = (int)b->groups.size() - 1; }
+        LaunchGroup& g = b->groups[gi];
+        for (int t = term_off[e]; t < term_off[e + 1]; ++t)
+            if (g_terms[gi].insert(term_of[t]).second) g.col_term.push_back(term_of[t]);
+        g_tok[gi].insert(mtok.begin(), mtok.end());
+        g.eqs.push_back(e);
+        b->eqs[e].group = gi;
     }
-    // per group: slots, cell offsets, fast-path encoding
+    // ---- evals
+    std::vector<std::vector<int>> eq_evals(n_eq);
+    {
+        std::set<std::pair<int, int>> seen;
+        for (int v = 0; v < n_eval; ++v) {
+            const int e = eval_eq[v], t = eval_target[v];
+            if (e < 0 || e >= n_eq) { delete b; return fail("eval %d references equation %d", v, e); }
+            const int T = term_off[e + 1] - term_off[e];
+            if (t < 0 || t >= T) { delete b; return fail("eval %d: target %d outside equation %d (%d terms)", v, t, e, T); }
+            if (!seen.insert({e, t}).second) { delete b; return fail("eval %d duplicates (equation %d, target %d)", v, e, t); }
+            eq_evals[e].push_back(v);
+            if (T <= 8) b->evals_gs8.push_back(v); else if (T <= 16) b->evals_gs16.push_back(v); else b->evals_gs32.push_back(v);
+        }
+    }
+    // ---- per group: columns, pair entries, tasks, flush maps, jobs -> one packed host image
+    auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    std::vector<char> img;
+    auto put = [&](const void* src, size_t bytes) { const size_t o = align(img.size()); img.resize(o + std::max<size_t>(bytes, 1)); if (bytes) memcpy(img.data() + o, src, bytes); return o; };
+    struct GOff { size_t cols, gfac, tasks, flush, slot_ev, slot_tci, tcols, dj_eq, dj_slot0; };
+    std::vector<GOff> goff(b->groups.size());
+    std::vector<int> pairent_all;
+    long long seg_off = 0, win_off = 0;
+    const size_t n_cells = (size_t)c->n_cells;
     for (size_t gi = 0; gi < b->groups.size(); ++gi) {
         LaunchGroup& g = b->groups[gi];
-        g.token_ids.assign(group_tok[gi].begin(), group_tok[gi].end());
+        g.token_ids.assign(g_tok[gi].begin(), g_tok[gi].end());
         std::map<int, int> slot;
         for (size_t u = 0; u < g.token_ids.size(); ++u) slot[g.token_ids[u]] = (int)u;
-        long long c_off = 0;
-        for (int e : g.eqs) {
-            EqDesc& q = b->eqs[e];
-            q.group = (int)gi;
-            q.c_off = c_off;
-            c_off += (long long)c->n_cells * nacc_of(q.T);
-            // fast equation: every term is a product of <= 6 token values once integer powers are expanded
-            int nsf[TMAX];
-            int sf[TMAX][6];
-            q.fast = 1;
-            for (int t = 0; t < q.T; ++t) {
-                nsf[t] = 0;
-                for (int f = q.fac_off[t]; f < q.fac_off[t + 1]; ++f) {
-                    factors[f].slot = slot[fac_token[f]];
-                    if (factors[f].kind != 0 || factors[f].ipow == 0) { q.fast = 0; continue; }
-                    for (int k = 0; k < factors[f].ipow; ++k) {
-                        if (nsf[t] < 6) sf[t][nsf[t]] = factors[f].slot;
-                        ++nsf[t];
-                    }
+        std::map<int, int> col_of;
+        for (size_t k = 0; k < g.col_term.size(); ++k) col_of[g.col_term[k]] = (int)k;
+        const int ones = (int)g.col_term.size();
+        g.ncols = ones + 1;
+        g.cp = (g.ncols + 7) & ~7;
+        const int nblk = g.cp / 8;
+        // columns
+        const int nbuild = g.cp + (b->weighted ? 1 : 0);
+        std::vector<ColDesc> cols(nbuild);
+        std::vector<FactorDesc> gfac;
+        for (int k = 0; k < nbuild; ++k) { memset(&cols[k], 0, sizeof(ColDesc)); cols[k].kind = 3; for (int q = 0; q < MAXSF; ++q) cols[k].off[q] = -1; }
+        for (int k = 0; k < ones; ++k) {
+            const int t = term_first[g.col_term[k]];
+            ColDesc& cd = cols[k];
+            bool fast = true;
+            int nsf = 0;
+            for (int f = fac_off[t]; f < fac_off[t + 1]; ++f) {
+                const int kind = fac_kind ? fac_kind[f] : 0;
+                const double pw = fac_power[f];
+                const int ip = (pw == 1.0) ? 1 : (pw == 2.0) ? 2 : (pw == 3.0) ? 3 : 0;
+                if (kind != 0 || ip == 0) { fast = false; continue; }
+                for (int q = 0; q < ip; ++q) { if (nsf < MAXSF) cd.off[nsf] = slot[fac_token[f]]; ++nsf; }
+            }
+            if (nsf > MAXSF) fast = false;
+            if (fast) { cd.kind = 0; cd.nf = (short)nsf; }
+            else {
+                cd.kind = 1; cd.nf = (short)(fac_off[t + 1] - fac_off[t]); cd.gfac_off = (int)gfac.size();
+                for (int f = fac_off[t]; f < fac_off[t + 1]; ++f) {
+                    FactorDesc d;
+                    memset(&d, 0, sizeof d);
+                    d.slot = slot[fac_token[f]];
+                    d.power = fac_power[f];
+                    d.kind = fac_kind ? fac_kind[f] : 0;
+                    d.param = fac_param ? fac_param[f] : 0.0;
+                    d.ipow = (d.power == 1.0) ? 1 : (d.power == 2.0) ? 2 : (d.power == 3.0) ? 3 : 0;
+                    gfac.push_back(d);
                 }
-                if (nsf[t] > 6) q.fast = 0;
-            }
-            for (int t = 0; t < TMAX; ++t) {
-                q.fastop[t] = make_int4(0, -1, -1, -1); q.fastop2[t] = make_int2(-1, -1);
-                q.pos[t] = q.perm[t] = (unsigned char)t;
-            }
-            // evaluation order: most slot factors first (fast equations only)
-            q.n2 = q.n3 = 0;
-            if (q.fast) {
-                int k = 0;
-                for (int want = 6; want >= 1; --want)
-                    for (int t = 0; t < q.T; ++t)
-                        if (nsf[t] == want) { q.perm[k] = (unsigned char)t; q.pos[t] = (unsigned char)k; ++k; }
-                for (int t = 0; t < q.T; ++t) {
-                    if (nsf[t] >= 2) ++q.n2;
-                    if (nsf[t] >= 3 && q.n3 < 1) q.n3 = 1;
-                    if (nsf[t] >= 5) q.n3 = 2;
-                    int4& op = q.fastop[q.pos[t]];
-                    op.x = sf[t][0];
-                    if (nsf[t] >= 2) op.z = sf[t][1];
-                    if (nsf[t] >= 3) op.y = sf[t][2];
-                    if (nsf[t] >= 4) op.w = sf[t][3];
-                    if (nsf[t] >= 5) q.fastop2[q.pos[t]].x = sf[t][4];
-                    if (nsf[t] >= 6) q.fastop2[q.pos[t]].y = sf[t][5];
-                }
-            }
-            {
-                int k = 0;
-                for (int i = 0; i < q.T; ++i)
-                    for (int j = i; j < q.T; ++j) q.accmap[k++] = (unsigned char)gidx(q.perm[i], q.perm[j], q.T);
-                for (int i = 0; i < q.T; ++i) q.accmap[k++] = (unsigned char)(q.T * (q.T + 1) / 2 + q.perm[i]);
             }
         }
+        cols[ones].kind = 2;
+        if (b->weighted) { cols[g.cp].kind = 0; cols[g.cp].nf = 1; cols[g.cp].off[0] = (int)g.token_ids.size(); }
+        g.n_gfac = (int)gfac.size();
+        // needed pairs -> entries
+        std::vector<int> pairent((size_t)g.cp * g.cp, -1);
+        for (int e : g.eqs) {
+            EqDesc& q = b->eqs[e];
+            memset(q.col, 0, sizeof q.col);
+            q.T = term_off[e + 1] - term_off[e];
+            for (int t = 0; t < q.T; ++t) q.col[t] = (short)col_of[term_of[term_off[e] + t]];
+            q.col[q.T] = (short)ones;
+            for (int i = 0; i <= q.T; ++i)
+                for (int j = 0; j <= q.T; ++j) pairent[(size_t)q.col[i] * g.cp + q.col[j]] = 0;
+        }
+        int n_ent = 0;
+        for (int i = 0; i < g.cp; ++i)
+            for (int j = i; j < g.cp; ++j)
+                if (pairent[(size_t)i * g.cp + j] == 0) { pairent[(size_t)i * g.cp + j] = pairent[(size_t)j * g.cp + i] = n_ent++; }
+        g.n_ent = n_ent;
+        if (n_cells * (size_t)n_ent * sizeof(double) > c->cell_budget_bytes) {
+            delete b;
+            return fail("launch group %zu needs a cell table of %zu bytes (> %zu): grid too fine for this many distinct terms",
+                        gi, n_cells * (size_t)n_ent * sizeof(double), c->cell_budget_bytes);
+        }
+        // block pairs, tasks, flush maps
+        std::vector<char> need((size_t)nblk * nblk, 0);
+        for (int i = 0; i < g.cp; ++i)
+            for (int j = i; j < g.cp; ++j)
+                if (pairent[(size_t)i * g.cp + j] >= 0) need[(size_t)(i / 8) * nblk + j / 8] = 1;
+        std::vector<TaskDesc> tasks;
+        build_tasks(nblk, need, tasks);
+        g.ntasks = (int)tasks.size();
+        if (g.ntasks > GRAM_MAX_WARPS) { delete b; return fail("internal: %d pass-A tasks exceed %d warps", g.ntasks, GRAM_MAX_WARPS); }
+        g.ksplit = (g.ntasks >= 8) ? 1 : std::max(1, std::min(4, GRAM_MAX_WARPS / g.ntasks));
+        std::vector<int> flush((size_t)g.ntasks * TASK_PAIRS * 64, -1);
+        for (int t = 0; t < g.ntasks; ++t)
+            for (int m = 0; m < TASK_PAIRS; ++m) {
+                if (!((tasks[t].mask >> m) & 1)) continue;
+                const int I = tasks[t].ablk[m / TASK_B], J = tasks[t].bblk[m % TASK_B];
+                for (int l = 0; l < 32; ++l)
+                    for (int h = 0; h < 2; ++h) {
+                        const int ci = I * 8 + l / 4, cj = J * 8 + 2 * (l % 4) + h;
+                        if (ci <= cj) flush[((size_t)(t * TASK_PAIRS + m) * 32 + l) * 2 + h] = pairent[(size_t)ci * g.cp + cj];
+                    }
+            }
+        // pass-B jobs.  Sum slots: the evals of every equation of <= DJ_T terms (one dense job per equation, heaviest
+        // first), then the evals of longer equations (one sparse job each); distinct target columns for sum|t|
+        std::vector<int> dense_eqs, sparse_eqs;
+        for (int e : g.eqs) {
+            if (eq_evals[e].empty()) continue;
+            ((term_off[e + 1] - term_off[e]) <= DJ_T ? dense_eqs : sparse_eqs).push_back(e);
+        }
+        std::stable_sort(dense_eqs.begin(), dense_eqs.end(), [&](int a, int bb) {
+            return (term_off[a + 1] - term_off[a]) * eq_evals[a].size() > (term_off[bb + 1] - term_off[bb]) * eq_evals[bb].size(); });
+        std::vector<int> slot_ev, dj_eq, dj_slot0;
+        for (int e : dense_eqs) {
+            dj_eq.push_back(e); dj_slot0.push_back((int)slot_ev.size());
+            for (int v : eq_evals[e]) slot_ev.push_back(v);
+        }
+        g.n_dense = (int)dense_eqs.size();
+        for (int e : sparse_eqs)
+            for (int v : eq_evals[e]) slot_ev.push_back(v);
+        g.n_slots = (int)slot_ev.size();
+        g.n_sparse = g.n_slots - (dj_slot0.empty() ? 0 : (int)(dj_slot0.back() + eq_evals[dense_eqs.back()].size()));
+        std::set<int> tset;
+        for (int v : slot_ev) tset.insert((int)b->eqs[eval_eq[v]].col[eval_target[v]]);
+        std::vector<int> tcols(tset.begin(), tset.end()), slot_tci;
+        for (int v : slot_ev)
+            slot_tci.push_back((int)(std::lower_bound(tcols.begin(), tcols.end(), (int)b->eqs[eval_eq[v]].col[eval_target[v]]) - tcols.begin()));
+        g.n_tcols = (int)tcols.size();
+        // tables
+        g.seg_off = seg_off; seg_off += (long long)c->geom.n_rows * n_ent + (b->weighted ? n_ent : 0);
+        g.win_off = win_off; win_off += (long long)(W + 1) * n_ent;
+        g.pe_off = (long long)pairent_all.size();
+        pairent_all.insert(pairent_all.end(), pairent.begin(), pairent.end());
+        for (int e : g.eqs) {
+            EqDesc& q = b->eqs[e];
+            q.ones_col = ones; q.n_ent = n_ent; q.w_off = g.win_off; q.pe_off = g.pe_off; q.cp = g.cp;
+        }
+        goff[gi].cols = put(cols.data(), cols.size() * sizeof(ColDesc));
+        goff[gi].gfac = put(gfac.data(), gfac.size() * sizeof(FactorDesc));
+        goff[gi].tasks = put(tasks.data(), tasks.size() * sizeof(TaskDesc));
+        goff[gi].flush = put(flush.data(), flush.size() * sizeof(int));
+        goff[gi].slot_ev = put(slot_ev.data(), slot_ev.size() * sizeof(int));
+        goff[gi].slot_tci = put(slot_tci.data(), slot_tci.size() * sizeof(int));
+        goff[gi].dj_eq = put(dj_eq.data(), dj_eq.size() * sizeof(int));
+        goff[gi].dj_slot0 = put(dj_slot0.data(), dj_slot0.size() * sizeof(int));
+        goff[gi].tcols = put(tcols.data(), tcols.size() * sizeof(int));
     }
-    // task order inside a group: most terms first, equations that run the same code variant (T, factor class)
-    // next to each other, so the warps of a CTA execute the same instructions at the same time
-    for (auto& g : b->groups) {
-        auto key = [&](int e) {
-            const EqDesc& q = b->eqs[e];
-            return (q.T << 8) | ((q.n2 <= 2 ? q.n2 : 3) << 4) | (q.n3 << 2) | (q.fast ? 0 : 2);
-        };
-        std::stable_sort(g.eqs.begin(), g.eqs.end(), [&](int a, int bb) { return key(a) > key(bb); });
-    }
-    std::vector<int> slot_eval((size_t)n_eq * TMAX, -1);
-    for (int v = 0; v < n_eval; ++v) {
-        const int e = eval_eq[v], t = eval_target[v];
-        if (e < 0 || e >= n_eq) { delete b; return fail("eval %d references equation %d", v, e); }
-        if (t < 0 || t >= b->eqs[e].T) { delete b; return fail("eval %d: target %d outside equation %d (%d terms)", v, t, e, b->eqs[e].T); }
-        if (slot_eval[(size_t)e * TMAX + t] >= 0) { delete b; return fail("eval %d duplicates (equation %d, target %d)", v, e, t); }
-        slot_eval[(size_t)e * TMAX + t] = v;
-        if (b->eqs[e].T + 1 <= 8) b->evals_gs8.push_back(v); else b->evals_gs16.push_back(v);
-    }
-    // lists: equations by group, evals by solver group size
+    b->seg_doubles = seg_off;
+    b->win_doubles = win_off;
     std::vector<int> lists;
-    for (auto& g : b->groups) {
-        g.list_off = (int)lists.size();
-        lists.insert(lists.end(), g.eqs.begin(), g.eqs.end());
-    }
-    b->off_gs8 = (int)lists.size();
-    lists.insert(lists.end(), b->evals_gs8.begin(), b->evals_gs8.end());
-    b->off_gs16 = (int)lists.size();
-    lists.insert(lists.end(), b->evals_gs16.begin(), b->evals_gs16.end());
-    if (lists.empty()) lists.push_back(0);
-    // pack the encoding into one pinned staging buffer -> one H2D copy
-    auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
-    const size_t o_eqs = 0;
-    const size_t o_fac = align(o_eqs + sizeof(EqDesc) * n_eq);
-    const size_t o_eveq = align(o_fac + sizeof(FactorDesc) * std::max(1, b->n_fac));
-    const size_t o_evtg = align(o_eveq + sizeof(int) * std::max(1, n_eval));
-    const size_t o_slot = align(o_evtg + sizeof(int) * std::max(1, n_eval));
-    const size_t o_list = align(o_slot + sizeof(int) * slot_eval.size());
-    const size_t total = align(o_list + sizeof(int) * lists.size());
+    b->off_gs8 = (int)lists.size();  lists.insert(lists.end(), b->evals_gs8.begin(), b->evals_gs8.end());
+    b->off_gs16 = (int)lists.size(); lists.insert(lists.end(), b->evals_gs16.begin(), b->evals_gs16.end());
+    b->off_gs32 = (int)lists.size(); lists.insert(lists.end(), b->evals_gs32.begin(), b->evals_gs32.end());
+    const size_t o_eqs = put(b->eqs.data(), sizeof(EqDesc) * n_eq);
+    const size_t o_eveq = put(eval_eq, sizeof(int) * n_eval);
+    const size_t o_evtg = put(eval_target, sizeof(int) * n_eval);
+    const size_t o_list = put(lists.data(), sizeof(int) * lists.size());
+    const size_t o_pe = put(pairent_all.data(), sizeof(int) * pairent_all.size());
+    const size_t total = align(img.size());
     // the pinned buffer may still feed an earlier asynchronous copy
     cudaStreamSynchronize(c->stream);
     if (ensure_pinned(c, total) || c->d_enc.ensure(total)) { delete b; return 1; }
-    char* h = (char*)c->h_pinned;
-    memcpy(h + o_eqs, b->eqs.data(), sizeof(EqDesc) * n_eq);
-    memcpy(h + o_fac, factors.data(), sizeof(FactorDesc) * b->n_fac);
-    if (n_eval) { memcpy(h + o_eveq, eval_eq, sizeof(int) * n_eval); memcpy(h + o_evtg, eval_target, sizeof(int) * n_eval); }
-    memcpy(h + o_slot, slot_eval.data(), sizeof(int) * slot_eval.size());
-    memcpy(h + o_list, lists.data(), sizeof(int) * lists.size());
-    cudaError_t ce = cudaMemcpyAsync(c->d_enc.ptr, h, total, cudaMemcpyHostToDevice, c->stream);
+    memcpy(c->h_pinned, img.data(), img.size());
+    cudaError_t ce = cudaMemcpyAsync(c->d_enc.ptr, c->h_pinned, total, cudaMemcpyHostToDevice, c->stream);
     if (ce != cudaSuccess) { delete b; return fail("encoding upload failed: %s", cudaGetErrorString(ce)); }
     char* d = (char*)c->d_enc.ptr;
     b->d_eqs = (EqDesc*)(d + o_eqs);
-    b->d_factors = (FactorDesc*)(d + o_fac);
     b->d_eval_eq = (int*)(d + o_eveq);
     b->d_eval_tgt = (int*)(d + o_evtg);
-    b->d_slot_eval = (int*)(d + o_slot);
     b->d_lists = (int*)(d + o_list);
+    b->d_pairent = (int*)(d + o_pe);
+    for (size_t gi = 0; gi < b->groups.size(); ++gi) {
+        LaunchGroup& g = b->groups[gi];
+        g.d_cols = (ColDesc*)(d + goff[gi].cols); g.d_gfac = (FactorDesc*)(d + goff[gi].gfac);
+        g.d_tasks = (TaskDesc*)(d + goff[gi].tasks); g.d_flush = (int*)(d + goff[gi].flush);
+        g.d_slot_ev = (int*)(d + goff[gi].slot_ev); g.d_slot_tci = (int*)(d + goff[gi].slot_tci); g.d_tcols = (int*)(d + goff[gi].tcols);
+        g.d_dj_eq = (int*)(d + goff[gi].dj_eq); g.d_dj_slot0 = (int*)(d + goff[gi].dj_slot0);
+    }
     // outputs
     const size_t ne = (size_t)std::max(1, n_eval);
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align(o + bytes); return r; };
-    const size_t oc = take(ne * TMAX * 8), oi = take(ne * 8), ost = take(ne * 8), osw = take(ne * W * KS * 8),
-                 owt = take(ne * TMAX * 8), osu = take(ne * 3 * 8), ob1 = take(ne * 8), ona = take(ne * 4), oaz = take(ne * 4), oit = take(ne * 4);
-    b->out_bytes = o;
+    const size_t oc = take(ne * TMAX * 8), oi = take(ne * 8), ost = take(ne * 8), owt = take(ne * TMAX * 8), osu = take(ne * 3 * 8),
+                 ob1 = take(ne * 8), ona = take(ne * 4), oaz = take(ne * 4), oit = take(ne * 4);
+    const size_t small_bytes = o;
+    const size_t osw = take(ne * W * KS * 8);
+    b->out_bytes = small_bytes;
     if (c->d_out.ensure(o)) { delete b; return 1; }
     char* od = (char*)c->d_out.ptr;
     b->d_coef = (double*)(od + oc); b->d_intercept = (double*)(od + oi); b->d_stab = (double*)(od + ost);
@@ -2427,6 +2250,80 @@ int epde_batch_residual_size(epde_batch* b, int64_t* n) {
     return 0;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)
+static PFN_cuTensorMapEncodeTiled_v12000 tensor_map_encoder() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess) fn = (PFN_cuTensorMapEncodeTiled_v12000)f;
+    }
+    return fn;
+}
+
+// tensor map of one token vector seen as the context's N-d grid, box = one pass-A token tile
+static int make_token_map(const epde_ctx* c, const double* base, CUtensorMap* out) {
+    auto enc = tensor_map_encoder();
+    if (!enc) return fail("cuTensorMapEncodeTiled is not available from this driver");
+    const int nd = c->ndim;
+    cuuint64_t dims[3]; cuuint64_t strides[2]; cuuint32_t box[3]; cuuint32_t estr[3] = {1, 1, 1};
+    if (nd == 3) {
+        dims[0] = c->shape[2]; dims[1] = c->shape[1]; dims[2] = c->shape[0];
+        strides[0] = c->shape[2] * 8; strides[1] = c->shape[2] * c->shape[1] * 8;
+        box[0] = c->box_c; box[1] = c->box_b; box[2] = c->box_a;
+    } else if (nd == 2) {
+        dims[0] = c->shape[1]; dims[1] = c->shape[0];
+        strides[0] = c->shape[1] * 8;
+        box[0] = c->box_c; box[1] = c->box_b;
+    } else {
+        dims[0] = c->shape[0];
+        box[0] = c->box_c;
+    }
+    const CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, nd, (void*)base, dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r);
+    return 0;
+}
+
+// one pass-A launch of a launch group: cell table of the (weighted or unweighted) column Gram
+static int launch_gram(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double* cells, bool weighted) {
+    (void)b;
+    static GramParams p;                        // 2.2 KB with the tensor maps: keep it off the stack
+    memset(&p, 0, sizeof p);
+    p.g = c->geom; p.cols = g.d_cols; p.gfac = g.d_gfac;
+    p.cp = g.cp;
+    p.U = (int)g.token_ids.size();
+    for (int u = 0; u < p.U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
+    p.nbuild = g.cp; p.wcol = g.cp;
+    if (weighted) { p.tok[p.U++] = c->weights; p.nbuild = g.cp + 1; }
+    p.tasks = g.d_tasks; p.ntasks = g.ntasks; p.ksplit = g.ksplit; p.flushmap = g.d_flush;
+    p.cells = cells; p.n_ent = g.n_ent;
+    p.box_a = c->box_a; p.box_b = c->box_b; p.box_c = c->box_c;
+    p.use_tma = (c->geom.aligned16 && tensor_map_encoder() && c->box_a <= 256 && c->box_b <= 256) ? 1 : 0;
+    if (getenv("EPDE_DEBUG_NO_TMA")) p.use_tma = 0;   // DEBUG ONLY
+    if (p.use_tma)
+        for (int u = 0; u < p.U; ++u)
+            if (make_token_map(c, p.tok[u], &p.tmap[u])) return 1;
+    const int nwarps = std::min(GRAM_MAX_WARPS, std::max(8, g.ntasks * g.ksplit));
+    const size_t tstride = ((size_t)p.box_a * p.box_b * p.box_c + 15) & ~(size_t)15;
+    const size_t smem = sizeof(double) * ((size_t)p.U * tstride + (size_t)p.nbuild * PP_A) + sizeof(ColDesc) * (size_t)p.nbuild +
+                        (g.ksplit > 1 ? sizeof(double) * (size_t)g.ntasks * (g.ksplit - 1) * TASK_PAIRS * 2 * 32 : 0);
+    if (smem > (size_t)c->smem_gram) return fail("pass A needs %zu bytes of shared memory (> %d)", smem, c->smem_gram);
+    const int per = (2 * (smem + 1024) <= (size_t)c->max_smem + 1024) ? 2 : 1;
+    const unsigned grid = (unsigned)std::min<long long>(c->geom.n_units, (long long)c->sm_count * per);
+    {
+        KernelSpan ks(c, EPDE_KERNEL_GRAM);
+        if (weighted) gram_dmma_kernel<true><<<grid, nwarps * 32, smem, c->stream>>>(p);
+        else gram_dmma_kernel<false><<<grid, nwarps * 32, smem, c->stream>>>(p);
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
 int epde_batch_gram(epde_batch* b, double* dev_seg) {
     if (!b || !b->ctx) return fail("null batch");
     epde_ctx* c = b->ctx;
@@ -2435,30 +2332,30 @@ int epde_batch_gram(epde_batch* b, double* dev_seg) {
         if (c->d_seg.ensure(sizeof(double) * (size_t)b->seg_doubles)) return 1;
         dev_seg = (double*)c->d_seg.ptr;
     }
-    long long need = 0;
-    for (auto& g : b->groups) need = std::max(need, g.cell_doubles);
-    if (c->d_cells.ensure(sizeof(double) * (size_t)need)) return 1;
+    size_t need = 0;
+    for (auto& g : b->groups) need = std::max(need, (size_t)c->n_cells * g.n_ent);
+    if (c->d_cells.ensure(sizeof(double) * need)) return 1;
+    double* cells = (double*)c->d_cells.ptr;
     for (auto& g : b->groups) {
-        if (launch_gram_group(c, b, g, (double*)c->d_cells.ptr)) return 1;
-        MargParams mp;
-        mp.g = c->geom; mp.eqs = b->d_eqs; mp.eq_list = b->d_lists + g.list_off;
-        mp.cells = (const double*)c->d_cells.ptr; mp.seg = dev_seg;
-        dim3 grid(c->geom.n_rows, (unsigned)g.eqs.size());
-        const size_t slab_smem = sizeof(double) * (size_t)c->geom.npieces * nacc_of(TMAX);
-        if (c->ndim == 3 && c->geom.nA >= 4 && slab_smem <= 40 * 1024) {
-            MargSlabParams sp;
-            sp.g = c->geom; sp.eqs = mp.eqs; sp.eq_list = mp.eq_list; sp.cells = mp.cells; sp.seg = dev_seg;
-            sp.eq_stride = (long long)c->geom.nA * (1 + c->geom.nB + c->geom.npieces) * nacc_of(TMAX);
-            if (c->d_marg.ensure(sizeof(double) * (size_t)sp.eq_stride * g.eqs.size())) return 1;
-            sp.part = (double*)c->d_marg.ptr;
+        double* seg = dev_seg + g.seg_off;
+        const unsigned ey = (unsigned)((g.n_ent + 127) / 128);
+        if (b->weighted) {
+            // unweighted total Gram first (LASSO sums, sparsity.py:54-55,73-76), kept behind the segment rows
+            if (launch_gram(c, b, g, cells, false)) return 1;
+            TotalParams tp;
+            tp.cells = cells; tp.n_cells = c->n_cells; tp.n_ent = g.n_ent; tp.parts = std::min(c->n_cells, 256);
+            if (c->d_total.ensure(sizeof(double) * (size_t)tp.parts * g.n_ent)) return 1;
+            tp.part = (double*)c->d_total.ptr; tp.total = seg + (long long)c->geom.n_rows * g.n_ent;
             KernelSpan ks(c, EPDE_KERNEL_MARGINAL);
-            marginal_slab_kernel<<<dim3(c->geom.nA, (unsigned)g.eqs.size()), 256, slab_smem, c->stream>>>(sp);
-            marginal_rows_kernel<<<grid, 64, 0, c->stream>>>(sp);
+            total_part_kernel<<<dim3(tp.parts, ey), 128, 0, c->stream>>>(tp);
+            total_final_kernel<<<ey, 128, 0, c->stream>>>(tp);
             c->launches++;
-        } else {
-            KernelSpan ks(c, EPDE_KERNEL_MARGINAL);
-            marginal_kernel<<<grid, 256, 0, c->stream>>>(mp);
+            CK(cudaGetLastError());
         }
+        if (launch_gram(c, b, g, cells, b->weighted)) return 1;
+        MargParams mp;
+        mp.g = c->geom; mp.cells = cells; mp.seg = seg; mp.n_ent = g.n_ent;
+        { KernelSpan ks(c, EPDE_KERNEL_MARGINAL); marginal_kernel<<<dim3(c->geom.n_rows, ey), 128, 0, c->stream>>>(mp); }
         CK(cudaGetLastError());
     }
     return 0;
@@ -2468,16 +2365,21 @@ int epde_batch_solve(epde_batch* b, const double* dev_seg) {
     if (!b || !b->ctx) return fail("null batch");
     epde_ctx* c = b->ctx;
     CK(cudaSetDevice(c->device));
-    double* seg = dev_seg ? (double*)dev_seg : (double*)c->d_seg.ptr;
+    const double* seg = dev_seg ? dev_seg : (const double*)c->d_seg.ptr;
     if (!seg) return fail("epde_batch_solve: no segment Grams (call epde_batch_gram first)");
     if (c->d_win.ensure(sizeof(double) * (size_t)b->win_doubles)) return 1;
-    WindowParams wp;
-    wp.g = c->geom; wp.eqs = b->d_eqs; wp.seg = seg; wp.win = (double*)c->d_win.ptr;
-    { KernelSpan ks(c, EPDE_KERNEL_MARGINAL); window_gram_kernel<<<dim3(c->geom.n_windows + 1, b->n_eq), 64, 0, c->stream>>>(wp); }
-    CK(cudaGetLastError());
+    for (auto& g : b->groups) {
+        WindowParams wp;
+        wp.g = c->geom; wp.seg = seg + g.seg_off; wp.win = (double*)c->d_win.ptr + g.win_off; wp.n_ent = g.n_ent;
+        wp.total = b->weighted ? seg + g.seg_off + (long long)c->geom.n_rows * g.n_ent : nullptr;
+        KernelSpan ks(c, EPDE_KERNEL_MARGINAL);
+        window_gram_kernel<<<dim3(c->geom.n_windows + 1, (unsigned)((g.n_ent + 127) / 128)), 128, 0, c->stream>>>(wp);
+        CK(cudaGetLastError());
+    }
     if (b->n_eval > 0) {
         SolveParams sp;
         sp.g = c->geom; sp.eqs = b->d_eqs; sp.eval_eq = b->d_eval_eq; sp.eval_tgt = b->d_eval_tgt; sp.win = (const double*)c->d_win.ptr;
+        sp.pairent = b->d_pairent;
         sp.mode = b->d_mode; sp.given_wterm = b->d_given_w; sp.given_b = b->d_given_b;
         sp.coef = b->d_coef; sp.intercept = b->d_intercept; sp.intercept_l1 = b->d_b1; sp.stability = b->d_stab; sp.sw = b->d_sw;
         sp.wterm = b->d_wterm; sp.n_active = b->d_nact; sp.all_zero = b->d_allzero; sp.iters = b->d_iters;
@@ -2492,6 +2394,11 @@ int epde_batch_solve(epde_batch* b, const double* dev_seg) {
             { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<16><<<(unsigned)b->evals_gs16.size(), SOLVE_THREADS, smem, c->stream>>>(sp); }
             CK(cudaGetLastError());
         }
+        if (!b->evals_gs32.empty()) {
+            sp.eval_list = b->d_lists + b->off_gs32;
+            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<32><<<(unsigned)b->evals_gs32.size(), SOLVE_THREADS, smem, c->stream>>>(sp); }
+            CK(cudaGetLastError());
+        }
     }
     b->solved = true;
     return 0;
@@ -2504,8 +2411,54 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
     CK(cudaSetDevice(c->device));
     double* sums = dev_sums ? dev_sums : b->d_sums;
     if (b->n_eval == 0) return 0;
-    for (auto& g : b->groups)
-        if (launch_resid_group(c, b, g, sums)) return 1;
+    const long long n_chunks = (c->N + PT_B - 1) / PT_B;
+    // one persistent CTA per SM: the chunk -> CTA assignment (and with it the summation order) depends only on the
+    // grid size, never on what else is in the batch
+    const int grid = (int)std::min<long long>(n_chunks, (long long)c->sm_count);
+    auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    for (auto& g : b->groups) {
+        if (g.n_slots == 0) continue;
+        const size_t o_ej = align(sizeof(DenseJob) * (size_t)g.n_dense), o_col = align(o_ej + sizeof(EvalJob) * (size_t)g.n_sparse),
+                     o_w = align(o_col + sizeof(short) * (size_t)g.n_sparse * TMAX), tot = align(o_w + sizeof(double) * (size_t)g.n_sparse * TMAX);
+        if (c->d_jobs.ensure(tot)) return 1;
+        char* jb = (char*)c->d_jobs.ptr;
+        ResidProgParams pp;
+        pp.eqs = b->d_eqs; pp.eval_eq = b->d_eval_eq; pp.eval_tgt = b->d_eval_tgt;
+        pp.dj_eq = g.d_dj_eq; pp.dj_slot0 = g.d_dj_slot0; pp.slot_ev = g.d_slot_ev;
+        pp.wterm = b->d_wterm; pp.intercept = b->d_intercept; pp.intercept_l1 = b->d_b1;
+        pp.djobs = (DenseJob*)jb; pp.jobs = (EvalJob*)(jb + o_ej); pp.job_col = (short*)(jb + o_col); pp.job_w = (double*)(jb + o_w);
+        pp.n_dense = g.n_dense; pp.n_sparse = g.n_sparse; pp.n_slots = g.n_slots;
+        { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_prog_kernel<<<(g.n_dense + g.n_sparse + 63) / 64, 64, 0, c->stream>>>(pp); }
+        CK(cudaGetLastError());
+        ResidParams p;
+        memset(&p, 0, sizeof p);
+        p.N = c->N; p.U = (int)g.token_ids.size();
+        for (int u = 0; u < p.U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
+        p.cols = g.d_cols; p.gfac = g.d_gfac; p.nbuild = g.cp;
+        p.djobs = pp.djobs; p.n_dense = g.n_dense;
+        p.jobs = pp.jobs; p.job_col = pp.job_col; p.job_w = pp.job_w; p.n_sparse = g.n_sparse;
+        p.n_slots = g.n_slots; p.tcols = g.d_tcols; p.n_tcols = g.n_tcols;
+        p.n_chunks = (int)n_chunks; p.aligned = 1;
+        const int nsum = 2 * g.n_slots + g.n_tcols;
+        if (c->d_partial.ensure(sizeof(double) * (size_t)grid * nsum)) return 1;
+        p.partial = (double*)c->d_partial.ptr;
+        const size_t tile_bytes = sizeof(double) * (size_t)p.U * PT_B;
+        const size_t rest = sizeof(double) * ((size_t)g.cp * PP_B + nsum) + sizeof(ColDesc) * (size_t)g.cp;
+        p.nstages = (2 * tile_bytes + rest <= (size_t)c->smem_resid) ? 2 : 1;
+        const size_t smem = p.nstages * tile_bytes + rest;
+        if (smem > (size_t)c->smem_resid) return fail("pass B needs %zu bytes of shared memory (> %d)", smem, c->smem_resid);
+        {
+            KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
+            if (b->want_l2) residual_cols_kernel<true><<<grid, RES_WARPS * 32, smem, c->stream>>>(p);
+            else residual_cols_kernel<false><<<grid, RES_WARPS * 32, smem, c->stream>>>(p);
+        }
+        CK(cudaGetLastError());
+        ResidFinalParams fp;
+        fp.slot_ev = g.d_slot_ev; fp.slot_tci = g.d_slot_tci; fp.partial = p.partial; fp.sums = sums;
+        fp.n_slots = g.n_slots; fp.n_tcols = g.n_tcols; fp.n_cta = grid; fp.want_l2 = b->want_l2 ? 1 : 0;
+        { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_final_kernel<<<(g.n_slots + 127) / 128, 128, 0, c->stream>>>(fp); }
+        CK(cudaGetLastError());
+    }
     return 0;
 }
 
@@ -2522,17 +2475,20 @@ int epde_batch_fetch(epde_batch* b, const double* dev_sums, double* coef, double
     // the pinned buffer doubles as the encoding staging area; the encoding copy is complete once
     // the stream reaches this point, so synchronise before reallocating / overwriting it
     CK(cudaStreamSynchronize(c->stream));
-    if (ensure_pinned(c, std::max(b->out_bytes, (size_t)1))) return 1;
+    const int W = c->geom.n_windows;
+    const size_t sw_bytes = sw_weights ? sizeof(double) * (size_t)ne * W * KS : 0;
+    if (ensure_pinned(c, b->out_bytes + sw_bytes + 256)) return 1;
     CK(cudaMemcpyAsync(c->h_pinned, c->d_out.ptr, b->out_bytes, cudaMemcpyDeviceToHost, c->stream));
+    // the sliding-window weights (ne x W x KS doubles) are copied only when the caller wants them
+    if (sw_weights) CK(cudaMemcpyAsync((char*)c->h_pinned + b->out_bytes, b->d_sw, sw_bytes, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     const char* h = (const char*)c->h_pinned;
     const char* d0 = (const char*)c->d_out.ptr;
     auto hp = [&](const void* dptr) { return h + ((const char*)dptr - d0); };
-    const int W = c->geom.n_windows;
     if (coef) memcpy(coef, hp(b->d_coef), sizeof(double) * ne * TMAX);
     if (intercept) memcpy(intercept, hp(b->d_intercept), sizeof(double) * ne);
     if (stability) memcpy(stability, hp(b->d_stab), sizeof(double) * ne);
-    if (sw_weights) memcpy(sw_weights, hp(b->d_sw), sizeof(double) * (size_t)ne * W * KS);
+    if (sw_weights) memcpy(sw_weights, h + b->out_bytes, sw_bytes);
     if (n_active) memcpy(n_active, hp(b->d_nact), sizeof(int) * ne);
     if (all_zero) memcpy(all_zero, hp(b->d_allzero), sizeof(int) * ne);
     if (iters) memcpy(iters, hp(b->d_iters), sizeof(int) * ne);
@@ -2563,7 +2519,6 @@ int epde_evaluate_batch(epde_ctx* c, int n_eq, const int32_t* term_off, const in
     if (rc) g_err = keep;
     return rc;
 }
-
 int epde_ctx_synchronize(epde_ctx* c) {
     if (!c) return fail("null context");
     CK(cudaSetDevice(c->device));
@@ -2630,15 +2585,46 @@ int epde_cache_upload_interior(epde_ctx* c, int id, const double* dev_full, int 
     }
     CK(cudaSetDevice(c->device));
     double*& tok = c->tokens[id];
-    if (!tok) {
-        cudaError_t e = cudaMalloc((void**)&tok, sizeof(double) * (size_t)c->N);
-        if (e != cudaSuccess) { c->tokens.erase(id); return fail("epde_cache_upload_interior: out of device memory (%s)", cudaGetErrorString(e)); }
-    }
+    if (token_alloc(c, &tok, "epde_cache_upload_interior")) { c->tokens.erase(id); return 1; }
     p.out = tok;
     const int grid = (int)std::min<long long>((c->N + 255) / 256, (long long)c->sm_count * 16);
     c->launches++;
     crop_interior_kernel<<<grid, 256, 0, c->stream>>>(p);
     CK(cudaGetLastError());
+    return 0;
+}
+
+int epde_measure_fp64_peak(int device, double seconds, double* dfma_tflops, double* dmma_tflops) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+        return fail("epde_measure_fp64_peak: no such CUDA device %d", device);
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    const int grid = prop.multiProcessorCount * 4, iters = 4000;
+    double* out = nullptr;
+    CK(cudaMalloc((void**)&out, sizeof(double) * (size_t)grid * 256));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    double best[2] = {0.0, 0.0};
+    for (int which = 0; which < 2; ++which) {
+        const double flop = which == 0 ? 2.0 * grid * 256.0 * 8 * iters : 2.0 * grid * 8.0 * 8 * iters * 256.0;
+        double spent = 0.0;
+        for (int rep = 0; rep < 1000 && (rep < 3 || spent < 0.5 * seconds * 1e3); ++rep) {
+            CK(cudaEventRecord(e0));
+            if (which == 0) fp64_dfma_kernel<8><<<grid, 256>>>(out, iters, 1.0000001, 1e-9);
+            else fp64_dmma_kernel<8><<<grid, 256>>>(out, iters, 1.0000001, 1e-9);
+            CK(cudaEventRecord(e1));
+            CK(cudaEventSynchronize(e1));
+            float ms = 0.f;
+            CK(cudaEventElapsedTime(&ms, e0, e1));
+            spent += ms;
+            if (rep >= 1) best[which] = std::max(best[which], flop / (ms * 1e-3) * 1e-12);
+        }
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
+    if (dfma_tflops) *dfma_tflops = best[0];
+    if (dmma_tflops) *dmma_tflops = best[1];
     return 0;
 }
 

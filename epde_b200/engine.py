@@ -19,7 +19,7 @@ import numpy as np
 
 from . import _lib
 
-MAX_TERMS = 8          # EPDE_MAX_TERMS
+MAX_TERMS = 32         # EPDE_MAX_TERMS
 MAX_FACTORS = 4        # EPDE_MAX_FACTORS
 KS = MAX_TERMS + 1     # stride of a sliding-window weight row
 

@@ -36,7 +36,7 @@ extern "C" {
 #endif
 
 #define EPDE_MAX_NDIM 3
-#define EPDE_MAX_TERMS 8      /* terms per equation handled by the register-resident Gram kernels */
+#define EPDE_MAX_TERMS 32     /* terms per equation (window systems of up to 32 unknowns: one warp per system) */
 #define EPDE_MAX_FACTORS 4    /* factors per term */
 #define EPDE_MAX_TOKENS 4096
 
@@ -66,7 +66,9 @@ int epde_ctx_set_shard(epde_ctx* ctx, int64_t axis0_offset, int64_t axis0_global
  * doubles.  Unlike the reference there is no tensor-count budget: the call fails with an
  * out-of-memory status instead of silently refusing. */
 int epde_cache_upload(epde_ctx* ctx, int token_id, const double* host, int64_t n);
-/* same, from a device vector (device-to-device copy on the context stream). */
+/* same, from a device vector: an ASYNCHRONOUS device-to-device copy on the context stream.  Stream contract:
+ * the producer of `dev` must have been ordered before the context stream reaches this call (run it on the same
+ * stream -- epde_ctx_set_stream -- or synchronise it first); call epde_ctx_synchronize before freeing `dev`. */
 int epde_cache_upload_device(epde_ctx* ctx, int token_id, const double* dev, int64_t n);
 /* Cache.get (cache.py:397-452): copy the token back to a host vector. */
 int epde_cache_download(epde_ctx* ctx, int token_id, double* host, int64_t n);
@@ -77,8 +79,10 @@ int epde_cache_delete(epde_ctx* ctx, int token_id);
 /* Cache.consumed_memory (cache.py:305-330): bytes of HBM held by token vectors. */
 int epde_cache_bytes(epde_ctx* ctx, int64_t* bytes);
 /* sample weights of the window regressions = g_func[g_func_mask] (cache.py:219-244,
- * sparsity.py:202).  Only the default all-ones mask (interface.py:540-545) is supported by the
- * kernels in this version: any other vector fails loudly. */
+ * sparsity.py:202, supplementary.py:455: X^T W X, X^T W y per window).  The LASSO sums, the L1 fitness
+ * and the total Gram stay unweighted exactly as in the reference (sparsity.py:54-55,73-76,
+ * fitness.py:142).  A vector of ones (the default 0/1 mask restricted to the interior,
+ * interface.py:540-545) switches the weighted path off again. */
 int epde_ctx_set_sample_weights(epde_ctx* ctx, const double* host, int64_t n);
 
 /* ---- geometry of the sliding windows (supplementary.py:411-425) ----------------------------- */
@@ -174,6 +178,11 @@ int epde_fd_gradient(epde_ctx* ctx, const double* dev_in, double* dev_out, int n
                      int axis, const double* coords);
 int epde_cache_upload_interior(epde_ctx* ctx, int token_id, const double* dev_full, int ndim,
                                const int64_t* full_shape, const int64_t* boundary);
+
+/* Measurement aid (no reference counterpart): sustained FP64 rate of `device` in TFLOP/s through plain FMA
+ * chains (SASS DFMA) and through the FP64 tensor-core instruction pass A uses (mma.sync m8n8k4 f64, SASS
+ * DMMA.8x8x4), each run for about seconds / 2.  The roofline of the streaming passes is FP64 issue, not HBM. */
+int epde_measure_fp64_peak(int device, double seconds, double* dfma_tflops, double* dmma_tflops);
 
 /* number of kernel launches issued by the library on this context since creation. */
 int epde_ctx_launch_count(epde_ctx* ctx, int64_t* launches);

@@ -282,10 +282,10 @@ def test_cache_api():
         with pytest.raises(epde_b200.EpdeB200Error, match='not in the cache'):
             eng.evaluate(epde_b200.encode([[[(9, 1.0)], [(3, 1.0)]]]))
         with pytest.raises(epde_b200.EpdeB200Error):
-            eng.evaluate(epde_b200.encode([[[(3, 1.0)]] * 9]))          # too many terms
+            eng.evaluate(epde_b200.encode([[[(3, 1.0)]] * (epde_b200.MAX_TERMS + 1)]))          # too many terms
         eng.set_sample_weights(np.ones(120))
-        with pytest.raises(epde_b200.EpdeB200Error, match='all-ones'):
-            eng.set_sample_weights(np.full(120, 0.5))
+        with pytest.raises(epde_b200.EpdeB200Error, match='size mismatch'):
+            eng.set_sample_weights(np.full(50, 0.5))
         eng.delete(3)
         assert 3 not in eng and eng.consumed_memory == 0
 
