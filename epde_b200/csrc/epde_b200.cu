@@ -74,7 +74,7 @@
 #define GRAM_MAX_WARPS 12
 #define PT_B 256               // points per pass-B chunk
 #define PP_B (PT_B + 4)
-#define RES_WARPS 12
+#define RES_WARPS 16
 
 static thread_local std::string g_err;
 
@@ -226,6 +226,14 @@ __device__ __forceinline__ double apply_factor(const FactorDesc& f, double x) {
 __device__ __forceinline__ int4 lds_v4(unsigned a) {
     int4 v;
     asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+// shared load the compiler may schedule freely among the arithmetic of its consumers: not volatile, but tied to an
+// `epoch` value that is produced after the barrier which made the data visible (so it cannot be hoisted above that
+// barrier) and that differs between jobs (so loads of different jobs are never merged)
+__device__ __forceinline__ double lds_f64_e(unsigned a, int epoch) {
+    double v;
+    asm("ld.shared.f64 %0, [%1];  // epoch %2" : "=d"(v) : "r"(a), "r"(epoch));
     return v;
 }
 __device__ __forceinline__ void sts_f64(unsigned a, double v) {
@@ -869,100 +877,60 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
 // (fitness.py:135-142 and 70-83).  Persistent CTAs (one per SM) walk over chunks of PT_B consecutive points
 // (token rows of the chunk fetched with one bulk async copy per token, two stages).  Phase 1 builds the column tile
 // of the launch group's dictionary once per chunk; phase 2: warps take jobs from a shared counter:
-//   dense job   one equation of <= 8 terms with all its evals: the equation's columns are loaded into registers
-//               once per 128 points (lane <-> 4 points) and every eval is a predicated dot over them (only the
-//               non-zero coefficients issue FMAs); the <= 8 per-eval sums of the job are reduced over the warp
-//               together (reduce-scatter butterfly: 9 shuffle steps instead of 40);
-//   sparse job  one eval of a longer equation: sparse dot of its target and surviving columns read from the tile;
+//   octet job   8 consecutive evals of the group's list (sorted by target column): lane <-> 4 points per 128-point
+//               sweep; a residual is the sparse dot of the eval's target and surviving columns read from the column
+//               tile (the target column stays in registers while consecutive evals share it); the 8 per-eval sums are
+//               reduced over the warp together (reduce-scatter butterfly: 9 shuffle steps instead of 40);
 //   target job  sum|t| of one distinct target column.
 // Chunk sums go to a per-CTA shared table in chunk order, written once per CTA and reduced over CTAs in CTA order by
 // residual_final_kernel: fixed summation order, no atomics on data.
 // ------------------------------------------------------------------------------------------
-#define DJ_T 8               // terms / evals of a dense job
+#define OCT 8                // evals per octet job
 
-struct DenseJob {            // built on the device from the solve outputs (residual_prog_kernel)
-    short col[DJ_T];         // columns of the equation's terms
-    int T, D;                // terms, evals
-    int slot0;               // sum slot of eval 0 (the evals of a job occupy consecutive slots)
-    int pad;
-    unsigned char mask[DJ_T];// per eval: bit k set <-> w[v][k] != 0
-    unsigned char pad8[8];   // keeps the double rows 16-byte aligned
-    double b1[DJ_T];         // offset of the L1 residual
-    double delta[DJ_T];      // r2 = r + delta (b1 - intercept: non-zero only when no feature survives)
-    double w[DJ_T][DJ_T];    // w[v][k]: +1 at the target column, -coefficient at the surviving features
-};
-static_assert(sizeof(DenseJob) % 16 == 0, "DenseJob rows are read as 16-byte pieces");
-
-struct EvalJob {             // 32 bytes
-    int tcol, nnz, slot, pad;
-    double b1;
-    double delta;
+struct EvalJob {             // 32 bytes, built on the device from the solve outputs
+    int tcol, nnz, pad0, pad1;   // target column (byte offset of its row in the column tile), surviving features
+    double b1;               // offset of the L1 residual
+    double delta;            // r2 = r + delta (b1 - intercept: non-zero only when no feature survives)
 };
 
 struct ResidProgParams {
     const EqDesc* eqs;
     const int* eval_eq;
     const int* eval_tgt;
-    const int* dj_eq;        // [n_dense] equation of every dense job
-    const int* dj_slot0;     // [n_dense]
-    const int* slot_ev;      // [n_slots] eval id of every sum slot (dense jobs first, then sparse evals)
+    const int* slot_ev;      // [n_slots] eval id of every sum slot (sorted by target column)
     const double* wterm;     // [n_eval][TMAX]
     const double* intercept;
     const double* intercept_l1;
-    DenseJob* djobs;         // [n_dense]
-    EvalJob* jobs;           // [n_sparse]
-    short* job_col;          // [n_sparse][TMAX]
-    double* job_w;           // [n_sparse][TMAX]
-    int n_dense, n_sparse, n_slots;
+    EvalJob* jobs;           // [n_slots rounded up to OCT]
+    int* job_col;            // [n_slots][TMAX] byte offsets of the surviving columns' rows in the column tile
+    double* job_w;           // [n_slots][TMAX]
+    int n_slots;
 };
 
 __global__ void residual_prog_kernel(ResidProgParams p) {
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q < p.n_dense) {
-        const EqDesc& eq = p.eqs[p.dj_eq[q]];
-        DenseJob dj;
-        memset(&dj, 0, sizeof dj);
-        dj.T = eq.T; dj.slot0 = p.dj_slot0[q];
-        for (int k = 0; k < eq.T; ++k) dj.col[k] = eq.col[k];
-        int D = 0;
-        for (int s = dj.slot0; s < p.n_slots && D < DJ_T; ++s) {
-            const int ev = p.slot_ev[s];
-            if (p.eval_eq[ev] != p.dj_eq[q]) break;
-            const int tgt = p.eval_tgt[ev];
-            unsigned m = 0;
-            for (int k = 0; k < eq.T; ++k) {
-                double w = (k == tgt) ? 1.0 : -p.wterm[(long long)ev * TMAX + k];
-                if (w != 0.0) m |= 1u << k;
-                dj.w[D][k] = w;
-            }
-            dj.mask[D] = (unsigned char)m;
-            dj.b1[D] = p.intercept_l1[ev];
-            dj.delta[D] = p.intercept_l1[ev] - p.intercept[ev];
-            ++D;
-        }
-        dj.D = D;
-        p.djobs[q] = dj;
-    } else if (q < p.n_dense + p.n_sparse) {
-        const int jj = q - p.n_dense;
-        const int slot = p.n_slots - p.n_sparse + jj;
-        const int ev = p.slot_ev[slot];
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n_pad = (p.n_slots + OCT - 1) / OCT * OCT;
+    if (s >= n_pad) return;
+    EvalJob j;
+    j.tcol = 0; j.nnz = 0; j.pad0 = j.pad1 = 0; j.b1 = 0.0; j.delta = 0.0;
+    if (s < p.n_slots) {
+        const int ev = p.slot_ev[s];
         const EqDesc& eq = p.eqs[p.eval_eq[ev]];
         const int tgt = p.eval_tgt[ev];
         int nnz = 0;
         for (int t = 0; t < eq.T; ++t) {
             const double w = p.wterm[(long long)ev * TMAX + t];
             if (t != tgt && w != 0.0) {
-                p.job_col[(long long)jj * TMAX + nnz] = eq.col[t];
-                p.job_w[(long long)jj * TMAX + nnz] = w;
+                p.job_col[(long long)s * TMAX + nnz] = (int)eq.col[t] * (PP_B * 8);
+                p.job_w[(long long)s * TMAX + nnz] = w;
                 ++nnz;
             }
         }
-        EvalJob j;
-        j.tcol = eq.col[tgt]; j.nnz = nnz; j.slot = slot; j.pad = 0;
+        j.tcol = (int)eq.col[tgt] * (PP_B * 8); j.nnz = nnz;
         j.b1 = p.intercept_l1[ev];
         j.delta = p.intercept_l1[ev] - p.intercept[ev];
-        p.jobs[jj] = j;
     }
+    p.jobs[s] = j;
 }
 
 struct ResidParams {
@@ -972,12 +940,9 @@ struct ResidParams {
     const ColDesc* cols;
     const FactorDesc* gfac;
     int nbuild;              // columns of the tile (cp)
-    const DenseJob* djobs;
-    int n_dense;
     const EvalJob* jobs;
-    const short* job_col;
+    const int* job_col;
     const double* job_w;
-    int n_sparse;
     int n_slots;             // evals of the group = sum slots
     const int* tcols;        // distinct target columns
     int n_tcols;
@@ -998,7 +963,7 @@ __device__ __forceinline__ double warp_sum(double v) {
 // sums of 8 per-lane values over the warp, all at once: after the three exchange steps lane l holds value
 // ((l >> 4) & 1) * 4 + ((l >> 3) & 1) * 2 + ((l >> 2) & 1) summed over the 8 lanes that share its low two bits; two more
 // butterfly steps finish it.  Returns that value's warp total (the same in the 4 lanes of a group).
-__device__ __forceinline__ double warp_sum8(const double (&a)[DJ_T], int lane) {
+__device__ __forceinline__ double warp_sum8(const double (&a)[OCT], int lane) {
     double b[4], c[2];
     const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
 #pragma unroll
@@ -1060,7 +1025,8 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
     unsigned phase[2] = {0, 0};
     int it = 0;
     if (p.nstages == 2 && (long long)blockIdx.x < p.n_chunks) resid_stage_issue(p, blockIdx.x, tiles, &s_bar[0], tid, nthreads);
-    const int njobs_all = p.n_dense + p.n_sparse + p.n_tcols;
+    const int n_oct = (p.n_slots + OCT - 1) / OCT;
+    const int njobs_all = n_oct + p.n_tcols;
     for (long long ci = blockIdx.x; ci < p.n_chunks; ci += gridDim.x, ++it) {
         const int st = (p.nstages == 2) ? (it & 1) : 0;
         double* tile = tiles + (size_t)st * p.U * PT_B;
@@ -1094,99 +1060,86 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
             if (lane == 0) jj = atomicAdd(&s_next, 1);
             jj = __shfl_sync(0xffffffffu, jj, 0);
             if (jj >= njobs_all) break;
-            if (jj < p.n_dense) {
-                // ---------------- dense job: one equation, all its evals
-                const DenseJob* dj = p.djobs + jj;
-                const int4 cq = *(const int4*)dj->col;
-                const int T = dj->T, D = dj->D;
-                unsigned coff[DJ_T];
-                coff[0] = (cq.x & 0xffff) * (PP_B * 8); coff[1] = ((unsigned)cq.x >> 16) * (PP_B * 8);
-                coff[2] = (cq.y & 0xffff) * (PP_B * 8); coff[3] = ((unsigned)cq.y >> 16) * (PP_B * 8);
-                coff[4] = (cq.z & 0xffff) * (PP_B * 8); coff[5] = ((unsigned)cq.z >> 16) * (PP_B * 8);
-                coff[6] = (cq.w & 0xffff) * (PP_B * 8); coff[7] = ((unsigned)cq.w >> 16) * (PP_B * 8);
-                const uint2 mq = *(const uint2*)dj->mask;
-                double a1[DJ_T], a2[DJ_T];
+            if (jj < n_oct) {
+                // ---------------- octet job: evals [8 jj, 8 jj + 8) of the list (padding evals: nnz 0, sums discarded)
+                // descriptors are fetched up front, spread over the lanes (lane v: header of eval v; lane z: entry z of
+                // each eval), and broadcast by shuffles inside the loops: no global load on the critical path
+                const EvalJob mine = p.jobs[(size_t)jj * OCT + (lane & 7)];
+                const int* jc = p.job_col + (size_t)jj * OCT * TMAX;
+                const double* jw = p.job_w + (size_t)jj * OCT * TMAX;
+                const bool full = npts == PT_B;
+                double a1[OCT], a2[OCT];
+                int cur_t = -1, cur_c = -1;
+                double t[RES_NPL], c1[RES_NPL];
 #pragma unroll
-                for (int v = 0; v < DJ_T; ++v) { a1[v] = 0.0; a2[v] = 0.0; }
+                for (int v = 0; v < OCT; ++v) {
+                    // every shuffle sits at the top level of the unrolled loop (none inside a conditional)
+                    const int nz = __shfl_sync(0xffffffffu, mine.nnz, v);
+                    const int tco = __shfl_sync(0xffffffffu, mine.tcol, v);
+                    const double b1 = __shfl_sync(0xffffffffu, mine.b1, v);
+                    // entry z of the eval in lane z (one coalesced fetch), broadcast by shuffle when used
+                    const int e_col = (lane < nz) ? jc[v * TMAX + lane] : 0;
+                    const double e_w = (lane < nz) ? jw[v * TMAX + lane] : 0.0;
+                    const int co0 = __shfl_sync(0xffffffffu, e_col, 0), co1 = __shfl_sync(0xffffffffu, e_col, 1);
+                    const double w0 = __shfl_sync(0xffffffffu, e_w, 0), w1 = __shfl_sync(0xffffffffu, e_w, 1);
+                    if (tco != cur_t) {
+                        cur_t = tco;
+#pragma unroll
+                        for (int k = 0; k < RES_NPL; ++k) t[k] = lds_f64_e(cl + tco + k * 256, jj);
+                    }
+                    double r[RES_NPL];
+#pragma unroll
+                    for (int k = 0; k < RES_NPL; ++k) r[k] = t[k] - b1;
+                    if (nz > 0) {
+                        // first surviving column: kept in registers while consecutive evals use the same one
+                        if (co0 != cur_c) {
+                            cur_c = co0;
+#pragma unroll
+                            for (int k = 0; k < RES_NPL; ++k) c1[k] = lds_f64_e(cl + co0 + k * 256, jj);
+                        }
+#pragma unroll
+                        for (int k = 0; k < RES_NPL; ++k) r[k] = fma(-w0, c1[k], r[k]);
+                    }
+                    if (nz > 1) {
+#pragma unroll
+                        for (int k = 0; k < RES_NPL; ++k) r[k] = fma(-w1, lds_f64_e(cl + co1 + k * 256, jj), r[k]);
+                    }
+                    if (nz > 2) {
 #pragma unroll 1
-                for (int sub = 0; sub < PT_B / 128; ++sub) {
-                    const unsigned base = cl + sub * 1024;
-                    double c[DJ_T][4];
+                        for (int z = 2; z < nz; ++z) {
+                            const unsigned ca = cl + (unsigned)__shfl_sync(0xffffffffu, e_col, z);
+                            const double w = __shfl_sync(0xffffffffu, e_w, z);
 #pragma unroll
-                    for (int k = 0; k < DJ_T; ++k) {
-                        if (k < T) {
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) c[k][i] = lds_f64(base + coff[k] + i * 256);
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) c[k][i] = 0.0;
+                            for (int k = 0; k < RES_NPL; ++k) r[k] = fma(-w, lds_f64_e(ca + k * 256, jj), r[k]);
                         }
                     }
-                    bool ok[4];
+                    double s1 = 0.0, s2 = 0.0;
+                    if (L2) {
+                        const double dl = __shfl_sync(0xffffffffu, mine.delta, v);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) ok[i] = sub * 128 + lane + 32 * i < npts;
+                        for (int k = 0; k < RES_NPL; ++k) { const double r2 = r[k] + dl; r[k] = (full || lane + 32 * k < npts) ? r[k] : 0.0; s2 = (full || lane + 32 * k < npts) ? fma(r2, r2, s2) : s2; }
 #pragma unroll
-                    for (int v = 0; v < DJ_T; ++v) {
-                        if (v < D) {
-                            const unsigned m = ((v < 4 ? mq.x : mq.y) >> (8 * (v & 3))) & 0xffu;
-                            const double2* wr = (const double2*)dj->w[v];
-                            const double2 w01 = __ldg(wr), w23 = __ldg(wr + 1), w45 = __ldg(wr + 2), w67 = __ldg(wr + 3);
-                            const double wk[DJ_T] = {w01.x, w01.y, w23.x, w23.y, w45.x, w45.y, w67.x, w67.y};
-                            const double b1 = __ldg(&dj->b1[v]);
-                            double r[4];
+                        for (int k = 0; k < RES_NPL; ++k) s1 += fabs(r[k]);
+                    } else if (full) {
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) r[i] = -b1;
+                        for (int k = 0; k < RES_NPL; ++k) s1 += fabs(r[k]);
+                    } else {
 #pragma unroll
-                            for (int k = 0; k < DJ_T; ++k) {
-                                if ((m >> k) & 1u) {
-#pragma unroll
-                                    for (int i = 0; i < 4; ++i) r[i] = fma(wk[k], c[k][i], r[i]);
-                                }
-                            }
-                            if (L2) {
-                                const double dl = __ldg(&dj->delta[v]);
-#pragma unroll
-                                for (int i = 0; i < 4; ++i) if (ok[i]) { const double r2 = r[i] + dl; a2[v] = fma(r2, r2, a2[v]); }
-                            }
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) if (ok[i]) a1[v] += fabs(r[i]);
-                        }
+                        for (int k = 0; k < RES_NPL; ++k) if (lane + 32 * k < npts) s1 += fabs(r[k]);
                     }
+                    a1[v] = s1; a2[v] = s2;
                 }
                 const int vi = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+                const int slot = jj * OCT + vi;
                 const double t1 = warp_sum8(a1, lane);
-                if ((lane & 3) == 0 && vi < D) s_sum[dj->slot0 + vi] += t1;
+                if ((lane & 3) == 0 && slot < p.n_slots) s_sum[slot] += t1;
                 if (L2) {
                     const double t2 = warp_sum8(a2, lane);
-                    if ((lane & 3) == 0 && vi < D) s_sum[p.n_slots + dj->slot0 + vi] += t2;
+                    if ((lane & 3) == 0 && slot < p.n_slots) s_sum[p.n_slots + slot] += t2;
                 }
-            } else if (jj < p.n_dense + p.n_sparse) {
-                // ---------------- sparse job: one eval of an equation with more than DJ_T terms
-                const int js = jj - p.n_dense;
-                const EvalJob job = p.jobs[js];
-                double r[RES_NPL];
-#pragma unroll
-                for (int k = 0; k < RES_NPL; ++k) r[k] = lds_f64(cl + job.tcol * (PP_B * 8) + k * 256) - job.b1;
-                for (int z = 0; z < job.nnz; ++z) {
-                    const int c = p.job_col[(long long)js * TMAX + z];
-                    const double w = p.job_w[(long long)js * TMAX + z];
-#pragma unroll
-                    for (int k = 0; k < RES_NPL; ++k) r[k] = fma(-w, lds_f64(cl + c * (PP_B * 8) + k * 256), r[k]);
-                }
-                double a1 = 0.0, a2 = 0.0;
-#pragma unroll
-                for (int k = 0; k < RES_NPL; ++k) {
-                    if (lane + 32 * k < npts) {
-                        a1 += fabs(r[k]);
-                        if (L2) { const double r2 = r[k] + job.delta; a2 = fma(r2, r2, a2); }
-                    }
-                }
-                a1 = warp_sum(a1);
-                if (L2) a2 = warp_sum(a2);
-                if (lane == 0) { s_sum[job.slot] += a1; if (L2) s_sum[p.n_slots + job.slot] += a2; }
             } else {
                 // ---------------- target job: sum|t| of one target column (padding points hold 0)
-                const int tc = jj - p.n_dense - p.n_sparse;
+                const int tc = jj - n_oct;
                 const int c = p.tcols[tc];
                 double a = 0.0;
 #pragma unroll
@@ -1521,13 +1474,12 @@ struct LaunchGroup {             // equations evaluated together over ONE dictio
     std::vector<int> col_term;   // column -> global distinct-term id (the ones column is appended after these)
     int ncols = 0, cp = 0, n_ent = 0;
     int ntasks = 0, ksplit = 1;
-    int n_slots = 0, n_dense = 0, n_sparse = 0, n_tcols = 0;   // pass-B jobs: evals, dense-equation jobs, sparse evals, target columns
+    int n_slots = 0, n_tcols = 0;   // pass-B jobs: evals (sum slots), distinct target columns
     int n_gfac = 0;
     long long seg_off = 0, win_off = 0, pe_off = 0;     // doubles / doubles / ints into the batch-wide tables
     // device pointers into ctx->d_enc
     ColDesc* d_cols = nullptr; FactorDesc* d_gfac = nullptr; TaskDesc* d_tasks = nullptr;
     int* d_flush = nullptr; int* d_slot_ev = nullptr; int* d_slot_tci = nullptr; int* d_tcols = nullptr;
-    int* d_dj_eq = nullptr; int* d_dj_slot0 = nullptr;
 };
 
 struct epde_batch {
@@ -2014,7 +1966,7 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
     auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
     std::vector<char> img;
     auto put = [&](const void* src, size_t bytes) { const size_t o = align(img.size()); img.resize(o + std::max<size_t>(bytes, 1)); if (bytes) memcpy(img.data() + o, src, bytes); return o; };
-    struct GOff { size_t cols, gfac, tasks, flush, slot_ev, slot_tci, tcols, dj_eq, dj_slot0; };
+    struct GOff { size_t cols, gfac, tasks, flush, slot_ev, slot_tci, tcols; };
     std::vector<GOff> goff(b->groups.size());
     std::vector<int> pairent_all;
     long long seg_off = 0, win_off = 0;
@@ -2108,30 +2060,19 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
                         if (ci <= cj) flush[((size_t)(t * TASK_PAIRS + m) * 32 + l) * 2 + h] = pairent[(size_t)ci * g.cp + cj];
                     }
             }
-        // pass-B jobs.  Sum slots: the evals of every equation of <= DJ_T terms (one dense job per equation, heaviest
-        // first), then the evals of longer equations (one sparse job each); distinct target columns for sum|t|
-        std::vector<int> dense_eqs, sparse_eqs;
-        for (int e : g.eqs) {
-            if (eq_evals[e].empty()) continue;
-            ((term_off[e + 1] - term_off[e]) <= DJ_T ? dense_eqs : sparse_eqs).push_back(e);
+        // pass-B jobs.  Sum slots = the evals of the group sorted by target column (consecutive evals then share the
+        // target registers); distinct target columns for sum|t|
+        std::vector<std::pair<int, int>> byt;      // (target column, eval)
+        for (int e : g.eqs)
+            for (int v : eq_evals[e]) byt.push_back({(int)b->eqs[e].col[eval_target[v]], v});
+        std::stable_sort(byt.begin(), byt.end());
+        std::vector<int> slot_ev, slot_tci, tcols;
+        for (auto& q : byt) {
+            if (tcols.empty() || tcols.back() != q.first) tcols.push_back(q.first);
+            slot_ev.push_back(q.second);
+            slot_tci.push_back((int)tcols.size() - 1);
         }
-        std::stable_sort(dense_eqs.begin(), dense_eqs.end(), [&](int a, int bb) {
-            return (term_off[a + 1] - term_off[a]) * eq_evals[a].size() > (term_off[bb + 1] - term_off[bb]) * eq_evals[bb].size(); });
-        std::vector<int> slot_ev, dj_eq, dj_slot0;
-        for (int e : dense_eqs) {
-            dj_eq.push_back(e); dj_slot0.push_back((int)slot_ev.size());
-            for (int v : eq_evals[e]) slot_ev.push_back(v);
-        }
-        g.n_dense = (int)dense_eqs.size();
-        for (int e : sparse_eqs)
-            for (int v : eq_evals[e]) slot_ev.push_back(v);
         g.n_slots = (int)slot_ev.size();
-        g.n_sparse = g.n_slots - (dj_slot0.empty() ? 0 : (int)(dj_slot0.back() + eq_evals[dense_eqs.back()].size()));
-        std::set<int> tset;
-        for (int v : slot_ev) tset.insert((int)b->eqs[eval_eq[v]].col[eval_target[v]]);
-        std::vector<int> tcols(tset.begin(), tset.end()), slot_tci;
-        for (int v : slot_ev)
-            slot_tci.push_back((int)(std::lower_bound(tcols.begin(), tcols.end(), (int)b->eqs[eval_eq[v]].col[eval_target[v]]) - tcols.begin()));
         g.n_tcols = (int)tcols.size();
         // tables
         g.seg_off = seg_off; seg_off += (long long)c->geom.n_rows * n_ent + (b->weighted ? n_ent : 0);
@@ -2148,8 +2089,6 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
         goff[gi].flush = put(flush.data(), flush.size() * sizeof(int));
         goff[gi].slot_ev = put(slot_ev.data(), slot_ev.size() * sizeof(int));
         goff[gi].slot_tci = put(slot_tci.data(), slot_tci.size() * sizeof(int));
-        goff[gi].dj_eq = put(dj_eq.data(), dj_eq.size() * sizeof(int));
-        goff[gi].dj_slot0 = put(dj_slot0.data(), dj_slot0.size() * sizeof(int));
         goff[gi].tcols = put(tcols.data(), tcols.size() * sizeof(int));
     }
     b->seg_doubles = seg_off;
@@ -2181,7 +2120,6 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
         g.d_cols = (ColDesc*)(d + goff[gi].cols); g.d_gfac = (FactorDesc*)(d + goff[gi].gfac);
         g.d_tasks = (TaskDesc*)(d + goff[gi].tasks); g.d_flush = (int*)(d + goff[gi].flush);
         g.d_slot_ev = (int*)(d + goff[gi].slot_ev); g.d_slot_tci = (int*)(d + goff[gi].slot_tci); g.d_tcols = (int*)(d + goff[gi].tcols);
-        g.d_dj_eq = (int*)(d + goff[gi].dj_eq); g.d_dj_slot0 = (int*)(d + goff[gi].dj_slot0);
     }
     // outputs
     const size_t ne = (size_t)std::max(1, n_eval);
@@ -2418,25 +2356,23 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
     auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
     for (auto& g : b->groups) {
         if (g.n_slots == 0) continue;
-        const size_t o_ej = align(sizeof(DenseJob) * (size_t)g.n_dense), o_col = align(o_ej + sizeof(EvalJob) * (size_t)g.n_sparse),
-                     o_w = align(o_col + sizeof(short) * (size_t)g.n_sparse * TMAX), tot = align(o_w + sizeof(double) * (size_t)g.n_sparse * TMAX);
+        const size_t n_pad = ((size_t)g.n_slots + OCT - 1) / OCT * OCT;
+        const size_t o_col = align(sizeof(EvalJob) * n_pad), o_w = align(o_col + sizeof(int) * n_pad * TMAX),
+                     tot = align(o_w + sizeof(double) * n_pad * TMAX);
         if (c->d_jobs.ensure(tot)) return 1;
         char* jb = (char*)c->d_jobs.ptr;
         ResidProgParams pp;
-        pp.eqs = b->d_eqs; pp.eval_eq = b->d_eval_eq; pp.eval_tgt = b->d_eval_tgt;
-        pp.dj_eq = g.d_dj_eq; pp.dj_slot0 = g.d_dj_slot0; pp.slot_ev = g.d_slot_ev;
+        pp.eqs = b->d_eqs; pp.eval_eq = b->d_eval_eq; pp.eval_tgt = b->d_eval_tgt; pp.slot_ev = g.d_slot_ev;
         pp.wterm = b->d_wterm; pp.intercept = b->d_intercept; pp.intercept_l1 = b->d_b1;
-        pp.djobs = (DenseJob*)jb; pp.jobs = (EvalJob*)(jb + o_ej); pp.job_col = (short*)(jb + o_col); pp.job_w = (double*)(jb + o_w);
-        pp.n_dense = g.n_dense; pp.n_sparse = g.n_sparse; pp.n_slots = g.n_slots;
-        { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_prog_kernel<<<(g.n_dense + g.n_sparse + 63) / 64, 64, 0, c->stream>>>(pp); }
+        pp.jobs = (EvalJob*)jb; pp.job_col = (int*)(jb + o_col); pp.job_w = (double*)(jb + o_w); pp.n_slots = g.n_slots;
+        { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_prog_kernel<<<(unsigned)((n_pad + 63) / 64), 64, 0, c->stream>>>(pp); }
         CK(cudaGetLastError());
         ResidParams p;
         memset(&p, 0, sizeof p);
         p.N = c->N; p.U = (int)g.token_ids.size();
         for (int u = 0; u < p.U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
         p.cols = g.d_cols; p.gfac = g.d_gfac; p.nbuild = g.cp;
-        p.djobs = pp.djobs; p.n_dense = g.n_dense;
-        p.jobs = pp.jobs; p.job_col = pp.job_col; p.job_w = pp.job_w; p.n_sparse = g.n_sparse;
+        p.jobs = pp.jobs; p.job_col = pp.job_col; p.job_w = pp.job_w;
         p.n_slots = g.n_slots; p.tcols = g.d_tcols; p.n_tcols = g.n_tcols;
         p.n_chunks = (int)n_chunks; p.aligned = 1;
         const int nsum = 2 * g.n_slots + g.n_tcols;
