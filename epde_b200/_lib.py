@@ -37,6 +37,7 @@ SIGNATURES = {
     'epde_batch_destroy': (C.c_int, [vp]),
     'epde_batch_set_given': (C.c_int, [vp, c_i32p, c_f64p, c_f64p]),
     'epde_batch_set_norms': (C.c_int, [vp, C.c_int]),
+    'epde_batch_info': (C.c_int, [vp, c_i64p]),
     'epde_batch_gram_size': (C.c_int, [vp, c_i64p]),
     'epde_batch_residual_size': (C.c_int, [vp, c_i64p]),
     'epde_batch_gram': (C.c_int, [vp, vp]),

@@ -1473,7 +1473,7 @@ struct LaunchGroup {             // equations evaluated together over ONE dictio
     std::vector<int> token_ids;  // slot -> token id
     std::vector<int> col_term;   // column -> global distinct-term id (the ones column is appended after these)
     int ncols = 0, cp = 0, n_ent = 0;
-    int ntasks = 0, ksplit = 1;
+    int ntasks = 0, ksplit = 1, n_block_pairs = 0;
     int n_slots = 0, n_tcols = 0;   // pass-B jobs: evals (sum slots), distinct target columns
     int n_gfac = 0;
     long long seg_off = 0, win_off = 0, pe_off = 0;     // doubles / doubles / ints into the batch-wide tables
@@ -2047,6 +2047,8 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
         std::vector<TaskDesc> tasks;
         build_tasks(nblk, need, tasks);
         g.ntasks = (int)tasks.size();
+        g.n_block_pairs = 0;
+        for (auto& t : tasks) g.n_block_pairs += t.pad0;
         if (g.ntasks > GRAM_MAX_WARPS) { delete b; return fail("internal: %d pass-A tasks exceed %d warps", g.ntasks, GRAM_MAX_WARPS); }
         g.ksplit = (g.ntasks >= 8) ? 1 : std::max(1, std::min(4, GRAM_MAX_WARPS / g.ntasks));
         std::vector<int> flush((size_t)g.ntasks * TASK_PAIRS * 64, -1);
@@ -2173,6 +2175,16 @@ int epde_batch_set_given(epde_batch* b, const int32_t* mode, const double* wterm
 int epde_batch_set_norms(epde_batch* b, int want_l2) {
     if (!b || !b->ctx) return fail("epde_batch_set_norms: null batch");
     b->want_l2 = want_l2 != 0;
+    return 0;
+}
+
+int epde_batch_info(epde_batch* b, int64_t* info) {
+    if (!b || !info) return fail("null argument");
+    int64_t cols = 0, ent = 0, bp = 0, tasks = 0;
+    for (auto& g : b->groups) {
+        cols += g.ncols; ent += g.n_ent; bp += g.n_block_pairs; tasks += g.ntasks;
+    }
+    info[0] = (int64_t)b->groups.size(); info[1] = cols; info[2] = ent; info[3] = bp; info[4] = tasks; info[5] = b->weighted ? 1 : 0;
     return 0;
 }
 

@@ -215,6 +215,14 @@ class Engine:
         _lib.check(self._lib.epde_ctx_launch_count(self._h, C.byref(r)))
         return int(r.value)
 
+    @staticmethod
+    def fp64_peak(device=0, seconds=1.0):
+        """(DFMA TFLOP/s, DMMA TFLOP/s) sustained on `device` (include/epde_b200.h epde_measure_fp64_peak)."""
+        a, b = C.c_double(0), C.c_double(0)
+        lib = _lib.load()
+        _lib.check(lib.epde_measure_fp64_peak(int(device), float(seconds), C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     # ---- measurement aid (include/epde_b200.h epde_ctx_set_timing)
     KERNEL_CLASSES = ('gram', 'marginal', 'solve', 'residual')
 
@@ -286,6 +294,13 @@ class Batch:
     def set_norms(self, want_l2=True):
         """which residual norms pass B accumulates (include/epde_b200.h epde_batch_set_norms)."""
         _lib.check(self._lib.epde_batch_set_norms(self._h, int(bool(want_l2))))
+
+    def info(self):
+        """{groups, columns, entries, block_pairs, tasks, weighted} of the batch (epde_batch_info)."""
+        a = (C.c_int64 * 8)()
+        _lib.check(self._lib.epde_batch_info(self._h, a))
+        return dict(groups=int(a[0]), columns=int(a[1]), entries=int(a[2]), block_pairs=int(a[3]), tasks=int(a[4]),
+                    weighted=bool(a[5]))
 
     @property
     def gram_size(self):

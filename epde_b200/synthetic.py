@@ -96,14 +96,7 @@ def make_tokens(shape, kind, xp=np, device=None, noise=1e-3, seed=0, axis0_range
         tk = make().reshape(-1)
         if noise:
             scale = noise * float(coarse[i].std())
-            if xp is np:
-                nz = np.empty(tk.shape[0])
-                for r in range(lo0, hi0):
-                    nz[(r - lo0) * row:(r - lo0 + 1) * row] = \
-                        np.random.default_rng([seed, i, r]).standard_normal(row)
-                tk = tk + scale * nz
-            else:
-                tk = tk + scale * _counter_normal(xp, lo0 * row, tk.shape[0], seed, i, device)
+            tk = tk + scale * _counter_normal(xp, lo0 * row, tk.shape[0], seed, i, device)
         out.append(tk.contiguous() if xp is not np else np.ascontiguousarray(tk))
     return out
 
@@ -117,21 +110,87 @@ def _s64(c):
 def _counter_normal(xp, start, n, seed, token, device):
     """standard normal noise as a pure function of (seed, token, GLOBAL point index): splitmix64 finaliser on the
     index, two 53-bit uniforms, Box-Muller.  Unlike a device generator the values do not depend on the launch
-    geometry torch picks on a given device, and a shard of the grid sees exactly the values of the whole grid."""
+    geometry torch picks on a given device, a shard of the grid sees exactly the values of the whole grid, and the
+    numpy path (CPU baseline / reference arm) draws the SAME stream as the torch path (GPU arm): both wrap 64-bit
+    integer arithmetic the same way."""
     key = _s64(seed * 0x632BE59BD9B4E019 + token * 0xD1342543DE82EF95 + 0x2545F4914F6CDD1D)
+    if xp is np:
+        out = np.empty(n)
+        step = 1 << 22                       # bounded temporaries on the host
+        with np.errstate(over='ignore'):
+            for lo in range(0, n, step):
+                m = min(step, n - lo)
+                idx = np.arange(start + lo, start + lo + m, dtype=np.int64)
+                out[lo:lo + m] = _box_muller(np, idx, np.int64(key), lambda a: a.astype(np.float64))
+        return out
     idx = xp.arange(start, start + n, dtype=xp.int64, device=device)
+    return _box_muller(xp, idx, key, lambda a: a.to(xp.float64))
+
+
+def _box_muller(xp, idx, key, to_f64):
+    c1, c2, c3 = (np.int64(_s64(c)) if xp is np else _s64(c)
+                  for c in (0x9E3779B97F4A7C15, 0xBF58476D1CE4E5B9, 0x94D049BB133111EB))
 
     def mix(z):
-        z = z * _s64(0x9E3779B97F4A7C15) + key
-        z = (z ^ ((z >> 30) & ((1 << 34) - 1))) * _s64(0xBF58476D1CE4E5B9)
-        z = (z ^ ((z >> 27) & ((1 << 37) - 1))) * _s64(0x94D049BB133111EB)
+        z = z * c1 + key
+        z = (z ^ ((z >> 30) & ((1 << 34) - 1))) * c2
+        z = (z ^ ((z >> 27) & ((1 << 37) - 1))) * c3
         return z ^ ((z >> 31) & ((1 << 33) - 1))
 
     m53 = (1 << 53) - 1
-    u1 = (((mix(idx * 2) >> 11) & m53).to(xp.float64) + 0.5) * 2.0 ** -53
-    u2 = ((mix(idx * 2 + 1) >> 11) & m53).to(xp.float64) * 2.0 ** -53
-    del idx
+    u1 = (to_f64((mix(idx * 2) >> 11) & m53) + 0.5) * 2.0 ** -53
+    u2 = to_f64((mix(idx * 2 + 1) >> 11) & m53) * 2.0 ** -53
     return xp.sqrt(-2.0 * xp.log(u1)) * xp.cos(2.0 * np.pi * u2)
+
+
+def data_checksum(token, xp=np):
+    """sampled sum of a token vector: the same number on every box / arm <=> the same data."""
+    return float(token[::4099].sum())
+
+
+def make_population_distinct(n_tokens, pop, seed=0, t_range=(3, 7), max_power=3):
+    """stress population with NO sharing: every term of every equation is distinct (products of 1-3 factors with
+    powers <= max_power), so the column dictionary de-duplicates nothing (report it beside the default)."""
+    rng = np.random.default_rng(seed)
+    seen, eqs = set(), []
+    while len(eqs) < pop:
+        T = int(rng.integers(t_range[0], t_range[1] + 1))
+        terms = []
+        while len(terms) < T:
+            nf = int(rng.integers(1, 4))
+            chosen = rng.choice(n_tokens, size=nf, replace=False)
+            term = [(int(c), float(rng.integers(1, max_power + 1)), 0, 0.0) for c in chosen]
+            key = frozenset(term)
+            if key in seen:
+                continue
+            seen.add(key)
+            terms.append(term)
+        if admissible_targets(terms):
+            eqs.append(terms)
+        else:
+            for t in terms:
+                seen.discard(frozenset(t))
+    return eqs
+
+
+def make_population_wide(n_tokens, pop, T, seed=0, max_power=3):
+    """stress population of T-term equations (T = 16, 30): distinct terms inside an equation."""
+    rng = np.random.default_rng(seed)
+    eqs = []
+    while len(eqs) < pop:
+        terms, seen = [], set()
+        while len(terms) < T:
+            nf = int(rng.integers(1, 4))
+            chosen = rng.choice(n_tokens, size=min(nf, n_tokens), replace=False)
+            term = [(int(c), float(rng.integers(1, max_power + 1)), 0, 0.0) for c in chosen]
+            key = frozenset(term)
+            if key in seen:
+                continue
+            seen.add(key)
+            terms.append(term)
+        if admissible_targets(terms):
+            eqs.append(terms)
+    return eqs
 
 
 def make_population(n_tokens, pop, seed=0, t_fresh=(5, 8), t_pruned=(2, 4), pruned_fraction=0.45,

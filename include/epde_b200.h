@@ -154,6 +154,9 @@ int epde_batch_set_given(epde_batch* b, const int32_t* mode, const double* wterm
  * the MOEADD path needs (L2LRFitness is its fitness operator, moeadd/strategy.py:60); fitness_l2 then comes back
  * as NaN.  Call before epde_batch_residual. */
 int epde_batch_set_norms(epde_batch* b, int want_l2);
+/* Measurement aid: info[0..5] = launch groups, dictionary columns (ones columns included), pair entries,
+ * 8x8 column-block pairs pass A computes per 4-point step (= DMMA.8x8x4 per step), pass-A warp tasks, weighted. */
+int epde_batch_info(epde_batch* b, int64_t* info);
 int epde_batch_gram_size(epde_batch* b, int64_t* n_doubles);
 int epde_batch_residual_size(epde_batch* b, int64_t* n_doubles);
 int epde_batch_gram(epde_batch* b, double* dev_seg);
