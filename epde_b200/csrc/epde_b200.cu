@@ -62,7 +62,7 @@
 #define LASSO_MAX_ITER 20      // sparsity.py:21
 #define LASSO_TOL 1e-4         // sparsity.py:21
 
-#define MAXU 12                // distinct tokens per launch group
+#define MAXU 32                // distinct tokens per launch group (the shared-memory budget may bind first)
 #define NBLK_MAX 10            // 8-column blocks of the column dictionary of a launch group
 #define CMAX (NBLK_MAX * 8)    // columns per launch group, ones column included
 #define MAXSF 6                // token values multiplied by a "fast" column (integer powers expanded)

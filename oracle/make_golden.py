@@ -241,12 +241,62 @@ def micro_fixtures():
     np.savez_compressed(os.path.join(OUT, 'micro.npz'), **out)
 
 
+def micro2_fixtures():
+    """round 2 additions, same entry points as micro_fixtures(): (a) WIDE systems -- F = 11, 15, 29 features, i.e.
+    equations of T = 12, 16, 30 terms (north_star 'n_terms ~ 5-30'; SURVEY 8d stress runs); (b) NON-TRIVIAL sample
+    weights g (a user `function_form`, interface.py:511-550): the window regressions are weighted
+    (supplementary.py:455) while the LASSO sums stay unweighted (sparsity.py:54-55,73-76)."""
+    rl.load_reference()
+    from epde.supplementary import calculate_weights
+    from epde.operators.common.sparsity import PhysicsInformedLasso
+    rng = np.random.default_rng(11)
+    out = {}
+    cases = [((40, 44), 11, 'wide', False), ((36, 40), 15, 'wide', False), ((48, 52), 29, 'wide', False),
+             ((20, 18, 16), 15, 'wide', False),
+             ((61, 61), 4, 'weighted', True), ((40, 52), 5, 'weighted', True), ((20, 24, 18), 5, 'weighted', True),
+             ((36, 40), 11, 'weighted', True)]
+    for ci, (shape, F, kind, weighted) in enumerate(cases):
+        axes = [np.linspace(0, 1, n) for n in shape]
+        gr = np.meshgrid(*axes, indexing='ij')
+        nd = len(shape)
+        cols = [np.sin((k % 5 + 1) * np.pi * gr[k % nd] + 0.37 * k) * np.cos((k % 7 + 2) * gr[(k + 1) % nd] + 0.11 * k)
+                + 0.3 * rng.standard_normal(shape) for k in range(F)]
+        X = np.stack([c.reshape(-1) for c in cols], axis=1)
+        w = rng.standard_normal(F) * (rng.random(F) < 0.5)
+        y = X @ w + 0.5 + 0.05 * rng.standard_normal(X.shape[0])
+        if weighted:
+            # a smooth positive bump, like the inverse-polynomial test function the reference keeps commented out
+            bump = np.ones(shape)
+            for a in gr:
+                bump = bump * (1.0 - 0.9 * (2 * a - 1) ** 2)
+            g = (0.05 + bump).reshape(-1)
+        else:
+            g = np.ones(X.shape[0])
+        cw = calculate_weights(X, y, g, np.array(shape))
+        est = PhysicsInformedLasso(grid_shape=np.array(shape))
+        est.fit(X, y, g)
+        out[f'c{ci}_shape'] = np.array(shape)
+        out[f'c{ci}_X'] = X
+        out[f'c{ci}_y'] = y
+        out[f'c{ci}_g'] = g
+        out[f'c{ci}_cw'] = cw
+        out[f'c{ci}_coef'] = est.coef_
+        out[f'c{ci}_b'] = np.float64(est.intercept_)
+        out[f'c{ci}_cached'] = est.cached_weights_
+        out[f'c{ci}_kind'] = np.array(kind)
+        print(f'[micro2] case {ci} {shape} F={F} {kind}: selected {int((est.coef_ != 0).sum())} of {F}')
+    out['n_cases'] = np.int64(len(cases))
+    np.savez_compressed(os.path.join(OUT, 'micro2.npz'), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = rl.REFERENCE_ROOT
     which = sys.argv[1:] or ['micro', 'wave', 'burgers', 'heat']
     if 'micro' in which:
         micro_fixtures()
+    if 'micro2' in which:
+        micro2_fixtures()
     if 'wave' in which:
         wave_cases(ref)
     if 'burgers' in which:

@@ -126,6 +126,40 @@ def test_golden_micro(ci):
     assert_sw(full.sw_weights[0, :, :F + 1], z[f'c{ci}_cw'], 'calculate_weights', col_scales=sc)
 
 
+@pytest.mark.parametrize('ci', range(8))
+def test_golden_micro2_wide_and_weighted(ci):
+    """reference-generated fixtures of round 2: equations of T = 12, 16, 30 terms (one warp per window system, four
+    column blocks of the dictionary) and NON-TRIVIAL sample weights (weighted window Grams, unweighted LASSO sums:
+    supplementary.py:455 vs sparsity.py:54-55,73-76)."""
+    z = load_fixture('micro2')
+    X, y, g = z[f'c{ci}_X'], z[f'c{ci}_y'], z[f'c{ci}_g']
+    shape = tuple(int(s) for s in z[f'c{ci}_shape'])
+    kind = str(z[f'c{ci}_kind'])
+    F = X.shape[1]
+    toks = [X[:, j] for j in range(F)] + [y]
+    eq = [[(j, 1.0, 0, 0.0)] for j in range(F + 1)]
+    enc = epde_b200.encode([eq], [(0, F)])
+    with make_engine(shape, toks) as eng:
+        if kind == 'weighted':
+            eng.set_sample_weights(g)
+        res = eng.evaluate(enc)
+        with eng.batch(enc) as b:
+            b.set_given([1], np.zeros((1, epde_b200.MAX_TERMS)), [0.0])
+            b.gram(); b.solve(); b.residual()
+            full = b.fetch()
+    ref_coef, ref_b = z[f'c{ci}_coef'], float(z[f'c{ci}_b'])
+    assert np.array_equal(res.coef[0, :F] != 0, ref_coef != 0), f'{kind} F={F}: selected set differs'
+    sc = natural_scales(X, y)
+    assert_rel(res.coef[0, :F], ref_coef, 'coef', atol=1e-9 * sc[:F])
+    assert_rel(res.intercept[0], ref_b, 'intercept', atol=1e-9 * sc[-1])
+    assert_sw(res.cached_weights(0), z[f'c{ci}_cached'], 'cached weights', col_scales=sc[np.append(ref_coef != 0, True)])
+    assert_sw(full.sw_weights[0, :, :F + 1], z[f'c{ci}_cw'], 'calculate_weights', col_scales=sc)
+    # the L1 fitness is unweighted whatever g is (fitness.py:142)
+    pred = X @ ref_coef + ref_b
+    fit = np.abs(y - pred).sum() / np.abs(y).sum() if np.any(ref_coef != 0) else np.abs(y - y.mean()).sum() / np.abs(y).sum()
+    assert_rel(res.fitness_l1[0], fit, 'L1 fitness', rtol=1e-6)
+
+
 def oracle_refs(tokens, shape, eqs, evals):
     out = {}
     for e, eq in enumerate(eqs):
@@ -162,6 +196,39 @@ def test_synthetic_vs_oracle(cfg, pop, seed):
     with make_engine(shape, tokens) as eng:
         res = eng.evaluate(epde_b200.encode(eqs, evals))
     check_against_oracle(res, tokens, shape, eqs, evals, cfg, min_checked=len(evals) // 2)
+
+
+@pytest.mark.parametrize('kind,pop', [('distinct', 48), ('wide16', 6), ('wide30', 4)])
+def test_stress_populations_vs_oracle(kind, pop):
+    """populations that stress the column dictionary: 'distinct' = no term shared between equations (several launch
+    groups, the grouping must not change any result); 'wide16' / 'wide30' = 16 / 30-term equations (SURVEY 8d stress
+    runs; window systems of up to 31 unknowns, pass-B evals with many surviving terms)."""
+    shape = (24, 20, 22) if kind == 'distinct' else (40, 36)
+    knd = 'heat' if len(shape) == 3 else 'wave'
+    tokens = syn.make_tokens(shape, knd, seed=4, noise=5e-2)
+    if kind == 'distinct':
+        eqs = syn.make_population_distinct(len(tokens), pop, seed=2)
+    else:
+        eqs = syn.make_population_wide(len(tokens), pop, int(kind[4:]), seed=2, max_power=2)
+    evals = syn.make_evals(eqs)
+    with make_engine(shape, tokens) as eng:
+        enc = epde_b200.encode(eqs, evals)
+        with eng.batch(enc) as b:
+            info = b.info()
+            b.gram(); b.solve(); b.residual()
+            res = b.fetch()
+        # the same evals one equation at a time: grouping / batch composition must not matter beyond rounding
+        solo = [eng.evaluate(epde_b200.encode([eq], [(0, t) for (e, t) in evals if e == i])) for i, eq in enumerate(eqs[:6])]
+    if kind == 'distinct':
+        assert info['groups'] >= 2, info
+    v0 = 0
+    for i, r in enumerate(solo):
+        n = r.coef.shape[0]
+        F = len(eqs[i]) - 1
+        assert np.array_equal(res.coef[v0:v0 + n, :F] != 0, r.coef[:, :F] != 0)
+        assert_rel(res.fitness_l1[v0:v0 + n], r.fitness_l1, f'{kind} eq {i} fitness batch vs solo', rtol=1e-7)
+        v0 += n
+    check_against_oracle(res, tokens, shape, eqs, evals, kind, min_checked=max(1, len(evals) // 4))
 
 
 @pytest.mark.parametrize('shape', [(9, 8), (2, 2), (5, 300), (300, 5), (7, 6, 5), (33, 17, 29), (31, 260), (4, 3, 513)])

@@ -139,3 +139,33 @@ def test_right_part_selection(name):
         assert_rel(r.fitness, fx['rps_fit'][e], f'{name} eq {e} rps fitness')
         checked += 1
     assert checked >= 1
+
+
+# ------------------------------------------------------------------------------------------
+# round 2 fixtures (oracle/make_golden.py micro2_fixtures): wide systems (T = 12, 16, 30) and non-trivial
+# sample weights, generated by the unmodified reference
+# ------------------------------------------------------------------------------------------
+N_MICRO2 = 8
+
+
+@pytest.mark.parametrize('ci', range(N_MICRO2))
+def test_micro2_wide_and_weighted(ci):
+    z = load_fixture('micro2')
+    assert int(z['n_cases']) == N_MICRO2
+    X, y, g, shape = z[f'c{ci}_X'], z[f'c{ci}_y'], z[f'c{ci}_g'], z[f'c{ci}_shape']
+    kind = str(z[f'c{ci}_kind'])
+    F = X.shape[1]
+    plan = orc.WindowPlan(shape)
+    cols = np.column_stack([X, y])
+    weighted = kind == 'weighted'
+    seg_w = orc.segment_grams(cols, plan, g if weighted else None)
+    win = orc.window_grams(seg_w, plan)
+    total = orc.segment_grams(cols, plan, None)[0].sum(axis=0) if weighted else seg_w[0].sum(axis=0)
+    gram = orc.calc_weights_gram(win, list(range(F)) + [F + 1], F)
+    assert_rel(gram, z[f'c{ci}_cw'], f'{kind} calculate_weights (gram form)', rtol=1e-6, atol=1e-9)
+    coef, b, cached = orc.lasso_fit_gram(win, total, list(range(F)), F)
+    ref_coef = z[f'c{ci}_coef']
+    assert np.array_equal(coef != 0, ref_coef != 0), f'{kind} F={F}: selected set differs'
+    assert_rel(coef, ref_coef, 'coef', rtol=1e-6, atol=1e-11)
+    assert_rel(b, float(z[f'c{ci}_b']), 'intercept', rtol=1e-6, atol=1e-9)
+    assert_rel(cached, z[f'c{ci}_cached'], 'cached weights', rtol=1e-6, atol=1e-9)
