@@ -9,10 +9,11 @@ tensor cores), sliding-window solves + LASSO, and the residual norms (pass B).  
 pair.
 
 Workloads (BASELINE.json configs; --workload):
-    heat512   config 5: 512^3 (t,x,y), population 128.  N > 1: grid-point sharding along t, NCCL
-              all-reduce of the segment Grams and of the residual sums (strong scaling).  DEFAULT.
-    heat256   config 4: 256^3, population 256.  N > 1: population sharding, no collective.
-    wave1024  config 3: 1024^2, population 64.   N > 1: population sharding.
+    heat512   config 5: 512^3 (t,x,y), population 128.  DEFAULT.
+    heat256   config 4: 256^3, population 256.
+    wave1024  config 3: 1024^2, population 64.
+N > 1: grid-point sharding along t with NCCL all-reduces of the segment tables and of the residual sums (strong
+scaling) for every workload; --sharding population deals equations to ranks instead (no collective).
 The JSON line follows the driver contract; `value` is device-resident throughput, `e2e` goes
 through the public host API (host encodings in, host results out, copies inside the timed region).
 `--impl reference` times the CPU port of the reference's algorithm (oracle/, numpy, all host
@@ -48,6 +49,10 @@ def parse_args():
     ap.add_argument('--seed', type=int, default=5)
     ap.add_argument('--cpu-seconds', type=float, default=20.0, help='budget of the cpu_baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--sharding', default='grid', choices=['grid', 'population'],
+                    help="N > 1: 'grid' = grid-point sharding along t + two NCCL all-reduces (default for every workload: the "
+                         "cost of the column-dictionary passes follows the grid, not the population); 'population' = equations "
+                         "dealt to ranks, token cache replicated, no collective")
     ap.add_argument('--population', default='default', choices=['default', 'distinct', 'wide16', 'wide30'],
                     help="'default' = the seeded mix of SURVEY 8d; 'distinct' = no term shared between equations; "
                          "'wide16' / 'wide30' = stress populations of 16 / 30-term equations (pop 32 unless --pop)")
@@ -342,7 +347,7 @@ def run_reference(args):
 def workload_config(args, shape, eqs, evals, world):
     from epde_b200 import synthetic as syn
     T = [len(e) for e in eqs]
-    grid_sharded = args.workload == 'heat512' and world > 1
+    grid_sharded = getattr(args, 'sharding', 'grid') == 'grid' and world > 1
     return {'workload': args.workload, 'grid': 'x'.join(map(str, shape)), 'population': len(eqs),
             'evals_per_step': len(evals), 'terms_per_equation': f'{min(T)}..{max(T)} (mean {np.mean(T):.2f})',
             'distinct_tokens_mean': float(np.mean([syn.distinct_tokens(e) for e in eqs])),
@@ -376,7 +381,7 @@ def run_b200(args):
         dist.init_process_group('nccl', device_id=dev)
 
     shape, kind, eqs, evals = build_workload(args.workload, args.pop, args.seed, args.population)
-    grid_sharded = args.workload == 'heat512' and world > 1
+    grid_sharded = args.sharding == 'grid' and world > 1
     from epde_b200 import sharding
     if grid_sharded:
         (lo, hi), local_shape, shard = sharding.grid_slab(shape, rank, world)

@@ -211,6 +211,8 @@ def encode_factor(factor, bound: Binding):
     .params_description)."""
     power = float(_param(factor, 'power', 1.0))
     fam = bound.families.get(factor.label)
+    if fam is None and getattr(factor, 'ftype', None) == 'grids':
+        fam = _engine.KIND_POWER         # GridTokens (prepared_tokens.py:312-356): coordinate of axis `dim` ** power
     if fam is None:
         return (bound.token_id(factor.label), power, _engine.KIND_POWER, 0.0)
     dim = int(_param(factor, 'dim'))

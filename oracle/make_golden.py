@@ -76,10 +76,11 @@ def term_key(term):
 
 
 def run_case(name, coords, data, boundary, max_deriv_order, n_random, seed, extra_eqs=(),
-             derivs=None):
+             derivs=None, preproc='FD', preproc_kwargs=None, extra_arrays=None):
     rl.load_reference()
     import epde.globals as gv
-    search = rl.make_search(coords, data, boundary, max_deriv_order, derivs=derivs)
+    search = rl.make_search(coords, data, boundary, max_deriv_order, derivs=derivs, preproc=preproc,
+                            preproc_kwargs=preproc_kwargs)
     l2lr, l2, rps = rl.make_operators()
     tokens = rl.cache_tokens()
     labels = [k[0] for k in tokens.keys()]
@@ -195,7 +196,7 @@ def run_case(name, coords, data, boundary, max_deriv_order, n_random, seed, extr
         ev_nact=np.array(ev_nact, dtype=np.int32),
         rps_ok=np.array(rps_ok), rps_target=np.array(rps_target, dtype=np.int32),
         rps_keep=np.array(rps_keep), rps_fit=np.array(rps_fit), rps_stab=np.array(rps_stab),
-        rps_wfinal=np.array(rps_wfinal))
+        rps_wfinal=np.array(rps_wfinal), **(extra_arrays or {}))
 
 
 def micro_fixtures():
@@ -289,6 +290,89 @@ def micro2_fixtures():
     np.savez_compressed(os.path.join(OUT, 'micro2.npz'), **out)
 
 
+def procedural_case(ref):
+    """(round 2) procedural token families evaluated by CustomEvaluator in the reference (evaluators.py:47-89 with
+    trig_eval_fun_np :141 and grid_eval_fun_np :150): sin / cos of a coordinate and powers of a coordinate, mixed with
+    the data tokens of the wave case.  Stores the per-target LASSOSparsity + L2LRFitness(out of place) results of the
+    unmodified reference for hand-written equations; the engine evaluates the same factors in-kernel (kinds 1, 2 and
+    0 on the coordinate token)."""
+    rl.load_reference()
+    import epde.globals as gv
+    from epde.interface.prepared_tokens import TrigonometricTokens, GridTokens
+    d = np.loadtxt(os.path.join(ref, 'examples/data/wave_sln_80.csv'), delimiter=',').T
+    t = np.linspace(0, 1, d.shape[0]); x = np.linspace(0, 1, d.shape[1])
+    coords = np.meshgrid(t, x, indexing='ij')
+    trig = TrigonometricTokens(freq=(0.5, 6.5), dimensionality=1)
+    grid = GridTokens(['t', 'x'], max_power=2, dimensionality=1)
+    search = rl.make_search(coords, d, 8, (2, 2), additional_tokens=[trig, grid])
+    l2lr, _, _ = rl.make_operators()
+    tokens = rl.cache_tokens()
+    labels = [k[0] for k in tokens.keys()]
+    mask = gv.grid_cache.g_func != 0
+    grids = [np.asarray(gv.grid_cache.get(str(dim)))[mask].reshape(-1) for dim in range(2)]
+    tok_arrays = [np.asarray(v, dtype=np.float64).reshape(-1) for v in tokens.values()] + grids
+    tok_id = {l: i for i, l in enumerate(labels)}
+    gid = {0: len(labels), 1: len(labels) + 1}
+    KIND = {'sin': 1, 'cos': 2}
+    # factor = (label, power) for data tokens, (label, power, freq, dim) for trig, (label, power, dim) for grids
+    eqs = [
+        [[('sin', 1, 3.0, 1), ('du/dx1', 1)], [('d^2u/dx1^2', 1)], [('u', 1)], [('d^2u/dx0^2', 1)]],
+        [[('cos', 1, 2.0, 0)], [('u', 1), ('sin', 1, 1.5, 1)], [('d^2u/dx1^2', 1)], [('du/dx0', 1)]],
+        [[('x', 1, 1), ('du/dx1', 1)], [('t', 2, 0)], [('d^2u/dx1^2', 1)], [('u', 2)], [('d^2u/dx0^2', 1)]],
+        [[('cos', 1, 6.0, 1), ('u', 1)], [('x', 2, 1)], [('du/dx1', 1)], [('d^2u/dx1^2', 1)], [('du/dx0', 1)]],
+        [[('sin', 1, 0.7, 0), ('cos', 1, 4.2, 1)], [('u', 1)], [('d^2u/dx1^2', 1)], [('d^2u/dx0^2', 1)]],
+    ]
+
+    def ftext(f):
+        if f[0] in KIND:
+            return '%s{power: %d, freq: %r, dim: %d}' % (f[0], f[1], float(f[2]), f[3])
+        if f[0] in ('t', 'x'):
+            return '%s{power: %d, dim: %d}' % (f[0], f[1], f[2])
+        return '%s{power: %d}' % (f[0], f[1])
+
+    def text(terms, target):
+        ts = [' * '.join(ftext(f) for f in term) for term in terms]
+        feats = [q for i, q in enumerate(ts) if i != target]
+        return ' + '.join('1.0 * ' + q for q in feats) + ' + 0. = ' + ts[target]
+
+    term_off, fac_off, fac_tok, fac_pow, fac_kind, fac_par = [0], [0], [], [], [], []
+    ev_eq, ev_tgt, ev_coef, ev_b, ev_fit, ev_sw, ev_nact = [], [], [], [], [], [], []
+    for qi, terms in enumerate(eqs):
+        for term in terms:
+            for f in term:
+                if f[0] in KIND:
+                    fac_tok.append(gid[f[3]]); fac_pow.append(float(f[1])); fac_kind.append(KIND[f[0]]); fac_par.append(float(f[2]))
+                elif f[0] in ('t', 'x'):
+                    fac_tok.append(gid[f[2]]); fac_pow.append(float(f[1])); fac_kind.append(0); fac_par.append(0.0)
+                else:
+                    fac_tok.append(tok_id[f[0]]); fac_pow.append(float(f[1])); fac_kind.append(0); fac_par.append(0.0)
+            fac_off.append(len(fac_tok))
+        term_off.append(len(fac_off) - 1)
+        T = len(terms)
+        for tgt in range(T):
+            if not any(f[0].startswith('d') for f in terms[tgt]):
+                continue
+            _, eq = rl.translate(text(terms, tgt), search)
+            eq.reset_state(True)
+            eq.target_idx = T - 1
+            fit = l2lr.apply(eq, {}, force_out_of_place=True)
+            wi = np.asarray(eq.weights_internal, dtype=np.float64)
+            sw = np.asarray(eq._cached_sw_weights, dtype=np.float64)
+            coef = np.full(KMAX, np.nan); coef[:T - 1] = wi
+            swp = np.full((sw.shape[0], KMAX), np.nan); swp[:, :sw.shape[1]] = sw
+            ev_eq.append(qi); ev_tgt.append(tgt); ev_coef.append(coef); ev_b.append(float(sw.mean(axis=0)[-1]))
+            ev_fit.append(np.nan if fit is None else float(fit)); ev_sw.append(swp); ev_nact.append(sw.shape[1] - 1)
+            print(f'[procedural] eq {qi} target {tgt}: fit={fit} weights={wi}')
+    np.savez_compressed(
+        os.path.join(OUT, 'procedural.npz'), shape=np.array(gv.grid_cache.inner_shape, dtype=np.int64),
+        labels=np.array(labels + ['grid0', 'grid1']), tokens=np.stack(tok_arrays),
+        term_off=np.array(term_off, dtype=np.int32), fac_off=np.array(fac_off, dtype=np.int32),
+        fac_tok=np.array(fac_tok, dtype=np.int32), fac_pow=np.array(fac_pow), fac_kind=np.array(fac_kind, dtype=np.int32),
+        fac_par=np.array(fac_par), ev_eq=np.array(ev_eq, dtype=np.int32), ev_tgt=np.array(ev_tgt, dtype=np.int32),
+        ev_coef=np.array(ev_coef), ev_b=np.array(ev_b), ev_fit=np.array(ev_fit), ev_sw=np.array(ev_sw),
+        ev_nact=np.array(ev_nact, dtype=np.int32))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = rl.REFERENCE_ROOT
@@ -297,10 +381,14 @@ def main():
         micro_fixtures()
     if 'micro2' in which:
         micro2_fixtures()
+    if 'procedural' in which:
+        procedural_case(ref)
     if 'wave' in which:
         wave_cases(ref)
     if 'burgers' in which:
         burgers_case(ref)
+    if 'burgers_poly' in which:
+        burgers_poly_case(ref)
     if 'heat' in which:
         heat_case()
 
@@ -326,6 +414,26 @@ def burgers_case(ref):
     coords = np.meshgrid(tb, xb, indexing='ij')
     burgers_eqs = [[[('u', 1), ('du/dx1', 1)], [('d^2u/dx1^2', 1)], [('du/dx0', 1)]]]
     run_case('burgers_b50', coords, u, 50, (1, 2), n_random=8, seed=3, extra_eqs=burgers_eqs)
+
+
+def burgers_poly_case(ref):
+    # (2b, round 2) BASELINE.json config 2 as written: Burgers 256x256, boundary 50, NOISY data (noise_data of
+    # projects/pic/data/burgers/burgers.py:38-40, 1 %) differentiated by the reference's 'poly' preprocessor
+    # (PolynomialDeriv: per-point Chebyshev fits over 9-point windows, deriv_calculators.py:111-134, cheb.py:14-85).
+    # The full-grid noisy field and the coordinate vectors are stored too: the device Chebyshev producer is checked
+    # against the derivative tokens of this fixture.
+    import scipy.io as sio
+    m = sio.loadmat(os.path.join(ref, 'projects/burgers/burgers.mat'))
+    u = np.ascontiguousarray(m['u'].T if m['u'].shape[0] != m['t'].size else m['u'])
+    tb = m['t'].reshape(-1); xb = m['x'].reshape(-1)
+    np.random.seed(12)
+    noisy = 1.0 * 0.01 * np.std(u) * np.random.normal(size=u.shape) + u
+    coords = np.meshgrid(tb, xb, indexing='ij')
+    burgers_eqs = [[[('u', 1), ('du/dx1', 1)], [('d^2u/dx1^2', 1)], [('du/dx0', 1)]]]
+    run_case('burgers_poly_b50', coords, noisy, 50, (1, 2), n_random=8, seed=6, extra_eqs=burgers_eqs, preproc='poly',
+             preproc_kwargs={'use_smoothing': False, 'mp_poolsize': 4, 'polynomial_window': 9, 'poly_order': None},
+             extra_arrays={'data_full': noisy, 'axis0': tb, 'axis1': xb, 'boundary': np.int64(50),
+                           'polynomial_window': np.int64(9)})
 
 
 def heat_case():

@@ -44,14 +44,15 @@ def load_reference():
 
 
 def make_search(coordinate_tensors, data, boundary, max_deriv_order, derivs=None,
-                additional_tokens=None):
-    """EpdeSearch + pool from arrays; FD derivatives unless ``derivs`` is given."""
+                additional_tokens=None, preproc='FD', preproc_kwargs=None):
+    """EpdeSearch + pool from arrays; FD derivatives (or the ``preproc`` preprocessor, e.g. 'poly' = per-point
+    Chebyshev fits, preprocessing/deriv_calculators.py:111-134) unless ``derivs`` is given."""
     load_reference()
     from epde.interface.interface import EpdeSearch
     s = EpdeSearch(use_solver=False, use_pic=True, boundary=boundary,
                    coordinate_tensors=tuple(coordinate_tensors), device='cpu',
                    verbose_params={'show_iter_idx': False})
-    s.set_preprocessor(default_preprocessor_type='FD', preprocessor_kwargs={})
+    s.set_preprocessor(default_preprocessor_type=preproc, preprocessor_kwargs=preproc_kwargs or {})
     kwargs = dict(data=data, variable_names=['u'], max_deriv_order=tuple(max_deriv_order),
                   additional_tokens=additional_tokens or [])
     if derivs is not None:

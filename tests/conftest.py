@@ -9,7 +9,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 GOLDEN = os.path.join(ROOT, 'tests', 'golden')
-EQ_FIXTURES = ['wave_b5', 'wave_b10', 'burgers_b50', 'heat3d_b4']
+EQ_FIXTURES = ['wave_b5', 'wave_b10', 'burgers_b50', 'heat3d_b4', 'burgers_poly_b50']
 
 
 def pytest_configure(config):
@@ -40,3 +40,15 @@ def has_gpu():
         return torch.cuda.is_available()
     except Exception:       # noqa: BLE001
         return False
+
+
+def fixture_equations_procedural(fx):
+    """golden CSR with factor kinds / params -> nested encoding [[[(token, power, kind, param)]]]."""
+    eqs = []
+    for e in range(len(fx['term_off']) - 1):
+        terms = []
+        for t in range(fx['term_off'][e], fx['term_off'][e + 1]):
+            terms.append([(int(fx['fac_tok'][f]), float(fx['fac_pow'][f]), int(fx['fac_kind'][f]), float(fx['fac_par'][f]))
+                          for f in range(fx['fac_off'][t], fx['fac_off'][t + 1])])
+        eqs.append(terms)
+    return eqs

@@ -198,6 +198,33 @@ def test_synthetic_vs_oracle(cfg, pop, seed):
     check_against_oracle(res, tokens, shape, eqs, evals, cfg, min_checked=len(evals) // 2)
 
 
+def test_golden_procedural_tokens():
+    """reference-generated fixture with sin / cos / coordinate-power factors (CustomEvaluator families,
+    evaluators.py:47-89,141,150) evaluated in-kernel from the coordinate tokens (factor kinds 1, 2, 0)."""
+    from conftest import fixture_equations_procedural
+    fx = load_fixture('procedural')
+    shape = tuple(int(s) for s in fx['shape'])
+    eqs = fixture_equations_procedural(fx)
+    evals = [(int(e), int(t)) for e, t in zip(fx['ev_eq'], fx['ev_tgt'])]
+    with make_engine(shape, list(fx['tokens'])) as eng:
+        res = eng.evaluate(epde_b200.encode(eqs, evals))
+    checked = 0
+    for v, (e, t) in enumerate(evals):
+        o = orc.evaluate_equation(fx['tokens'], shape, eqs[e], targets=[t])[0]
+        if o.cond > COND_MAX:
+            continue
+        F = len(eqs[e]) - 1
+        ref = fx['ev_coef'][v, :F]
+        assert np.array_equal(res.coef[v, :F] != 0, ref != 0), f'eval {v}: selected set'
+        assert_rel(res.coef[v, :F], ref, f'eval {v} coef', rtol=1e-6, atol=1e-9 * max(1.0, np.abs(ref).max()))
+        assert_rel(res.intercept[v], fx['ev_b'][v], f'eval {v} intercept', rtol=1e-6, atol=1e-9)
+        assert bool(res.all_zero[v]) == bool(np.isnan(fx['ev_fit'][v]))
+        if not res.all_zero[v]:
+            assert_rel(res.fitness_l1[v], fx['ev_fit'][v], f'eval {v} fitness', rtol=1e-6)
+        checked += 1
+    assert checked >= 8
+
+
 @pytest.mark.parametrize('kind,pop', [('distinct', 48), ('wide16', 6), ('wide30', 4)])
 def test_stress_populations_vs_oracle(kind, pop):
     """populations that stress the column dictionary: 'distinct' = no term shared between equations (several launch

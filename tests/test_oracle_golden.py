@@ -169,3 +169,28 @@ def test_micro2_wide_and_weighted(ci):
     assert_rel(coef, ref_coef, 'coef', rtol=1e-6, atol=1e-11)
     assert_rel(b, float(z[f'c{ci}_b']), 'intercept', rtol=1e-6, atol=1e-9)
     assert_rel(cached, z[f'c{ci}_cached'], 'cached weights', rtol=1e-6, atol=1e-9)
+
+
+def test_procedural_tokens_fixture():
+    """sin / cos / coordinate-power tokens (CustomEvaluator families, evaluators.py:141,150): oracle == reference."""
+    from conftest import fixture_equations_procedural
+    fx = load_fixture('procedural')
+    shape = tuple(int(s) for s in fx['shape'])
+    eqs = fixture_equations_procedural(fx)
+    assert any(f[2] in (1, 2) for eq in eqs for term in eq for f in term)
+    checked = 0
+    for v in range(len(fx['ev_eq'])):
+        eq = eqs[int(fx['ev_eq'][v])]
+        o = orc.evaluate_equation(fx['tokens'], shape, eq, targets=[int(fx['ev_tgt'][v])])[0]
+        if o.cond > COND_MAX:
+            continue
+        F = len(eq) - 1
+        ref = fx['ev_coef'][v, :F]
+        assert np.array_equal(o.coef != 0, ref != 0), f'eval {v}: selected set'
+        assert_rel(o.coef, ref, f'eval {v} coef', rtol=1e-6, atol=1e-9 * max(1.0, np.abs(ref).max()))
+        if np.isnan(fx['ev_fit'][v]):
+            assert o.all_zero
+        else:
+            assert_rel(o.fitness, fx['ev_fit'][v], f'eval {v} fitness', rtol=1e-6)
+        checked += 1
+    assert checked >= 8
