@@ -1620,6 +1620,43 @@ __global__ void __launch_bounds__(256) crop_interior_kernel(CropParams p) {
 // C ABI
 // ------------------------------------------------------------------------------------------
 
+// Chebyshev-window derivative (preprocessing/cheb.py:14-85 as PolynomialDeriv applies it point by point,
+// deriv_calculators.py:111-134): at an interior index of the axis the m-th derivative of the least-squares Chebyshev
+// polynomial through the `window` neighbouring values, evaluated at the centre, is a LINEAR functional of those values;
+// the host computes its weights per index with numpy's own Chebyshev.fit (epde_b200/producers.py), the kernel applies
+// them.  Within `bound` of either end the reference switches to one-sided finite differences (preprocessing/fin_der.py).
+struct PolyParams {
+    const double* in;
+    double* out;
+    const double* w;         // [n][window] weights of the derivative at index i over in[i - window/2 .. i + window/2]
+    const double* x;         // [n] coordinates of the axis
+    long long total, stride; // elements; distance between neighbours along the axis
+    int n, window, bound, order;
+};
+
+__global__ void __launch_bounds__(256) poly_derivative_kernel(PolyParams p) {
+    for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < p.total; q += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)((q / p.stride) % p.n);
+        const double* c = p.in + q;
+        double v;
+        if (i >= p.bound && i <= p.n - p.bound) {
+            const int h = (p.window - 1) / 2;
+            const double* w = p.w + (size_t)i * p.window;
+            v = 0.0;
+            for (int j = 0; j < p.window; ++j) v = fma(w[j], c[(long long)(j - h) * p.stride], v);
+        } else {
+            const int sgn = (i < p.bound) ? 1 : -1;             // fin_der.py:13-17: I = idx +/- arange(6)
+            const double dx = p.x[i + sgn] - p.x[i];
+            const double f0 = c[0], f1 = c[(long long)sgn * p.stride], f2 = c[(long long)2 * sgn * p.stride],
+                         f3 = c[(long long)3 * sgn * p.stride], f4 = c[(long long)4 * sgn * p.stride];
+            if (p.order == 1) v = (f1 - f0) / dx;
+            else if (p.order == 2) v = (2 * f0 - 5 * f1 + 4 * f2 - f3) / (dx * dx);
+            else v = (-2.5 * f0 + 9 * f1 - 12 * f2 + 7 * f3 - 1.5 * f4) / (dx * dx * dx);
+        }
+        p.out[q] = v;
+    }
+}
+
 // sustained FP64 rate measurement (epde_measure_fp64_peak): independent FMA chains / DMMA chains, no memory traffic
 template <int CHAINS>
 __global__ void __launch_bounds__(256) fp64_dfma_kernel(double* out, int iters, double a, double b) {
@@ -2511,6 +2548,35 @@ int epde_fd_gradient(epde_ctx* c, const double* dev_in, double* dev_out, int ndi
     const int grid = (int)std::min<long long>((p.total + 255) / 256, (long long)c->sm_count * 16);
     c->launches++;
     fd_gradient_kernel<<<grid, 256, 0, c->stream>>>(p);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int epde_poly_derivative(epde_ctx* c, const double* dev_in, double* dev_out, int ndim, const int64_t* shape, int axis,
+                         int order, int window, const double* weights, const double* coords) {
+    if (!c || !dev_in || !dev_out || !shape || !weights || !coords) return fail("epde_poly_derivative: null argument");
+    if (ndim < 1 || ndim > EPDE_MAX_NDIM || axis < 0 || axis >= ndim) return fail("epde_poly_derivative: bad ndim / axis");
+    if (dev_in == dev_out) return fail("epde_poly_derivative: in-place differentiation is not supported");
+    if (order < 1 || order > 3) return fail("epde_poly_derivative: derivative order %d not in 1..3 (fin_der.py:33)", order);
+    if (window < 3 || !(window & 1)) return fail("epde_poly_derivative: window %d must be odd and >= 3", window);
+    const int n = (int)shape[axis];
+    const int bound = window / 2 + 1;                   // deriv_calculators.py:117
+    if (n < 2 * bound + 1 || n < 6) return fail("epde_poly_derivative: axis %d has %d points, too few for window %d", axis, n, window);
+    CK(cudaSetDevice(c->device));
+    PolyParams p;
+    memset(&p, 0, sizeof p);
+    p.in = dev_in; p.out = dev_out; p.n = n; p.window = window; p.bound = bound; p.order = order;
+    p.total = 1; p.stride = 1;
+    for (int d = 0; d < ndim; ++d) { p.total *= shape[d]; if (d > axis) p.stride *= shape[d]; }
+    const size_t wbytes = sizeof(double) * (size_t)n * window, xbytes = sizeof(double) * (size_t)n;
+    if (c->d_fd.ensure(wbytes + xbytes)) return 1;
+    CK(cudaMemcpyAsync(c->d_fd.ptr, weights, wbytes, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync((char*)c->d_fd.ptr + wbytes, coords, xbytes, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));               // pageable host sources
+    p.w = (const double*)c->d_fd.ptr; p.x = (const double*)((char*)c->d_fd.ptr + wbytes);
+    const int grid = (int)std::min<long long>((p.total + 255) / 256, (long long)c->sm_count * 16);
+    c->launches++;
+    poly_derivative_kernel<<<grid, 256, 0, c->stream>>>(p);
     CK(cudaGetLastError());
     return 0;
 }

@@ -303,3 +303,162 @@ def make_moeadd_director(batched=True, params_filename=None, **director_params):
     director.builder = StrategyBuilder(MOEADDSectorProcesser)
     director.use_baseline(use_solver=False, batched=batched, **director_params)
     return director
+
+
+# ------------------------------------------------------------------------------------------
+# the process-global tensor cache on the device (epde/cache/cache.py:141-524,
+# globals.py:26-42) and its persistence (section 8f item 4: loader.py:242-283)
+# ------------------------------------------------------------------------------------------
+from collections.abc import MutableMapping      # noqa: E402
+
+from epde.cache.cache import Cache as _RefCache  # noqa: E402
+
+
+class _HbmDict(MutableMapping):
+    """The ``memory_default['numpy']`` dictionary of a Cache with its values in HBM: storing an (N,) float64 vector
+    uploads it as an engine token and keeps NO host copy; reading downloads a fresh copy (callers get values, never
+    references -- the reference's contract is 'do not mutate', cache.py:397-427).  Anything that is not a vector of N
+    points (N = points of the inner grid) stays on the host."""
+
+    def __init__(self, owner):
+        self._owner = owner
+        self._ids = {}          # key -> engine token id
+        self._host = {}         # key -> object kept on the host (not an (N,) vector)
+
+    def _bound(self):
+        return self._owner.device_binding()
+
+    def __setitem__(self, key, value):
+        arr = np.asarray(value)
+        b = self._bound()
+        if arr.dtype != object and arr.ndim >= 1 and arr.size == b.engine.n_points:
+            tid = b.token_id(('cache', key), create=True)
+            b.engine.upload(tid, np.ascontiguousarray(arr, dtype=np.float64).reshape(-1))
+            self._ids[key] = (tid, arr.shape)
+            self._host.pop(key, None)
+            # power-1 entries of plain tokens are what equations reference by factor label (supplementary.py:216-220)
+            if isinstance(key, tuple) and len(key) == 2 and isinstance(key[0], str) and key[1] == (1.0,):
+                b.token_ids[key[0]] = tid
+        else:
+            self._host[key] = value
+            self._ids.pop(key, None)
+
+    def __getitem__(self, key):
+        if key in self._ids:
+            tid, shape = self._ids[key]
+            return self._bound().engine.download(tid).reshape(shape)
+        return self._host[key]
+
+    def __delitem__(self, key):
+        if key in self._ids:
+            tid, _ = self._ids.pop(key)
+            b = self._bound()
+            b.engine.delete(tid)
+            b.token_ids.pop(('cache', key), None)
+            if isinstance(key, tuple) and len(key) == 2 and b.token_ids.get(key[0]) == tid:
+                b.token_ids.pop(key[0], None)
+        else:
+            del self._host[key]
+
+    def __iter__(self):
+        yield from self._ids
+        yield from self._host
+
+    def __len__(self):
+        return len(self._ids) + len(self._host)
+
+    def __contains__(self, key):
+        try:
+            return key in self._ids or key in self._host
+        except TypeError:
+            return False
+
+    def nbytes(self):
+        return 8 * self._bound().engine.n_points * len(self._ids)
+
+
+class DeviceTensorCache(_RefCache):
+    """``epde.cache.cache.Cache`` whose base tensors live in HBM only: a drop-in for ``global_var.tensor_cache``.
+    Every inherited method keeps its behaviour (add / get / __contains__ / delete_entry / get_all / prune_tensors /
+    the count-based budget of memory_usage_properties); what changes is where ``memory_default['numpy']`` keeps its
+    values.  ``use_structural`` with base data marks entries as merged instead of copying the dictionary (the copy
+    would bring every tensor back to the host; ``get(structural=True)`` already redirects merged labels to the base
+    data, cache.py:412-414).  The engine is bound lazily from EPDE's globals at the first stored tensor (the inner
+    shape is known once ``grid_cache.set_boundaries`` has run, cache.py:250-270)."""
+
+    def __init__(self, device='cpu'):
+        super().__init__(device=device)
+        self.memory_default['numpy'] = _HbmDict(self)
+        self._b200_binding = None
+
+    def device_binding(self):
+        if self._b200_binding is None:
+            global _bound_to
+            self._b200_binding = bind_from_epde_globals(force=True)
+            _bound_to = self
+        return self._b200_binding
+
+    def use_structural(self, use_base_data=True, label=None, replacing_data=None):
+        if use_base_data and label is None:
+            for key in self.memory_default['numpy'].keys():
+                self.structural_and_base_merged[key] = True
+            return
+        if use_base_data and isinstance(label, tuple):
+            self.structural_and_base_merged[label] = True
+            return
+        super().use_structural(use_base_data=use_base_data, label=label, replacing_data=replacing_data)
+
+    @property
+    def consumed_memory(self):
+        mem = self.memory_default['numpy'].nbytes()
+        mem += int(np.sum([np.asarray(v).nbytes for v in self.memory_normalized['numpy'].values()]))
+        for lab, merged in self.structural_and_base_merged.items():
+            if not merged:
+                mem += self.memory_structural['numpy'][lab].nbytes
+        return mem
+
+    # ---- persistence (loader.py:242-283 pickles a Cache through its __dict__): host form and back
+    def to_host_cache(self):
+        """a plain reference ``Cache`` holding numpy copies of everything: what EPDELoader / pickle can store."""
+        host = _RefCache(device=self._device)
+        for k, v in self.__dict__.items():
+            if k in ('memory_default', '_b200_binding'):
+                continue
+            setattr(host, k, v)
+        host.memory_default = {'torch': dict(self.memory_default['torch']),
+                               'numpy': {k: np.array(v) for k, v in self.memory_default['numpy'].items()}}
+        return host
+
+    @classmethod
+    def from_host_cache(cls, host):
+        """re-upload a restored reference ``Cache`` (SURVEY.md section 5 'checkpoint / resume')."""
+        dev = cls(device=getattr(host, '_device', 'cpu'))
+        for k, v in host.__dict__.items():
+            if k != 'memory_default':
+                setattr(dev, k, v)
+        dev._b200_binding = None
+        for k, v in host.memory_default['numpy'].items():
+            dev.memory_default['numpy'][k] = v
+        dev.memory_default['torch'] = dict(host.memory_default.get('torch', {}))
+        return dev
+
+
+def install_device_tensor_cache():
+    """Make every ``EpdeSearch`` created from now on keep its tensor cache in HBM: wraps ``globals.init_caches``
+    (globals.py:26-42), which EPDE calls while setting the domain up (interface.py:486-509), so that it installs a
+    :class:`DeviceTensorCache` as ``global_var.tensor_cache``.  Returns a function that undoes the wrapping."""
+    original = global_var.init_caches
+    if getattr(original, '_b200_wrapped', False):
+        return lambda: None
+
+    def init_caches(set_grids=False, device='cpu'):
+        original(set_grids=set_grids, device=device)
+        global_var.tensor_cache = DeviceTensorCache(device=device)
+        ops.unbind()
+
+    init_caches._b200_wrapped = True
+    global_var.init_caches = init_caches
+
+    def undo():
+        global_var.init_caches = original
+    return undo

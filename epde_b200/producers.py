@@ -88,3 +88,78 @@ def fd_derivatives(engine, data, coords, max_order, boundary, first_token_id=0, 
     engine.synchronize()
     del alive
     return ids
+
+
+def chebyshev_window_weights(coords, order, window=9, n_der=None, poly_order=None):
+    """[n][window] weights W with  d^order/dx^order (Chebyshev LSQ fit of the window)(x_i) = sum_j W[i, j] * f[i - h + j].
+
+    Follows get_cheb_for_point / process_point_cheb (preprocessing/cheb.py:14-85) to the letter: polynomial degree
+    n_der + 1 (``poly_order`` if given; one less when it equals the window size), ``Chebyshev.fit`` on the raw window
+    coordinates (numpy maps them to [-1, 1] and solves the least squares by SVD), derivative of the fitted series at the
+    centre coordinate.  The fit is linear in the window values, so fitting the unit vectors gives the functional; rows
+    within window // 2 + 1 of either end are left zero (the kernel uses one-sided differences there, fin_der.py)."""
+    from numpy.polynomial.chebyshev import Chebyshev
+    x = np.ascontiguousarray(coords, dtype=np.float64).reshape(-1)
+    n, h = x.size, (window - 1) // 2
+    n_der = int(order if n_der is None else n_der)
+    deg = (n_der + 1) if poly_order is None else int(poly_order)
+    if window == deg:
+        deg -= 1
+    bound = window // 2 + 1
+    W = np.zeros((n, window))
+    eye = np.eye(window)
+    cache = {}
+    for i in range(bound, n - bound + 1):
+        xr = x[i - h:i + h + 1]
+        key = tuple(np.round((xr - xr[0]) / (xr[-1] - xr[0]), 14))     # equal relative spacing -> same fit up to scale
+        ref = cache.get(key)
+        if ref is not None and ref[1] == (float(xr[0]), float(xr[-1])):
+            W[i] = ref[0]
+            continue
+        row = np.array([Chebyshev.fit(xr, eye[j], deg).deriv(m=int(order))(xr[int(xr.size / 2.)]) for j in range(window)])
+        W[i] = row
+        cache[key] = (row, (float(xr[0]), float(xr[-1])))
+    return W
+
+
+def poly_derivatives(engine, data, coords, max_order, boundary, first_token_id=0, field_token_id=None,
+                     polynomial_window=9, poly_order=None):
+    """The reference's 'poly' preprocessor on the device: ``PolynomialDeriv`` (deriv_calculators.py:111-134 -- a
+    4-process pool over grid points, each fitting Chebyshev polynomials through a 9-point window per axis,
+    cheb.py:40-85) followed by the boundary crop into the HBM cache.  Same arguments and token order as
+    :func:`fd_derivatives`; derivative orders above 3 are not defined by the reference (fin_der.py:33)."""
+    import torch
+    lib = engine._lib
+    dev = torch.device('cuda', engine.device)
+    if isinstance(data, np.ndarray):
+        field = torch.from_numpy(np.ascontiguousarray(data, dtype=np.float64)).to(dev)
+    else:
+        field = data.to(dev, torch.float64).contiguous()
+    nd = field.dim()
+    shape = tuple(int(s) for s in field.shape)
+    if isinstance(max_order, int):
+        max_order = [max_order] * nd
+    if isinstance(boundary, int):
+        boundary = [boundary] * nd
+    if len(coords) != nd or len(max_order) != nd or len(boundary) != nd:
+        raise ValueError('Given derivative orders do not match the data tensor dimensionality')      # cheb.py:55
+    coords = [np.ascontiguousarray(c, dtype=np.float64).reshape(-1) for c in coords]
+    shp, shp_p = _i64(shape)
+    bnd, bnd_p = _i64(boundary)
+    torch.cuda.current_stream(dev).synchronize()
+    if field_token_id is not None:
+        _lib.check(lib.epde_cache_upload_interior(engine._h, int(field_token_id), C.c_void_p(field.data_ptr()), nd,
+                                                  shp_p, bnd_p))
+    ids, nxt = [], int(first_token_id)
+    out = torch.empty_like(field)
+    for dim in range(nd):
+        for m in range(1, int(max_order[dim]) + 1):
+            W = chebyshev_window_weights(coords[dim], m, polynomial_window, n_der=int(max_order[dim]), poly_order=poly_order)
+            _lib.check(lib.epde_poly_derivative(engine._h, C.c_void_p(field.data_ptr()), C.c_void_p(out.data_ptr()), nd, shp_p,
+                                                int(dim), int(m), int(polynomial_window), W.ctypes.data_as(_lib.c_f64p),
+                                                coords[dim].ctypes.data_as(_lib.c_f64p)))
+            _lib.check(lib.epde_cache_upload_interior(engine._h, nxt, C.c_void_p(out.data_ptr()), nd, shp_p, bnd_p))
+            engine.synchronize()              # `out` is reused by the next derivative
+            ids.append(nxt)
+            nxt += 1
+    return ids

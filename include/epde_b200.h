@@ -181,6 +181,15 @@ int epde_fd_gradient(epde_ctx* ctx, const double* dev_in, double* dev_out, int n
                      int axis, const double* coords);
 int epde_cache_upload_interior(epde_ctx* ctx, int token_id, const double* dev_full, int ndim,
                                const int64_t* full_shape, const int64_t* boundary);
+/* epde_poly_derivative = one derivative of the reference's 'poly' preprocessor (PolynomialDeriv,
+ * epde/preprocessing/deriv_calculators.py:111-134 -> process_point_cheb, preprocessing/cheb.py:40-85): the `order`-th
+ * derivative along `axis` of the least-squares Chebyshev polynomial through the `window` (odd) values centred on each
+ * point; within window / 2 + 1 points of either end the one-sided finite differences of preprocessing/fin_der.py.
+ * The fit is linear in the window values: `weights` (host, [shape[axis]][window]) holds, per index of the axis, the
+ * derivative-at-the-centre functional as numpy's Chebyshev.fit defines it (computed by epde_b200/producers.py);
+ * `coords` = host coordinate vector of the axis.  Full-grid device tensors, dev_out != dev_in, asynchronous. */
+int epde_poly_derivative(epde_ctx* ctx, const double* dev_in, double* dev_out, int ndim, const int64_t* shape,
+                         int axis, int order, int window, const double* weights, const double* coords);
 
 /* Measurement aid (no reference counterpart): sustained FP64 rate of `device` in TFLOP/s through plain FMA
  * chains (SASS DFMA) and through the FP64 tensor-core instruction pass A uses (mma.sync m8n8k4 f64, SASS

@@ -562,3 +562,41 @@ def evaluate_equation_streamed(tokens, grid_shape, equation, targets=None):
         r.fitness = float(s[0] / s[1])
         r.fitness_l2 = float(np.sqrt(s[2]))
     return results
+
+
+# ----------------------------------------------------------------------------------------
+# token producer: the 'poly' preprocessor (preprocessing/deriv_calculators.py:111-134, cheb.py:14-85, fin_der.py)
+# restated point by point for SMALL grids (pure Python loop over points, as the reference does in its process pool)
+# ----------------------------------------------------------------------------------------
+def poly_derivative_points(data, coords, axis, order, n_der, window=9, poly_order=None):
+    """order-th derivative along `axis` of `data` (full grid) exactly as process_point_cheb computes it per point:
+    Chebyshev.fit over the window at interior indices (cheb.py:14-37), one-sided finite differences within
+    window // 2 + 1 points of the ends (fin_der.py:12-36).  coords: 1-D coordinate vector of the axis."""
+    from numpy.polynomial.chebyshev import Chebyshev
+    data = np.asarray(data, dtype=np.float64)
+    x = np.asarray(coords, dtype=np.float64).reshape(-1)
+    n = data.shape[axis]
+    bound = window // 2 + 1
+    deg = (n_der + 1) if poly_order is None else poly_order
+    if window == deg:
+        deg -= 1
+    moved = np.moveaxis(data, axis, 0).reshape(n, -1)
+    out = np.empty_like(moved)
+    h = (window - 1) // 2
+    for i in range(n):
+        if bound <= i <= n - bound:
+            xr = x[i - h:i + h + 1]
+            for c in range(moved.shape[1]):
+                out[i, c] = Chebyshev.fit(xr, moved[i - h:i + h + 1, c], deg).deriv(m=order)(xr[int(xr.size / 2.)])
+        else:
+            I = i + np.arange(6) if i < bound else i - np.arange(6)
+            F, xx = moved[I], x[I]
+            dx = xx[1] - xx[0]
+            if order == 1:
+                out[i] = (F[1] - F[0]) / dx
+            elif order == 2:
+                out[i] = (2 * F[0] - 5 * F[1] + 4 * F[2] - F[3]) / dx ** 2
+            else:
+                out[i] = (-2.5 * F[0] + 9 * F[1] - 12 * F[2] + 7 * F[3] - 1.5 * F[4]) / dx ** 3
+    shape = (n,) + tuple(s for d, s in enumerate(data.shape) if d != axis)
+    return np.moveaxis(out.reshape(shape), 0, axis)

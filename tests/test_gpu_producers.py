@@ -75,3 +75,42 @@ def test_produced_tokens_feed_the_evaluator():
         c = eng.evaluate(enc)
     for k in ('coef', 'intercept', 'fitness_l1', 'fitness_l2', 'stability'):
         assert np.array_equal(getattr(a, k), getattr(c, k)), k
+
+
+def test_poly_derivatives_match_reference_fixture():
+    """device Chebyshev producer (producers.poly_derivatives -> epde_poly_derivative) on the noisy Burgers field ==
+    the derivative tokens the reference's 'poly' preprocessor (PolynomialDeriv, deriv_calculators.py:111-134) produced
+    for BASELINE config 2 (tests/golden/burgers_poly_b50.npz): 1e-10 relative to the token's scale."""
+    from conftest import load_fixture
+    fx = load_fixture('burgers_poly_b50')
+    u, t, x, b = fx['data_full'], fx['axis0'], fx['axis1'], int(fx['boundary'])
+    labels = [str(l) for l in fx['labels']]
+    inner = tuple(int(s) for s in fx['shape'])
+    with epde_b200.Engine(inner, device=0) as eng:
+        ids = producers.poly_derivatives(eng, u, [t, x], (1, 2), b, first_token_id=1, field_token_id=0)
+        names = producers.deriv_labels('u', (1, 2))
+        assert np.array_equal(eng.download(0), fx['tokens'][labels.index('u')])
+        for i, lab in zip(ids, names):
+            ref = fx['tokens'][labels.index(lab)]
+            got = eng.download(i)
+            assert np.abs(got - ref).max() <= 1e-10 * np.abs(ref).max(), (lab, np.abs(got - ref).max(), np.abs(ref).max())
+
+
+@pytest.mark.parametrize('shape,max_order', [((24, 30), (2, 3)), ((14, 16, 18), (1, 2, 2))])
+def test_poly_derivatives_with_boundary_rows(shape, max_order):
+    """boundary 0: the rows within window // 2 + 1 of the ends use the one-sided differences of fin_der.py; checked
+    against the point-by-point restatement of cheb.py / fin_der.py (oracle.poly_derivative_points), non-uniform axes."""
+    from oracle import epde_oracle as orc
+    rng = np.random.default_rng(5)
+    coords = [np.sort(rng.random(n)) * (2 + d) if d == 1 else np.linspace(0, 1 + d, n) for d, n in enumerate(shape)]
+    grids = np.meshgrid(*coords, indexing='ij')
+    data = np.sin(2.0 * grids[0]) * np.cos(grids[-1]) + 0.02 * rng.standard_normal(shape)
+    with epde_b200.Engine(shape, device=0) as eng:
+        ids = producers.poly_derivatives(eng, data, coords, max_order, 0, first_token_id=0)
+        k = 0
+        for dim in range(len(shape)):
+            for m in range(1, max_order[dim] + 1):
+                ref = orc.poly_derivative_points(data, coords[dim], dim, m, max_order[dim]).reshape(-1)
+                got = eng.download(ids[k])
+                assert np.abs(got - ref).max() <= 1e-9 * np.abs(ref).max(), (dim, m, np.abs(got - ref).max())
+                k += 1

@@ -194,3 +194,29 @@ def test_procedural_tokens_fixture():
             assert_rel(o.fitness, fx['ev_fit'][v], f'eval {v} fitness', rtol=1e-6)
         checked += 1
     assert checked >= 8
+
+
+def test_poly_derivative_restatement_matches_reference_fixture():
+    """oracle.poly_derivative_points (restated cheb.py / fin_der.py) == the derivative tokens the reference's 'poly'
+    preprocessor produced for the noisy Burgers field (a strip of the grid: the per-point fits are slow on the host),
+    and the linear-functional form the device producer uses (producers.chebyshev_window_weights) == both."""
+    from epde_b200.producers import chebyshev_window_weights
+    fx = load_fixture('burgers_poly_b50')
+    u, t, x, b = fx['data_full'], fx['axis0'], fx['axis1'], int(fx['boundary'])
+    labels = [str(l) for l in fx['labels']]
+    inner = (u.shape[0] - 2 * b, u.shape[1] - 2 * b)
+    cols = slice(b, b + 6)                                   # 6 columns of the interior
+    for lab, axis, m, nder in (('du/dx0', 0, 1, 1), ('d^2u/dx1^2', 1, 2, 2)):
+        ref = fx['tokens'][labels.index(lab)].reshape(inner)
+        if axis == 0:
+            got = orc.poly_derivative_points(u[:, cols], t, 0, m, nder)[b:-b, :]
+            want = ref[:, :6]
+        else:
+            got = orc.poly_derivative_points(u[cols, :], x, 1, m, nder)[:, b:-b]
+            want = ref[:6, :]
+        assert_rel(got, want, f'{lab} restatement', rtol=1e-10, atol=1e-10 * np.abs(want).max())
+        W = chebyshev_window_weights([t, x][axis], m, 9, n_der=nder)
+        i = b + 3
+        win = u[i - 4:i + 5, b] if axis == 0 else u[b, i - 4:i + 5]
+        assert_rel(float(W[i] @ win), ref[3, 0] if axis == 0 else ref[0, 3], f'{lab} functional', rtol=1e-9,
+                   atol=1e-10 * np.abs(want).max())

@@ -262,3 +262,69 @@ def test_director_runs_epde_search_fit(integration):
                 np.testing.assert_allclose(eq.coefficients_stability, ref.coefficients_stability, rtol=1e-5, atol=1e-12)
                 checked += 1
     assert checked >= 4
+
+
+def test_device_tensor_cache_as_global_cache_and_persistence(integration):
+    """with install_device_tensor_cache() EPDE's own `global_var.tensor_cache` keeps its
+    base tensors in the engine only (no numpy copies), every consumer of the Cache API still works (create_pool,
+    Factor.evaluate through Equation.evaluate, the operator mirrors, a short MOEADD fit), and the cache survives a
+    pickle round trip of its host form (what EPDELoader stores) with a re-upload."""
+    import copy
+    import pickle
+    ei, ops, made = integration
+    import epde.globals as gv
+    from epde.interface.interface import EpdeSearch
+    undo = ei.install_device_tensor_cache()
+    try:
+        d = np.loadtxt(os.path.join(rl.REFERENCE_ROOT, 'examples/data/wave_sln_80.csv'), delimiter=',').T
+        t = np.linspace(0, 1, d.shape[0]); x = np.linspace(0, 1, d.shape[1])
+        grids = np.meshgrid(t, x, indexing='ij')
+        np.random.seed(3)
+        s = EpdeSearch(multiobjective_mode=True, use_default_strategy=False, director=ei.make_moeadd_director(),
+                       use_solver=False, use_pic=True, boundary=10, coordinate_tensors=tuple(grids), device='cpu',
+                       verbose_params={'show_iter_idx': False})
+        s.set_preprocessor(default_preprocessor_type='FD', preprocessor_kwargs={})
+        s.create_pool(data=d, variable_names=['u'], max_deriv_order=(2, 2), additional_tokens=[])
+        tc = gv.tensor_cache
+        assert isinstance(tc, ei.DeviceTensorCache)
+        store = tc.memory_default['numpy']
+        n_pts = int(np.prod(gv.grid_cache.inner_shape))
+        assert len(store._ids) >= 5 and not any(np.asarray(v).size == n_pts for v in store._host.values())
+        eng = made[-1]
+        assert tc.consumed_memory == 8 * n_pts * len(store._ids) == eng.consumed_memory
+        # reference-side consumers read through the same object
+        key = ('du/dx0', (1.0,))
+        assert (key, False) in tc and key in tc
+        ref_vec = np.gradient(d, t, axis=0)[10:-10, 10:-10].reshape(-1)
+        np.testing.assert_allclose(tc.get(key), ref_vec, rtol=1e-12, atol=1e-14)
+        _, eq = rl.translate('1.0 * u{power: 2} * du/dx1{power: 1} + 1.0 * d^2u/dx1^2{power: 1} + 0. = d^2u/dx0^2{power: 1}', s)
+        eq.target_idx = 2
+        _, target, feats = eq.evaluate(normalize=True, return_val=False)
+        u_in = d[10:-10, 10:-10].reshape(-1)
+        np.testing.assert_allclose(feats[:, 0], u_in ** 2 * np.gradient(d, x, axis=1)[10:-10, 10:-10].reshape(-1), rtol=1e-12)
+        # the mirrors use the tokens that are already resident (no second upload of the same label)
+        before = len(eng.tokens)
+        fit = _wire(ops.L2LRFitness, ops.LASSOSparsity, ops.LinRegBasedCoeffsEquation)
+        val = fit.apply(eq, {}, force_out_of_place=True)
+        ref_l2lr, _, _ = rl.make_operators()
+        eq2 = copy.deepcopy(eq)
+        ref_val = ref_l2lr.apply(eq2, {}, force_out_of_place=True)
+        assert (val is None) == (ref_val is None)
+        if val is not None:
+            np.testing.assert_allclose(val, ref_val, rtol=1e-6)
+        assert len([k for k in eng.tokens]) <= before + 0
+        # persistence: host form -> pickle -> restore -> re-upload
+        blob = pickle.dumps(tc.to_host_cache())
+        host = pickle.loads(blob)
+        assert type(host).__name__ == 'Cache' and isinstance(host.memory_default['numpy'], dict)
+        restored = ei.DeviceTensorCache.from_host_cache(host)
+        np.testing.assert_array_equal(restored.get(key), tc.get(key))
+        assert set(restored.memory_default['numpy'].keys()) == set(store.keys())
+        # and a short search on top of the device cache
+        s.set_moeadd_params(population_size=3, training_epochs=1)
+        s.fit(data=d, variable_names=['u'], max_deriv_order=(2, 2), equation_terms_max_number=3, data_fun_pow=2,
+              additional_tokens=[], equation_factors_max_number={'factors_num': [1, 2], 'probas': [0.8, 0.2]},
+              eq_sparsity_interval=(1e-6, 1e-4))
+        assert all(eq.fitness_calculated for lvl in s.optimizer.pareto_levels.levels for soeq in lvl for eq in soeq)
+    finally:
+        undo()
