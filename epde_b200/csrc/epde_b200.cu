@@ -71,7 +71,9 @@
 #define PP_A (PT_A + 4)        // its pitch: == 4 (mod 16) doubles -> conflict-free DMMA fragment loads
 #define TASK_A 2               // a pass-A task covers TASK_A x TASK_B block pairs
 #define TASK_B 3
-#define GRAM_MAX_WARPS 12
+#define GRAM_MAX_WARPS 12     // consumer (tensor-core) warps of pass A
+#define GRAM_PROD_WARPS 10     // producer (term assembly) warps of pass A (fewer when the consumers need the slots)
+#define GRAM_MAX_THREADS 704
 #define PT_B 256               // points per pass-B chunk
 #define PP_B (PT_B + 4)
 #define RES_WARPS 16
@@ -253,29 +255,29 @@ __device__ __forceinline__ void load_cols_to_smem(ColDesc* s_cols, const ColDesc
 template <int NPL>
 __device__ __forceinline__ void build_columns(unsigned ct, int ppb, unsigned cols, int nbuild, const FactorDesc* gfac,
                                               unsigned tile, int tstride_b, const int (&toffb)[NPL],
-                                              const bool (&valid)[NPL], int warp, int nwarps, int lane) {
+                                              const bool (&valid)[NPL], int warp, int nwarps, int lane, int epoch) {
     for (int c = warp; c < nbuild; c += nwarps) {
         const int4 q0 = lds_v4(cols + c * 32), q1 = lds_v4(cols + c * 32 + 16);
         const int nf = q1.z & 0xffff, kind = q1.z >> 16;
         double v[NPL];
         if (kind == 0) {
 #pragma unroll
-            for (int k = 0; k < NPL; ++k) v[k] = lds_f64(tile + q0.x + toffb[k]);
+            for (int k = 0; k < NPL; ++k) v[k] = lds_f64_e(tile + q0.x + toffb[k], epoch);
             if (nf > 1) {
 #pragma unroll
-                for (int k = 0; k < NPL; ++k) v[k] *= lds_f64(tile + q0.y + toffb[k]);
+                for (int k = 0; k < NPL; ++k) v[k] *= lds_f64_e(tile + q0.y + toffb[k], epoch);
                 if (nf > 2) {
 #pragma unroll
-                    for (int k = 0; k < NPL; ++k) v[k] *= lds_f64(tile + q0.z + toffb[k]);
+                    for (int k = 0; k < NPL; ++k) v[k] *= lds_f64_e(tile + q0.z + toffb[k], epoch);
                     if (nf > 3) {
 #pragma unroll
-                        for (int k = 0; k < NPL; ++k) v[k] *= lds_f64(tile + q0.w + toffb[k]);
+                        for (int k = 0; k < NPL; ++k) v[k] *= lds_f64_e(tile + q0.w + toffb[k], epoch);
                         if (nf > 4) {
 #pragma unroll
-                            for (int k = 0; k < NPL; ++k) v[k] *= lds_f64(tile + q1.x + toffb[k]);
+                            for (int k = 0; k < NPL; ++k) v[k] *= lds_f64_e(tile + q1.x + toffb[k], epoch);
                             if (nf > 5) {
 #pragma unroll
-                                for (int k = 0; k < NPL; ++k) v[k] *= lds_f64(tile + q1.y + toffb[k]);
+                                for (int k = 0; k < NPL; ++k) v[k] *= lds_f64_e(tile + q1.y + toffb[k], epoch);
                             }
                         }
                     }
@@ -287,7 +289,7 @@ __device__ __forceinline__ void build_columns(unsigned ct, int ppb, unsigned col
             for (int f = 0; f < nf; ++f) {
                 const FactorDesc fd = gfac[q1.w + f];
 #pragma unroll
-                for (int k = 0; k < NPL; ++k) v[k] *= apply_factor(fd, lds_f64(tile + fd.slot * tstride_b + toffb[k]));
+                for (int k = 0; k < NPL; ++k) v[k] *= apply_factor(fd, lds_f64_e(tile + fd.slot * tstride_b + toffb[k], epoch));
             }
         } else {
 #pragma unroll
@@ -336,6 +338,7 @@ struct GramParams {
     double* cells;           // [n_cells][n_ent]
     int n_ent;
     int use_tma;             // 1: token tiles come through the tensor maps below; 0: plain loads (odd last axis)
+    int nstages;             // token-tile buffers (2: the next unit's tile lands while this one is consumed)
     int box_a, box_b, box_c; // tile extents = TMA box (slot A rows, slot B rows, last-axis columns)
     alignas(64) CUtensorMap tmap[MAXU + 1];
 };
@@ -353,125 +356,202 @@ __device__ __forceinline__ void tma_load_tile(double* dst, const CUtensorMap* tm
                      ::"r"(d), "l"(tm), "r"(b), "r"(c0) : "memory");
 }
 
+// the k-step loop of one consumer warp, specialised on the task's pair mask: a predicated-off DMMA occupies the FP64
+// tensor pipe exactly like an executed one (measured: scratch/dmma_feed.cu), so inactive pair slots must not exist in
+// the instruction stream at all -- one instantiation per mask, selected once per chunk.
+template <int MASK, bool WEIGHTED>
+__device__ __forceinline__ void gram_ksteps(double (&acc)[TASK_PAIRS][2], unsigned ct, const unsigned (&a_off)[TASK_A],
+                                            const unsigned (&b_off)[TASK_B], unsigned w_off, int kpart, int nks, int ksplit) {
+    constexpr bool use_a[TASK_A] = {(MASK & 0x07) != 0, (MASK & 0x38) != 0};
+    constexpr bool use_b[TASK_B] = {(MASK & 0x09) != 0, (MASK & 0x12) != 0, (MASK & 0x24) != 0};
+    for (int s = kpart; s < nks; s += ksplit) {
+        double a[TASK_A], b[TASK_B];
+#pragma unroll
+        for (int i = 0; i < TASK_A; ++i) if (use_a[i]) a[i] = lds_f64(ct + a_off[i] + s * 32);
+#pragma unroll
+        for (int j = 0; j < TASK_B; ++j) if (use_b[j]) b[j] = lds_f64(ct + b_off[j] + s * 32);
+        if (WEIGHTED) {
+            const double w = lds_f64(ct + w_off + s * 32);
+#pragma unroll
+            for (int j = 0; j < TASK_B; ++j) if (use_b[j]) b[j] *= w;
+        }
+#pragma unroll
+        for (int i = 0; i < TASK_A; ++i)
+#pragma unroll
+            for (int j = 0; j < TASK_B; ++j)
+                if ((MASK >> (i * TASK_B + j)) & 1) dmma884(acc[i * TASK_B + j][0], acc[i * TASK_B + j][1], a[i], b[j]);
+    }
+}
+
 template <bool WEIGHTED>
-__global__ void __launch_bounds__(GRAM_MAX_WARPS * 32, 2) gram_dmma_kernel(const __grid_constant__ GramParams p) {
+__device__ __forceinline__ void gram_ksteps_dispatch(int mask, double (&acc)[TASK_PAIRS][2], unsigned ct,
+                                                     const unsigned (&a_off)[TASK_A], const unsigned (&b_off)[TASK_B],
+                                                     unsigned w_off, int kpart, int nks, int ksplit) {
+    switch (mask) {
+#define GK(M) case M: gram_ksteps<M, WEIGHTED>(acc, ct, a_off, b_off, w_off, kpart, nks, ksplit); break;
+#define GK8(B) GK(B) GK(B + 1) GK(B + 2) GK(B + 3) GK(B + 4) GK(B + 5) GK(B + 6) GK(B + 7)
+        GK8(0) GK8(8) GK8(16) GK8(24) GK8(32) GK8(40) GK8(48) GK8(56)
+#undef GK8
+#undef GK
+        default: break;
+    }
+}
+
+// named barriers (bar.sync / bar.arrive with an explicit thread count): producer <-> consumer hand-over of the two
+// column-tile buffers, and a consumer-only barrier for the ksplit reduction
+#define BAR_FULL 1           // + buffer: producers arrive, consumers wait
+#define BAR_EMPTY 3          // + buffer: consumers arrive, producers wait
+#define BAR_CONS 5
+__device__ __forceinline__ void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
+// Warp-specialised: the first `ncons` warps are CONSUMERS (one pass-A task each, DMMA only), the remaining warps are
+// PRODUCERS (TMA token tiles -> column tile).  Two column-tile buffers: the producers build chunk k + 1 while the
+// consumers run the tensor cores on chunk k, so the FP64 tensor pipe never waits for term assembly.
+template <bool WEIGHTED>
+__global__ void __launch_bounds__(GRAM_MAX_THREADS, 1) gram_dmma_kernel(const __grid_constant__ GramParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ uint64_t s_bar;
+    __shared__ uint64_t s_bar[2];
     const int tid = threadIdx.x, nthreads = blockDim.x;
     const int warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
+    const int ncons = p.ntasks * p.ksplit, nprod = nwarps - ncons;
     const int tstride = (p.box_a * p.box_b * p.box_c + 15) & ~15;           // doubles per token tile (128-byte multiple)
-    double* tile = (double*)smem_raw;                                        // [U][box_a][box_b][box_c]
-    double* ctp = tile + (size_t)p.U * tstride;                              // [nbuild][PP_A]
-    ColDesc* s_cols = (ColDesc*)(ctp + (size_t)p.nbuild * PP_A);             // [nbuild]
+    double* tiles = (double*)smem_raw;                                       // [nstages][U][box_a][box_b][box_c]
+    double* ctp = tiles + (size_t)p.nstages * p.U * tstride;                 // [2][nbuild][PP_A]
+    ColDesc* s_cols = (ColDesc*)(ctp + (size_t)2 * p.nbuild * PP_A);         // [nbuild]
     double* scratch = (double*)(s_cols + p.nbuild);                          // [ntasks][ksplit - 1][TASK_PAIRS * 2][32]
     load_cols_to_smem(s_cols, p.cols, p.nbuild, tstride * 8, tid, nthreads);
-    if (tid == 0) mbar_init(&s_bar, 1);
+    if (tid == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
-    const unsigned ct = smem_addr(ctp), tile_a = smem_addr(tile), cols_a = smem_addr(s_cols);
+    const unsigned ct0 = smem_addr(ctp), ctb = (unsigned)(p.nbuild * PP_A * 8), cols_a = smem_addr(s_cols);
 
-    // ---- this warp's task
-    const int ntw = p.ntasks * p.ksplit;
-    const bool worker = warp < ntw;
-    const int task = worker ? warp / p.ksplit : 0, kpart = worker ? warp % p.ksplit : 0;
-    const TaskDesc td = p.tasks[task];
-    unsigned a_off[TASK_A], b_off[TASK_B];
-    const unsigned ct_base = ct + (unsigned)(((lane >> 2) * PP_A + (lane & 3)) * 8);
-#pragma unroll
-    for (int i = 0; i < TASK_A; ++i) a_off[i] = ct_base + (unsigned)(td.ablk[i] * 8 * PP_A * 8);
-#pragma unroll
-    for (int j = 0; j < TASK_B; ++j) b_off[j] = ct_base + (unsigned)(td.bblk[j] * 8 * PP_A * 8);
-    const unsigned w_off = ct + (unsigned)((p.wcol * PP_A + (lane & 3)) * 8);
-    bool on[TASK_PAIRS];
-#pragma unroll
-    for (int m = 0; m < TASK_PAIRS; ++m) on[m] = worker && ((td.mask >> m) & 1);
-    const int* fmap = p.flushmap + ((size_t)task * TASK_PAIRS * 32 + lane) * 2;
-
-    unsigned phase = 0;
-    for (int ui = blockIdx.x; ui < p.g.n_units; ui += gridDim.x) {
-        const UnitDesc u = p.g.units[ui];
-        const int wb = u.b_hi - u.b_lo;
-        const int nrows = (u.a_hi - u.a_lo) * wb;
-        const int shift = u.col_lo & 1;             // the tile starts on the even column at or before col_lo
-        // ---- stage the token tile of the unit (everyone finished reading the previous one: chunk barriers below)
-        if (p.use_tma) {
-            if (tid == 0) {
-                fence_proxy_async();
-                mbar_expect_tx(&s_bar, (unsigned)(p.U * p.box_a * p.box_b * p.box_c * 8));
-                for (int us = 0; us < p.U; ++us) {
-                    double* dst = tile + (size_t)us * tstride;
-                    if (p.g.ndim == 3) tma_load_tile(dst, &p.tmap[us], 3, u.col_lo - shift, u.b_lo, u.a_lo, &s_bar);
-                    else if (p.g.ndim == 2) tma_load_tile(dst, &p.tmap[us], 2, u.col_lo - shift, u.b_lo, 0, &s_bar);
-                    else tma_load_tile(dst, &p.tmap[us], 1, u.col_lo - shift, 0, 0, &s_bar);
+    if (warp >= ncons) {
+        // =========================== producers ===========================
+        const int pw_ = warp - ncons, ptid = tid - ncons * 32, pthreads = nprod * 32;
+        unsigned phase[2] = {0, 0};
+        int it = 0, chunk = 0;
+        auto issue = [&](int ui, int st) {
+            const UnitDesc u = p.g.units[ui];
+            double* tile = tiles + (size_t)st * p.U * tstride;
+            const int shift = u.col_lo & 1;
+            if (p.use_tma) {
+                if (ptid == 0) {
+                    fence_proxy_async();
+                    mbar_expect_tx(&s_bar[st], (unsigned)(p.U * p.box_a * p.box_b * p.box_c * 8));
+                    for (int us = 0; us < p.U; ++us) {
+                        double* dst = tile + (size_t)us * tstride;
+                        if (p.g.ndim == 3) tma_load_tile(dst, &p.tmap[us], 3, u.col_lo - shift, u.b_lo, u.a_lo, &s_bar[st]);
+                        else if (p.g.ndim == 2) tma_load_tile(dst, &p.tmap[us], 2, u.col_lo - shift, u.b_lo, 0, &s_bar[st]);
+                        else tma_load_tile(dst, &p.tmap[us], 1, u.col_lo - shift, 0, 0, &s_bar[st]);
+                    }
+                }
+            } else {
+                const int wb = u.b_hi - u.b_lo, nrows = (u.a_hi - u.a_lo) * wb;
+                const int total = p.U * nrows * u.ncols;
+                for (int q = ptid; q < total; q += pthreads) {
+                    const int cc = q % u.ncols, rr = q / u.ncols;
+                    const int us = rr / nrows, row = rr - us * nrows;
+                    const int ra = row / wb, rb = row - ra * wb;
+                    const long long off = (long long)(u.a_lo + ra) * p.g.strideA + (long long)(u.b_lo + rb) * p.g.strideB + u.col_lo + cc;
+                    tile[(size_t)us * tstride + (ra * p.box_b + rb) * p.box_c + shift + cc] = __ldg(p.tok[us] + off);
                 }
             }
-            mbar_wait(&s_bar, phase);
-            phase ^= 1;
-        } else {
-            const int total = p.U * nrows * u.ncols;
-            for (int q = tid; q < total; q += nthreads) {
-                const int cc = q % u.ncols, rr = q / u.ncols;
-                const int us = rr / nrows, row = rr - us * nrows;
-                const int ra = row / wb, rb = row - ra * wb;
-                const long long off = (long long)(u.a_lo + ra) * p.g.strideA + (long long)(u.b_lo + rb) * p.g.strideB + u.col_lo + cc;
-                tile[(size_t)us * tstride + (ra * p.box_b + rb) * p.box_c + shift + cc] = __ldg(p.tok[us] + off);
+        };
+        if (p.nstages == 2 && (int)blockIdx.x < p.g.n_units) issue(blockIdx.x, 0);
+        for (int ui = blockIdx.x; ui < p.g.n_units; ui += gridDim.x, ++it) {
+            const UnitDesc u = p.g.units[ui];
+            const int st = (p.nstages == 2) ? (it & 1) : 0;
+            if (p.nstages == 2) {
+                // the other stage was last read while building the previous unit: every producer is past that
+                bar_sync(BAR_CONS + 1, pthreads);
+                if (ui + (int)gridDim.x < p.g.n_units) issue(ui + gridDim.x, st ^ 1);
+            } else {
+                bar_sync(BAR_CONS + 1, pthreads);
+                issue(ui, 0);
             }
-            __syncthreads();
+            if (p.use_tma) { mbar_wait(&s_bar[st], phase[st]); phase[st] ^= 1; }
+            else bar_sync(BAR_CONS + 1, pthreads);
+            // the tile address is re-defined by a volatile statement AFTER the wait: the (non-volatile, freely scheduled)
+            // tile loads of build_columns depend on it and so cannot move above the arrival of the data
+            unsigned tile_a = smem_addr(tiles + (size_t)st * p.U * tstride);
+            asm volatile("mov.u32 %0, %0;" : "+r"(tile_a) :: "memory");
+            const int wb = u.b_hi - u.b_lo;
+            const int nrows = (u.a_hi - u.a_lo) * wb;
+            const int shift = u.col_lo & 1;
+            for (int q = 0; q < u.npieces; ++q) {
+                const int ps = p.g.piece_start[u.piece_lo + q];
+                const int pw = p.g.piece_start[u.piece_lo + q + 1] - ps;
+                const int c_lo = ps - u.col_lo + shift;
+                const int npts = nrows * pw;
+                for (int c0 = 0; c0 < npts; c0 += PT_A, ++chunk) {
+                    const int bf = chunk & 1;
+                    int toffb[PT_A / 32];
+                    bool valid[PT_A / 32];
+#pragma unroll
+                    for (int k = 0; k < PT_A / 32; ++k) {
+                        const int pi = c0 + lane + 32 * k;
+                        valid[k] = pi < npts;
+                        const int r = pi / pw;
+                        const int ra = r / wb;
+                        toffb[k] = valid[k] ? (((ra * p.box_b + (r - ra * wb)) * p.box_c + c_lo + (pi - r * pw)) * 8) : 0;
+                    }
+                    bar_sync(BAR_EMPTY + bf, nthreads);                  // consumers are done with this buffer
+                    build_columns<PT_A / 32>(ct0 + bf * ctb, PP_A * 8, cols_a, p.nbuild, p.gfac, tile_a, tstride * 8, toffb, valid,
+                                             pw_, nprod, lane, chunk);
+                    __threadfence_block();
+                    bar_arrive(BAR_FULL + bf, nthreads);
+                }
+            }
         }
+        return;
+    }
 
+    // =========================== consumers ===========================
+    const int task = warp / p.ksplit, kpart = warp % p.ksplit;
+    const TaskDesc td = p.tasks[task];
+    unsigned a_off[TASK_A], b_off[TASK_B];
+    const unsigned frag = (unsigned)(((lane >> 2) * PP_A + (lane & 3)) * 8);
+#pragma unroll
+    for (int i = 0; i < TASK_A; ++i) a_off[i] = frag + (unsigned)(td.ablk[i] * 8 * PP_A * 8);
+#pragma unroll
+    for (int j = 0; j < TASK_B; ++j) b_off[j] = frag + (unsigned)(td.bblk[j] * 8 * PP_A * 8);
+    const unsigned w_off = (unsigned)((p.wcol * PP_A + (lane & 3)) * 8);
+    bool on[TASK_PAIRS];
+#pragma unroll
+    for (int m = 0; m < TASK_PAIRS; ++m) on[m] = (td.mask >> m) & 1;
+    const int* fmap = p.flushmap + ((size_t)task * TASK_PAIRS * 32 + lane) * 2;
+    const int cthreads = ncons * 32;
+    bar_arrive(BAR_EMPTY + 0, nthreads);                                  // both buffers start empty
+    bar_arrive(BAR_EMPTY + 1, nthreads);
+    int chunk = 0;
+    for (int ui = blockIdx.x; ui < p.g.n_units; ui += gridDim.x) {
+        const UnitDesc u = p.g.units[ui];
+        const int nrows = (u.a_hi - u.a_lo) * (u.b_hi - u.b_lo);
         for (int q = 0; q < u.npieces; ++q) {
-            const int ps = p.g.piece_start[u.piece_lo + q];
-            const int pw = p.g.piece_start[u.piece_lo + q + 1] - ps;
-            const int c_lo = ps - u.col_lo + shift;
+            const int pw = p.g.piece_start[u.piece_lo + q + 1] - p.g.piece_start[u.piece_lo + q];
             const int npts = nrows * pw;
             double acc[TASK_PAIRS][2];
 #pragma unroll
             for (int m = 0; m < TASK_PAIRS; ++m) { acc[m][0] = 0.0; acc[m][1] = 0.0; }
-            for (int c0 = 0; c0 < npts; c0 += PT_A) {
-                int toffb[PT_A / 32];
-                bool valid[PT_A / 32];
-#pragma unroll
-                for (int k = 0; k < PT_A / 32; ++k) {
-                    const int pi = c0 + lane + 32 * k;
-                    valid[k] = pi < npts;
-                    const int r = pi / pw;
-                    const int ra = r / wb;
-                    toffb[k] = valid[k] ? (((ra * p.box_b + (r - ra * wb)) * p.box_c + c_lo + (pi - r * pw)) * 8) : 0;
-                }
-                build_columns<PT_A / 32>(ct, PP_A * 8, cols_a, p.nbuild, p.gfac, tile_a, tstride * 8, toffb, valid, warp, nwarps, lane);
-                __syncthreads();
-                if (worker) {
-                    const int nks = (min(PT_A, npts - c0) + 3) >> 2;
-                    for (int s = kpart; s < nks; s += p.ksplit) {
-                        double a[TASK_A], b[TASK_B];
-#pragma unroll
-                        for (int i = 0; i < TASK_A; ++i) a[i] = lds_f64(a_off[i] + s * 32);
-#pragma unroll
-                        for (int j = 0; j < TASK_B; ++j) b[j] = lds_f64(b_off[j] + s * 32);
-                        if (WEIGHTED) {
-                            const double w = lds_f64(w_off + s * 32);
-#pragma unroll
-                            for (int j = 0; j < TASK_B; ++j) b[j] *= w;
-                        }
-#pragma unroll
-                        for (int i = 0; i < TASK_A; ++i)
-#pragma unroll
-                            for (int j = 0; j < TASK_B; ++j)
-                                if (on[i * TASK_B + j]) dmma884(acc[i * TASK_B + j][0], acc[i * TASK_B + j][1], a[i], b[j]);
-                    }
-                }
-                __syncthreads();
+            for (int c0 = 0; c0 < npts; c0 += PT_A, ++chunk) {
+                const int bf = chunk & 1;
+                const unsigned ct = ct0 + bf * ctb;
+                bar_sync(BAR_FULL + bf, nthreads);                        // the producers have built this buffer
+                const int nks = (min(PT_A, npts - c0) + 3) >> 2;
+                gram_ksteps_dispatch<WEIGHTED>(td.mask, acc, ct, a_off, b_off, w_off, kpart, nks, p.ksplit);
+                bar_arrive(BAR_EMPTY + bf, nthreads);
             }
             // ---- flush the run
             double* out = p.cells + ((long long)u.cell * p.g.npieces + u.piece_lo + q) * p.n_ent;
             if (p.ksplit > 1) {
-                if (worker && kpart > 0) {
+                if (kpart > 0) {
                     double* sc = scratch + ((size_t)(task * (p.ksplit - 1) + kpart - 1) * TASK_PAIRS * 2) * 32 + lane;
 #pragma unroll
                     for (int m = 0; m < TASK_PAIRS; ++m) { sc[(2 * m) * 32] = acc[m][0]; sc[(2 * m + 1) * 32] = acc[m][1]; }
                 }
-                __syncthreads();
-                if (worker && kpart == 0) {
+                bar_sync(BAR_CONS, cthreads);
+                if (kpart == 0) {
                     for (int k = 1; k < p.ksplit; ++k) {
                         const double* sc = scratch + ((size_t)(task * (p.ksplit - 1) + k - 1) * TASK_PAIRS * 2) * 32 + lane;
 #pragma unroll
@@ -479,7 +559,7 @@ __global__ void __launch_bounds__(GRAM_MAX_WARPS * 32, 2) gram_dmma_kernel(const
                     }
                 }
             }
-            if (worker && kpart == 0) {
+            if (kpart == 0) {
 #pragma unroll
                 for (int m = 0; m < TASK_PAIRS; ++m) {
                     if (!on[m]) continue;
@@ -488,7 +568,7 @@ __global__ void __launch_bounds__(GRAM_MAX_WARPS * 32, 2) gram_dmma_kernel(const
                     if (e1 >= 0) out[e1] = acc[m][1];
                 }
             }
-            if (p.ksplit > 1) __syncthreads();      // scratch is reused by the next run
+            if (p.ksplit > 1) bar_sync(BAR_CONS, cthreads);               // scratch is reused by the next run
         }
     }
 }
@@ -933,6 +1013,107 @@ __global__ void residual_prog_kernel(ResidProgParams p) {
     p.jobs[s] = j;
 }
 
+// Pass B walks the evals of a launch group sorted by (target column, first surviving column), so that consecutive
+// evals of an octet reuse the registers that hold those two columns, and reads their descriptors from a COMPACT
+// table (32-byte headers in that order + CSR lists of (column, weight) entries) small enough to sit in shared memory.
+// The surviving sets only exist after the solve, so ordering and packing run on the device: one CTA, bitonic sort of
+// 64-bit keys (column, column, slot), then a prefix sum of the entry counts.  More than SORT_MAX evals: slot order.
+#define SORT_MAX 8192
+struct EvalHdr {             // 32 bytes
+    int tcol;                // byte offset of the target column's row in the column tile
+    int nnz;                 // surviving features
+    int off;                 // first entry in the CSR arrays
+    int slot;                // sum slot (-1: padding)
+    double b1, delta;
+};
+
+struct ResidPackParams {
+    const EvalJob* jobs;     // [n_slots] in slot order
+    const int* job_col;      // [n_slots][TMAX]
+    const double* job_w;     // [n_slots][TMAX]
+    EvalHdr* hdr;            // [n_slots rounded up to OCT] in walking order
+    int* ent_col;            // [sum nnz]
+    double* ent_w;           // [sum nnz]
+    int* meta;               // [0] = sum nnz
+    int n_slots;
+};
+
+__global__ void __launch_bounds__(1024) residual_pack_kernel(ResidPackParams p) {
+    extern __shared__ unsigned long long s_key[];          // n2 keys, then n2 ints (scan)
+    const int n_pad = (p.n_slots + OCT - 1) / OCT * OCT;
+    int n2 = 1;
+    while (n2 < p.n_slots) n2 <<= 1;
+    if (n2 > SORT_MAX) {                                    // too many evals for the shared-memory sort: slot order, serial scan
+        if (threadIdx.x == 0) {
+            int off = 0;
+            for (int q = 0; q < n_pad; ++q) {
+                EvalHdr h;
+                h.tcol = 0; h.nnz = 0; h.off = off; h.slot = -1; h.b1 = 0.0; h.delta = 0.0;
+                if (q < p.n_slots) {
+                    const EvalJob j = p.jobs[q];
+                    h.tcol = j.tcol; h.nnz = j.nnz; h.slot = q; h.b1 = j.b1; h.delta = j.delta;
+                    for (int z = 0; z < j.nnz; ++z) { p.ent_col[off + z] = p.job_col[(long long)q * TMAX + z]; p.ent_w[off + z] = p.job_w[(long long)q * TMAX + z]; }
+                    off += j.nnz;
+                }
+                p.hdr[q] = h;
+            }
+            p.meta[0] = off;
+        }
+        return;
+    }
+    int* s_scan = (int*)(s_key + n2);
+    for (int q = threadIdx.x; q < n2; q += blockDim.x) {
+        unsigned long long k = ~0ull;
+        if (q < p.n_slots) {
+            const EvalJob j = p.jobs[q];
+            const unsigned long long c0 = j.nnz > 0 ? (unsigned long long)(p.job_col[(long long)q * TMAX] / (PP_B * 8)) : 0xffffull;
+            k = ((unsigned long long)(j.tcol / (PP_B * 8)) << 44) | (c0 << 24) | (unsigned long long)q;
+        }
+        s_key[q] = k;
+    }
+    __syncthreads();
+    for (int k = 2; k <= n2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int q = threadIdx.x; q < n2; q += blockDim.x) {
+                const int x = q ^ j;
+                if (x > q) {
+                    const unsigned long long a = s_key[q], b = s_key[x];
+                    const bool up = (q & k) == 0;
+                    if ((a > b) == up) { s_key[q] = b; s_key[x] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    // inclusive scan of the entry counts in walking order (Hillis-Steele, n2 <= 8192)
+    for (int q = threadIdx.x; q < n2; q += blockDim.x)
+        s_scan[q] = q < p.n_slots ? p.jobs[(int)(s_key[q] & 0xffffffull)].nnz : 0;
+    __syncthreads();
+    for (int d = 1; d < n2; d <<= 1) {
+        int add[SORT_MAX / 1024];
+        int m = 0;
+        for (int q = threadIdx.x; q < n2; q += blockDim.x) add[m++] = q >= d ? s_scan[q - d] : 0;
+        __syncthreads();
+        m = 0;
+        for (int q = threadIdx.x; q < n2; q += blockDim.x) s_scan[q] += add[m++];
+        __syncthreads();
+    }
+    for (int q = threadIdx.x; q < n_pad; q += blockDim.x) {
+        EvalHdr h;
+        h.tcol = 0; h.nnz = 0; h.off = 0; h.slot = -1; h.b1 = 0.0; h.delta = 0.0;
+        if (q < p.n_slots) {
+            const int slot = (int)(s_key[q] & 0xffffffull);
+            const EvalJob j = p.jobs[slot];
+            h.tcol = j.tcol; h.nnz = j.nnz; h.off = s_scan[q] - j.nnz; h.slot = slot; h.b1 = j.b1; h.delta = j.delta;
+            for (int z = 0; z < j.nnz; ++z) {
+                p.ent_col[h.off + z] = p.job_col[(long long)slot * TMAX + z];
+                p.ent_w[h.off + z] = p.job_w[(long long)slot * TMAX + z];
+            }
+        }
+        p.hdr[q] = h;
+    }
+    if (threadIdx.x == 0) p.meta[0] = p.n_slots > 0 ? s_scan[p.n_slots - 1] : 0;
+}
+
 struct ResidParams {
     long long N;
     int U;
@@ -940,9 +1121,11 @@ struct ResidParams {
     const ColDesc* cols;
     const FactorDesc* gfac;
     int nbuild;              // columns of the tile (cp)
-    const EvalJob* jobs;
-    const int* job_col;
-    const double* job_w;
+    const EvalHdr* hdr;      // [n_slots rounded up to OCT] in walking order (residual_pack_kernel)
+    const int* ent_col;      // CSR entries: byte offsets of the surviving columns' rows in the column tile
+    const double* ent_w;
+    const int* meta;         // [0] = number of entries
+    int desc_smem;           // bytes of shared memory available for a copy of the descriptors (0: read them from global)
     int n_slots;             // evals of the group = sum slots
     const int* tcols;        // distinct target columns
     int n_tcols;
@@ -1016,6 +1199,23 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
     const int nsum = 2 * p.n_slots + p.n_tcols;
     load_cols_to_smem(s_cols, p.cols, p.nbuild, PT_B * 8, tid, nthreads);
     for (int q = tid; q < nsum; q += nthreads) s_sum[q] = 0.0;
+    // descriptors of the evals: a shared-memory copy when it fits (generic pointers: the loops below do not care)
+    const int n_oct = (p.n_slots + OCT - 1) / OCT;
+    const EvalHdr* hdr = p.hdr;
+    const int* ent_col = p.ent_col;
+    const double* ent_w = p.ent_w;
+    {
+        const int n_ent = p.meta[0];
+        const size_t need = sizeof(EvalHdr) * (size_t)n_oct * OCT + (sizeof(double) + sizeof(int)) * (size_t)n_ent + 16;
+        if (need <= (size_t)p.desc_smem) {
+            EvalHdr* sh = (EvalHdr*)(s_sum + ((nsum + 1) & ~1));
+            double* sw = (double*)(sh + (size_t)n_oct * OCT);
+            int* sc = (int*)(sw + n_ent);
+            for (int q = tid; q < n_oct * OCT * 2; q += nthreads) ((double2*)sh)[q] = ((const double2*)p.hdr)[q];
+            for (int q = tid; q < n_ent; q += nthreads) { sw[q] = p.ent_w[q]; sc[q] = p.ent_col[q]; }
+            hdr = sh; ent_col = sc; ent_w = sw;
+        }
+    }
     if (tid == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
@@ -1025,7 +1225,6 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
     unsigned phase[2] = {0, 0};
     int it = 0;
     if (p.nstages == 2 && (long long)blockIdx.x < p.n_chunks) resid_stage_issue(p, blockIdx.x, tiles, &s_bar[0], tid, nthreads);
-    const int n_oct = (p.n_slots + OCT - 1) / OCT;
     const int njobs_all = n_oct + p.n_tcols;
     for (long long ci = blockIdx.x; ci < p.n_chunks; ci += gridDim.x, ++it) {
         const int st = (p.nstages == 2) ? (it & 1) : 0;
@@ -1049,7 +1248,9 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
             bool valid[RES_NPL];
 #pragma unroll
             for (int k = 0; k < RES_NPL; ++k) { valid[k] = lane + 32 * k < npts; toffb[k] = valid[k] ? (lane + 32 * k) * 8 : 0; }
-            build_columns<RES_NPL>(ct, PP_B * 8, cols_a, p.nbuild, p.gfac, smem_addr(tile), PT_B * 8, toffb, valid, warp, nwarps, lane);
+            unsigned tile_a = smem_addr(tile);
+            asm volatile("mov.u32 %0, %0;" : "+r"(tile_a) :: "memory");     // defined after the wait: see gram_dmma_kernel
+            build_columns<RES_NPL>(ct, PP_B * 8, cols_a, p.nbuild, p.gfac, tile_a, PT_B * 8, toffb, valid, warp, nwarps, lane, (int)ci);
         }
         if (tid == 0) s_next = 0;
         __syncthreads();
@@ -1064,9 +1265,8 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
                 // ---------------- octet job: evals [8 jj, 8 jj + 8) of the list (padding evals: nnz 0, sums discarded)
                 // descriptors are fetched up front, spread over the lanes (lane v: header of eval v; lane z: entry z of
                 // each eval), and broadcast by shuffles inside the loops: no global load on the critical path
-                const EvalJob mine = p.jobs[(size_t)jj * OCT + (lane & 7)];
-                const int* jc = p.job_col + (size_t)jj * OCT * TMAX;
-                const double* jw = p.job_w + (size_t)jj * OCT * TMAX;
+                const EvalHdr mine = hdr[(size_t)jj * OCT + (lane & 7)];
+                const int my_slot = mine.slot;
                 const bool full = npts == PT_B;
                 double a1[OCT], a2[OCT];
                 int cur_t = -1, cur_c = -1;
@@ -1078,8 +1278,9 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
                     const int tco = __shfl_sync(0xffffffffu, mine.tcol, v);
                     const double b1 = __shfl_sync(0xffffffffu, mine.b1, v);
                     // entry z of the eval in lane z (one coalesced fetch), broadcast by shuffle when used
-                    const int e_col = (lane < nz) ? jc[v * TMAX + lane] : 0;
-                    const double e_w = (lane < nz) ? jw[v * TMAX + lane] : 0.0;
+                    const int eo = __shfl_sync(0xffffffffu, mine.off, v) + lane;
+                    const int e_col = (lane < nz) ? ent_col[eo] : 0;
+                    const double e_w = (lane < nz) ? ent_w[eo] : 0.0;
                     const int co0 = __shfl_sync(0xffffffffu, e_col, 0), co1 = __shfl_sync(0xffffffffu, e_col, 1);
                     const double w0 = __shfl_sync(0xffffffffu, e_w, 0), w1 = __shfl_sync(0xffffffffu, e_w, 1);
                     if (tco != cur_t) {
@@ -1130,12 +1331,12 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
                     a1[v] = s1; a2[v] = s2;
                 }
                 const int vi = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-                const int slot = jj * OCT + vi;
+                const int slot = __shfl_sync(0xffffffffu, my_slot, vi);
                 const double t1 = warp_sum8(a1, lane);
-                if ((lane & 3) == 0 && slot < p.n_slots) s_sum[slot] += t1;
+                if ((lane & 3) == 0 && slot >= 0) s_sum[slot] += t1;
                 if (L2) {
                     const double t2 = warp_sum8(a2, lane);
-                    if ((lane & 3) == 0 && slot < p.n_slots) s_sum[p.n_slots + slot] += t2;
+                    if ((lane & 3) == 0 && slot >= 0) s_sum[p.n_slots + slot] += t2;
                 }
             } else {
                 // ---------------- target job: sum|t| of one target column (padding points hold 0)
@@ -1542,6 +1743,10 @@ static void build_tasks(int nblk, const std::vector<char>& need /* [nblk * nblk]
         for (int q = 1; q < 4; ++q) if (load[q] < load[k]) k = q;
         bins[k].push_back(t); load[k] += t.pad0;
     }
+    // warp w sits on scheduler w % 4 and takes bins[w % 4][w / 4]: bins with more tasks first, so that the interleaved
+    // order has no holes
+    std::stable_sort(std::begin(bins), std::end(bins), [](const std::vector<TaskDesc>& a, const std::vector<TaskDesc>& b) {
+        return a.size() > b.size(); });
     std::vector<TaskDesc> out;
     for (size_t r = 0; out.size() < tasks.size(); ++r)
         for (int k = 0; k < 4; ++k) if (r < bins[k].size()) out.push_back(bins[k][r]);
@@ -1737,6 +1942,8 @@ int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx**
         for (const void* fn : gram) if (set_dyn_smem(fn, c->max_smem, &c->smem_gram)) { delete c; return 1; }
         for (const void* fn : resid) if (set_dyn_smem(fn, c->max_smem, &c->smem_resid)) { delete c; return 1; }
         for (const void* fn : solve) if (set_dyn_smem(fn, c->max_smem, &c->smem_solve)) { delete c; return 1; }
+        int unused = c->max_smem;
+        if (set_dyn_smem((const void*)residual_pack_kernel, c->max_smem, &unused)) { delete c; return 1; }
     }
     c->N = 1;
     for (int d = 0; d < ndim; ++d) {
@@ -2295,13 +2502,16 @@ static int launch_gram(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double*
     if (p.use_tma)
         for (int u = 0; u < p.U; ++u)
             if (make_token_map(c, p.tok[u], &p.tmap[u])) return 1;
-    const int nwarps = std::min(GRAM_MAX_WARPS, std::max(8, g.ntasks * g.ksplit));
+    const int ncons = g.ntasks * g.ksplit;
+    const int nwarps = ncons + std::min(GRAM_PROD_WARPS, GRAM_MAX_THREADS / 32 - ncons);
     const size_t tstride = ((size_t)p.box_a * p.box_b * p.box_c + 15) & ~(size_t)15;
-    const size_t smem = sizeof(double) * ((size_t)p.U * tstride + (size_t)p.nbuild * PP_A) + sizeof(ColDesc) * (size_t)p.nbuild +
+    const size_t tile_bytes = sizeof(double) * (size_t)p.U * tstride;
+    const size_t rest = sizeof(double) * 2 * (size_t)p.nbuild * PP_A + sizeof(ColDesc) * (size_t)p.nbuild +
                         (g.ksplit > 1 ? sizeof(double) * (size_t)g.ntasks * (g.ksplit - 1) * TASK_PAIRS * 2 * 32 : 0);
+    p.nstages = (2 * tile_bytes + rest <= (size_t)c->smem_gram) ? 2 : 1;
+    const size_t smem = p.nstages * tile_bytes + rest;
     if (smem > (size_t)c->smem_gram) return fail("pass A needs %zu bytes of shared memory (> %d)", smem, c->smem_gram);
-    const int per = (2 * (smem + 1024) <= (size_t)c->max_smem + 1024) ? 2 : 1;
-    const unsigned grid = (unsigned)std::min<long long>(c->geom.n_units, (long long)c->sm_count * per);
+    const unsigned grid = (unsigned)std::min<long long>(c->geom.n_units, (long long)c->sm_count);
     {
         KernelSpan ks(c, EPDE_KERNEL_GRAM);
         if (weighted) gram_dmma_kernel<true><<<grid, nwarps * 32, smem, c->stream>>>(p);
@@ -2407,7 +2617,9 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
         if (g.n_slots == 0) continue;
         const size_t n_pad = ((size_t)g.n_slots + OCT - 1) / OCT * OCT;
         const size_t o_col = align(sizeof(EvalJob) * n_pad), o_w = align(o_col + sizeof(int) * n_pad * TMAX),
-                     tot = align(o_w + sizeof(double) * n_pad * TMAX);
+                     o_hdr = align(o_w + sizeof(double) * n_pad * TMAX), o_ec = align(o_hdr + sizeof(EvalHdr) * n_pad),
+                     o_ew = align(o_ec + sizeof(int) * n_pad * TMAX), o_meta = align(o_ew + sizeof(double) * n_pad * TMAX),
+                     tot = align(o_meta + 64);
         if (c->d_jobs.ensure(tot)) return 1;
         char* jb = (char*)c->d_jobs.ptr;
         ResidProgParams pp;
@@ -2416,12 +2628,22 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
         pp.jobs = (EvalJob*)jb; pp.job_col = (int*)(jb + o_col); pp.job_w = (double*)(jb + o_w); pp.n_slots = g.n_slots;
         { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_prog_kernel<<<(unsigned)((n_pad + 63) / 64), 64, 0, c->stream>>>(pp); }
         CK(cudaGetLastError());
+        ResidPackParams sp;
+        sp.jobs = pp.jobs; sp.job_col = pp.job_col; sp.job_w = pp.job_w; sp.n_slots = g.n_slots;
+        sp.hdr = (EvalHdr*)(jb + o_hdr); sp.ent_col = (int*)(jb + o_ec); sp.ent_w = (double*)(jb + o_ew); sp.meta = (int*)(jb + o_meta);
+        {
+            int n2 = 1;
+            while (n2 < g.n_slots) n2 <<= 1;
+            KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
+            residual_pack_kernel<<<1, 1024, n2 <= SORT_MAX ? (sizeof(unsigned long long) + sizeof(int)) * n2 : 0, c->stream>>>(sp);
+        }
+        CK(cudaGetLastError());
         ResidParams p;
         memset(&p, 0, sizeof p);
         p.N = c->N; p.U = (int)g.token_ids.size();
         for (int u = 0; u < p.U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
         p.cols = g.d_cols; p.gfac = g.d_gfac; p.nbuild = g.cp;
-        p.jobs = pp.jobs; p.job_col = pp.job_col; p.job_w = pp.job_w;
+        p.hdr = sp.hdr; p.ent_col = sp.ent_col; p.ent_w = sp.ent_w; p.meta = sp.meta;
         p.n_slots = g.n_slots; p.tcols = g.d_tcols; p.n_tcols = g.n_tcols;
         p.n_chunks = (int)n_chunks; p.aligned = 1;
         const int nsum = 2 * g.n_slots + g.n_tcols;
@@ -2430,8 +2652,12 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
         const size_t tile_bytes = sizeof(double) * (size_t)p.U * PT_B;
         const size_t rest = sizeof(double) * ((size_t)g.cp * PP_B + nsum) + sizeof(ColDesc) * (size_t)g.cp;
         p.nstages = (2 * tile_bytes + rest <= (size_t)c->smem_resid) ? 2 : 1;
-        const size_t smem = p.nstages * tile_bytes + rest;
+        size_t smem = p.nstages * tile_bytes + rest + 16;
         if (smem > (size_t)c->smem_resid) return fail("pass B needs %zu bytes of shared memory (> %d)", smem, c->smem_resid);
+        // whatever is left holds a copy of the eval descriptors (headers + an entry per surviving coefficient: at most
+        // 32 + 12 * TMAX bytes per eval, typically ~50); the kernel falls back to global reads when they do not fit
+        p.desc_smem = (int)std::min<size_t>((size_t)c->smem_resid - smem, n_pad * (sizeof(EvalHdr) + 12 * (size_t)TMAX) + 64);
+        smem += (size_t)p.desc_smem;
         {
             KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
             if (b->want_l2) residual_cols_kernel<true><<<grid, RES_WARPS * 32, smem, c->stream>>>(p);
