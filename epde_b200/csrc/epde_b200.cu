@@ -1125,6 +1125,8 @@ struct ResidParams {
     const int* ent_col;      // CSR entries: byte offsets of the surviving columns' rows in the column tile
     const double* ent_w;
     const int* meta;         // [0] = number of entries
+    int wcol;                // weighted mode: row of the column tile that holds the sample weights g (L2Fitness multiplies
+                             // its residual by g, fitness.py:81-82), else -1
     int desc_smem;           // bytes of shared memory available for a copy of the descriptors (0: read them from global)
     int n_slots;             // evals of the group = sum slots
     const int* tcols;        // distinct target columns
@@ -1318,7 +1320,12 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
                     if (L2) {
                         const double dl = __shfl_sync(0xffffffffu, mine.delta, v);
 #pragma unroll
-                        for (int k = 0; k < RES_NPL; ++k) { const double r2 = r[k] + dl; r[k] = (full || lane + 32 * k < npts) ? r[k] : 0.0; s2 = (full || lane + 32 * k < npts) ? fma(r2, r2, s2) : s2; }
+                        for (int k = 0; k < RES_NPL; ++k) {
+                            double r2 = r[k] + dl;
+                            if (p.wcol >= 0) r2 *= lds_f64_e(cl + p.wcol * (PP_B * 8) + k * 256, jj);
+                            r[k] = (full || lane + 32 * k < npts) ? r[k] : 0.0;
+                            s2 = (full || lane + 32 * k < npts) ? fma(r2, r2, s2) : s2;
+                        }
 #pragma unroll
                         for (int k = 0; k < RES_NPL; ++k) s1 += fabs(r[k]);
                     } else if (full) {
@@ -2642,7 +2649,8 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
         memset(&p, 0, sizeof p);
         p.N = c->N; p.U = (int)g.token_ids.size();
         for (int u = 0; u < p.U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
-        p.cols = g.d_cols; p.gfac = g.d_gfac; p.nbuild = g.cp;
+        p.cols = g.d_cols; p.gfac = g.d_gfac; p.nbuild = g.cp; p.wcol = -1;
+        if (b->weighted && b->want_l2) { p.tok[p.U++] = c->weights; p.nbuild = g.cp + 1; p.wcol = g.cp; }
         p.hdr = sp.hdr; p.ent_col = sp.ent_col; p.ent_w = sp.ent_w; p.meta = sp.meta;
         p.n_slots = g.n_slots; p.tcols = g.d_tcols; p.n_tcols = g.n_tcols;
         p.n_chunks = (int)n_chunks; p.aligned = 1;
@@ -2650,7 +2658,7 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
         if (c->d_partial.ensure(sizeof(double) * (size_t)grid * nsum)) return 1;
         p.partial = (double*)c->d_partial.ptr;
         const size_t tile_bytes = sizeof(double) * (size_t)p.U * PT_B;
-        const size_t rest = sizeof(double) * ((size_t)g.cp * PP_B + nsum) + sizeof(ColDesc) * (size_t)g.cp;
+        const size_t rest = sizeof(double) * ((size_t)p.nbuild * PP_B + nsum + 2) + sizeof(ColDesc) * (size_t)p.nbuild;
         p.nstages = (2 * tile_bytes + rest <= (size_t)c->smem_resid) ? 2 : 1;
         size_t smem = p.nstages * tile_bytes + rest + 16;
         if (smem > (size_t)c->smem_resid) return fail("pass B needs %zu bytes of shared memory (> %d)", smem, c->smem_resid);

@@ -158,6 +158,8 @@ def test_golden_micro2_wide_and_weighted(ci):
     pred = X @ ref_coef + ref_b
     fit = np.abs(y - pred).sum() / np.abs(y).sum() if np.any(ref_coef != 0) else np.abs(y - y.mean()).sum() / np.abs(y).sum()
     assert_rel(res.fitness_l1[0], fit, 'L1 fitness', rtol=1e-6)
+    # L2Fitness multiplies its residual by g (fitness.py:81-82)
+    assert_rel(res.fitness_l2[0], np.linalg.norm((pred - y) * g), 'L2 fitness (weighted residual)', rtol=1e-6)
 
 
 def oracle_refs(tokens, shape, eqs, evals):
