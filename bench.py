@@ -429,11 +429,18 @@ def run_b200(args):
     seg = torch.zeros(batch.gram_size, dtype=torch.float64, device=dev)
     sums = torch.zeros(batch.residual_size, dtype=torch.float64, device=dev)
 
+    sol = torch.zeros(batch.solution_size(False), dtype=torch.float64, device=dev) if grid_sharded else None
+
     def device_step():
         batch.gram(seg.data_ptr())
         if grid_sharded:
             dist.all_reduce(seg)
-        batch.solve(seg.data_ptr())
+            # every rank solves 1 / world of the evals; the solution block is merged by a sum
+            batch.solve_part(seg.data_ptr(), rank, world, sol.data_ptr())
+            dist.all_reduce(sol)
+            batch.set_solution(sol.data_ptr())
+        else:
+            batch.solve(seg.data_ptr())
         batch.residual(sums.data_ptr())
         if grid_sharded:
             dist.all_reduce(sums)

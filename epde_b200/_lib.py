@@ -43,6 +43,9 @@ SIGNATURES = {
     'epde_batch_gram': (C.c_int, [vp, vp]),
     'epde_batch_solve': (C.c_int, [vp, vp]),
     'epde_batch_residual': (C.c_int, [vp, vp]),
+    'epde_batch_solution_size': (C.c_int, [vp, C.c_int, c_i64p]),
+    'epde_batch_solve_part': (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp]),
+    'epde_batch_set_solution': (C.c_int, [vp, vp, C.c_int]),
     'epde_batch_fetch': (C.c_int, [vp, vp] + _OUT),
     'epde_ctx_synchronize': (C.c_int, [vp]),
     'epde_fd_gradient': (C.c_int, [vp, vp, vp, C.c_int, c_i64p, C.c_int, c_f64p]),

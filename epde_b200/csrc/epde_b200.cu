@@ -578,13 +578,16 @@ __global__ void __launch_bounds__(GRAM_MAX_THREADS, 1) gram_dmma_kernel(const __
 // grid = (n_rows, ceil(n_ent / 128)); thread <-> pair entry, so a warp reads 256 contiguous bytes of every cell
 // record; four independent partial sums keep loads in flight.
 // ------------------------------------------------------------------------------------------
+#define MARG_SPLIT 8           // partial sums per segment row (more loads in flight; summed in split order afterwards)
 struct MargParams {
     Geom g;
     const double* cells;
+    double* part;            // [MARG_SPLIT][n_rows][n_ent]
     double* seg;             // [n_rows][n_ent]
     int n_ent;
 };
 
+// grid = (n_rows, ceil(n_ent / 128), MARG_SPLIT)
 __global__ void __launch_bounds__(128) marginal_kernel(MargParams p) {
     const int ent = blockIdx.y * 128 + threadIdx.x;
     if (ent >= p.n_ent) return;
@@ -592,6 +595,8 @@ __global__ void __launch_bounds__(128) marginal_kernel(MargParams p) {
     const int nb = m.b_hi - m.b_lo, np = m.p_hi - m.p_lo;
     const long long inner = (long long)nb * np;
     const long long total = (long long)(m.a_hi - m.a_lo) * inner;
+    const long long per = (total + MARG_SPLIT - 1) / MARG_SPLIT;
+    const long long lo = (long long)blockIdx.z * per, hi = min(total, lo + per);
     const double* C = p.cells + ent;
     auto at = [&](long long q) -> double {
         const int ia = (int)(q / inner);
@@ -601,13 +606,93 @@ __global__ void __launch_bounds__(128) marginal_kernel(MargParams p) {
         return __ldcs(C + cell * p.n_ent);
     };
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    long long q = 0;
-    for (; q + 3 < total; q += 4) {
+    long long q = lo;
+    for (; q + 3 < hi; q += 4) {
         const double v0 = at(q), v1 = at(q + 1), v2 = at(q + 2), v3 = at(q + 3);
         s0 += v0; s1 += v1; s2 += v2; s3 += v3;
     }
-    for (; q < total; ++q) s0 += at(q);
-    p.seg[(long long)m.row * p.n_ent + ent] = (s0 + s1) + (s2 + s3);
+    for (; q < hi; ++q) s0 += at(q);
+    p.part[((long long)blockIdx.z * p.g.n_rows + m.row) * p.n_ent + ent] = (s0 + s1) + (s2 + s3);
+}
+
+// grid = (n_rows, ceil(n_ent / 128))
+__global__ void __launch_bounds__(128) marginal_final_kernel(MargParams p) {
+    const int ent = blockIdx.y * 128 + threadIdx.x;
+    if (ent >= p.n_ent) return;
+    const int row = blockIdx.x;
+    double s = 0.0;
+#pragma unroll
+    for (int z = 0; z < MARG_SPLIT; ++z) s += p.part[((long long)z * p.g.n_rows + row) * p.n_ent + ent];
+    p.seg[(long long)row * p.n_ent + ent] = s;
+}
+
+// Grids with two leading slots (3-D): every cell belongs to one segment row of EACH axis, so the kernel above reads the
+// cell table three times.  Two steps read it once: step 1, one CTA per (slot-A cell index a, 128 entries), walks the
+// contiguous slab [a][all b][all pieces] and leaves  tot[a], byB[a][b], byP[a][piece]  (byP accumulates in shared
+// memory, one column per thread); step 2 sums those over the ranges of each segment row, in index order.
+struct MargSlabParams {
+    Geom g;
+    const double* cells;
+    double* part;            // [nA][1 + nB + npieces][n_ent]
+    double* seg;
+    int n_ent;
+};
+
+// grid = (nA, ceil(n_ent / 128)); dynamic shared memory: npieces * 128 doubles
+__global__ void __launch_bounds__(128) marginal_slab_kernel(MargSlabParams p) {
+    extern __shared__ double s_pp[];               // [npieces][128]
+    const int a = blockIdx.x, tid = threadIdx.x;
+    const int ent = blockIdx.y * 128 + tid;
+    const int nB = p.g.nB, np = p.g.npieces;
+    for (int q = 0; q < np; ++q) s_pp[q * 128 + tid] = 0.0;
+    if (ent >= p.n_ent) return;
+    const double* C = p.cells + (long long)a * nB * np * p.n_ent + ent;
+    double* out = p.part + (long long)a * (1 + nB + np) * p.n_ent + ent;
+    double tot = 0.0;
+    for (int b = 0; b < nB; ++b) {
+        const double* Cb = C + (long long)b * np * p.n_ent;
+        double v0 = 0.0, v1 = 0.0;
+        int q = 0;
+        for (; q + 3 < np; q += 4) {
+            const double x0 = __ldcs(Cb + (long long)q * p.n_ent), x1 = __ldcs(Cb + (long long)(q + 1) * p.n_ent),
+                         x2 = __ldcs(Cb + (long long)(q + 2) * p.n_ent), x3 = __ldcs(Cb + (long long)(q + 3) * p.n_ent);
+            s_pp[q * 128 + tid] += x0; s_pp[(q + 1) * 128 + tid] += x1; s_pp[(q + 2) * 128 + tid] += x2; s_pp[(q + 3) * 128 + tid] += x3;
+            v0 += x0 + x1; v1 += x2 + x3;
+        }
+        for (; q < np; ++q) { const double x = __ldcs(Cb + (long long)q * p.n_ent); s_pp[q * 128 + tid] += x; v0 += x; }
+        const double vb = v0 + v1;
+        out[(long long)(1 + b) * p.n_ent] = vb;
+        tot += vb;
+    }
+    out[0] = tot;
+    for (int q = 0; q < np; ++q) out[(long long)(1 + nB + q) * p.n_ent] = s_pp[q * 128 + tid];
+}
+
+// grid = (n_rows, ceil(n_ent / 128))
+__global__ void __launch_bounds__(128) marginal_rows_kernel(MargSlabParams p) {
+    const int ent = blockIdx.y * 128 + threadIdx.x;
+    if (ent >= p.n_ent) return;
+    const MargDesc m = p.g.marg[blockIdx.x];
+    const long long rowlen = (long long)(1 + p.g.nB + p.g.npieces) * p.n_ent;
+    const double* P = p.part + ent;
+    double s = 0.0;
+    if (m.kind == 0) {
+        for (int a = m.a_lo; a < m.a_hi; ++a) s += P[a * rowlen];
+    } else {
+        const int lo = (m.kind == 1) ? 1 + m.b_lo : 1 + p.g.nB + m.p_lo;
+        const int n = (m.kind == 1) ? m.b_hi - m.b_lo : m.p_hi - m.p_lo;
+        for (int q = 0; q < n; ++q) {
+            double t0 = 0.0, t1 = 0.0;
+            int a = 0;
+            for (; a + 1 < p.g.nA; a += 2) {
+                t0 += P[a * rowlen + (long long)(lo + q) * p.n_ent];
+                t1 += P[(a + 1) * rowlen + (long long)(lo + q) * p.n_ent];
+            }
+            if (a < p.g.nA) t0 += P[a * rowlen + (long long)(lo + q) * p.n_ent];
+            s += t0 + t1;
+        }
+    }
+    p.seg[(long long)m.row * p.n_ent + ent] = s;
 }
 
 // window row = direct sum of the segment rows of the window; row W = every point (all rows of axis 0).
@@ -688,9 +773,10 @@ struct SolveParams {
     double* stability;       // [n_eval]
     double* sw;              // [n_eval][W][KS]
     double* wterm;           // [n_eval][TMAX]   coefficient per TERM index (0 for target / inactive)
-    int* n_active;
-    int* all_zero;
-    int* iters;
+    double* n_active;        // counts are stored as doubles: the whole solution block is one float64 all-reduce under
+    double* all_zero;        // grid sharding (epde_batch_solve_part)
+    double* iters;
+    int part, nparts;        // this launch solves the evals at list positions part, part + nparts, ...
 };
 
 #define SOLVE_THREADS 128
@@ -714,7 +800,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
     extern __shared__ double s_sw[];           // [W][KS]
 
     const int tid = threadIdx.x;
-    const int ev = p.eval_list[blockIdx.x];
+    const int ev = p.eval_list[blockIdx.x * p.nparts + p.part];
     const int e = p.eval_eq[ev];
     const int tgt = p.eval_tgt[ev];
     const EqDesc& eq = p.eqs[e];
@@ -942,9 +1028,9 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
         for (int j = 0; j < F; ++j) p.wterm[(long long)ev * TMAX + feat_term(j)] = s_coef[j];
         p.intercept[ev] = s_b;
         p.intercept_l1[ev] = (nact == 0) ? Gt[tgt * KS + T] / Gt[T * KS + T] : s_b;
-        p.n_active[ev] = nact;
-        p.all_zero[ev] = (nact == 0);
-        p.iters[ev] = s_sweeps;
+        p.n_active[ev] = (double)nact;
+        p.all_zero[ev] = (nact == 0) ? 1.0 : 0.0;
+        p.iters[ev] = (double)s_sweeps;
         // stability = sum(cv[:-1]) / ndim over the columns of the cached weights (fitness.py:160-169)
         double st = 0.0;
         for (int a = 0; a < n - 1; ++a) st += s_cvraw[a];
@@ -1467,7 +1553,7 @@ struct epde_ctx {
     int box_a = 1, box_b = 1;    // leading extents of the token tile / TMA box (largest cell of slot A / slot B)
     int box_c = 32;              // its last-axis extent: tile_cols, or tile_cols + 2 when units may start on odd columns
     DevBuf d_geom;               // packed geometry tables
-    DevBuf d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given, d_jobs, d_fd, d_total;
+    DevBuf d_cells, d_seg, d_win, d_enc, d_out, d_partial, d_given, d_jobs, d_fd, d_total, d_marg;
     void* h_pinned = nullptr; size_t h_pinned_cap = 0;
     epde_batch* live = nullptr;
     long long launches = 0;
@@ -1705,8 +1791,10 @@ struct epde_batch {
     // outputs in ctx->d_out
     double* d_coef = nullptr; double* d_intercept = nullptr; double* d_stab = nullptr;
     double* d_sw = nullptr; double* d_wterm = nullptr; double* d_sums = nullptr; double* d_b1 = nullptr;
-    int* d_nact = nullptr; int* d_allzero = nullptr; int* d_iters = nullptr;
-    size_t out_bytes = 0;
+    double* d_nact = nullptr; double* d_allzero = nullptr; double* d_iters = nullptr;
+    size_t out_bytes = 0;      // solution block + residual sums: what epde_batch_fetch always copies
+    size_t sol_bytes = 0;      // solution block (everything the solve writes except the window weights)
+    size_t sw_bytes = 0;
     long long seg_doubles = 0, win_doubles = 0;
     int* d_mode = nullptr; double* d_given_w = nullptr; double* d_given_b = nullptr;
     bool solved = false;
@@ -1951,6 +2039,7 @@ int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx**
         for (const void* fn : solve) if (set_dyn_smem(fn, c->max_smem, &c->smem_solve)) { delete c; return 1; }
         int unused = c->max_smem;
         if (set_dyn_smem((const void*)residual_pack_kernel, c->max_smem, &unused)) { delete c; return 1; }
+        if (set_dyn_smem((const void*)marginal_slab_kernel, c->max_smem, &unused)) { delete c; return 1; }
     }
     c->N = 1;
     for (int d = 0; d < ndim; ++d) {
@@ -1972,7 +2061,7 @@ int epde_ctx_destroy(epde_ctx* c) {
     if (c->weights) cudaFree(c->weights);
     c->d_geom.release(); c->d_cells.release(); c->d_seg.release(); c->d_win.release(); c->d_enc.release();
     c->d_out.release(); c->d_partial.release(); c->d_given.release(); c->d_jobs.release(); c->d_fd.release();
-    c->d_total.release();
+    c->d_total.release(); c->d_marg.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto& sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto& ev : c->free_events) cudaEventDestroy(ev);
@@ -2378,16 +2467,18 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
     const size_t ne = (size_t)std::max(1, n_eval);
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align(o + bytes); return r; };
-    const size_t oc = take(ne * TMAX * 8), oi = take(ne * 8), ost = take(ne * 8), owt = take(ne * TMAX * 8), osu = take(ne * 3 * 8),
-                 ob1 = take(ne * 8), ona = take(ne * 4), oaz = take(ne * 4), oit = take(ne * 4);
-    const size_t small_bytes = o;
+    const size_t oc = take(ne * TMAX * 8), oi = take(ne * 8), ost = take(ne * 8), owt = take(ne * TMAX * 8), ob1 = take(ne * 8),
+                 ona = take(ne * 8), oaz = take(ne * 8), oit = take(ne * 8);
+    b->sol_bytes = o;
+    const size_t osu = take(ne * 3 * 8);
+    b->out_bytes = o;
     const size_t osw = take(ne * W * KS * 8);
-    b->out_bytes = small_bytes;
+    b->sw_bytes = o - osw;
     if (c->d_out.ensure(o)) { delete b; return 1; }
     char* od = (char*)c->d_out.ptr;
     b->d_coef = (double*)(od + oc); b->d_intercept = (double*)(od + oi); b->d_stab = (double*)(od + ost);
     b->d_sw = (double*)(od + osw); b->d_wterm = (double*)(od + owt); b->d_sums = (double*)(od + osu); b->d_b1 = (double*)(od + ob1);
-    b->d_nact = (int*)(od + ona); b->d_allzero = (int*)(od + oaz); b->d_iters = (int*)(od + oit);
+    b->d_nact = (double*)(od + ona); b->d_allzero = (double*)(od + oaz); b->d_iters = (double*)(od + oit);
     c->live = b;
     *out = b;
     return 0;
@@ -2557,15 +2648,32 @@ int epde_batch_gram(epde_batch* b, double* dev_seg) {
             CK(cudaGetLastError());
         }
         if (launch_gram(c, b, g, cells, b->weighted)) return 1;
-        MargParams mp;
-        mp.g = c->geom; mp.cells = cells; mp.seg = seg; mp.n_ent = g.n_ent;
-        { KernelSpan ks(c, EPDE_KERNEL_MARGINAL); marginal_kernel<<<dim3(c->geom.n_rows, ey), 128, 0, c->stream>>>(mp); }
+        const size_t slab_smem = sizeof(double) * (size_t)c->geom.npieces * 128;
+        if (c->ndim == 3 && c->geom.nA >= 4 && slab_smem <= 100 * 1024) {
+            MargSlabParams sp;
+            sp.g = c->geom; sp.cells = cells; sp.seg = seg; sp.n_ent = g.n_ent;
+            if (c->d_marg.ensure(sizeof(double) * (size_t)c->geom.nA * (1 + c->geom.nB + c->geom.npieces) * g.n_ent)) return 1;
+            sp.part = (double*)c->d_marg.ptr;
+            KernelSpan ks(c, EPDE_KERNEL_MARGINAL);
+            marginal_slab_kernel<<<dim3(c->geom.nA, ey), 128, slab_smem, c->stream>>>(sp);
+            marginal_rows_kernel<<<dim3(c->geom.n_rows, ey), 128, 0, c->stream>>>(sp);
+            c->launches++;
+        } else {
+            MargParams mp;
+            mp.g = c->geom; mp.cells = cells; mp.seg = seg; mp.n_ent = g.n_ent;
+            if (c->d_marg.ensure(sizeof(double) * (size_t)MARG_SPLIT * c->geom.n_rows * g.n_ent)) return 1;
+            mp.part = (double*)c->d_marg.ptr;
+            KernelSpan ks(c, EPDE_KERNEL_MARGINAL);
+            marginal_kernel<<<dim3(c->geom.n_rows, ey, MARG_SPLIT), 128, 0, c->stream>>>(mp);
+            marginal_final_kernel<<<dim3(c->geom.n_rows, ey), 128, 0, c->stream>>>(mp);
+            c->launches++;
+        }
         CK(cudaGetLastError());
     }
     return 0;
 }
 
-int epde_batch_solve(epde_batch* b, const double* dev_seg) {
+static int solve_impl(epde_batch* b, const double* dev_seg, int part, int nparts) {
     if (!b || !b->ctx) return fail("null batch");
     epde_ctx* c = b->ctx;
     CK(cudaSetDevice(c->device));
@@ -2587,23 +2695,62 @@ int epde_batch_solve(epde_batch* b, const double* dev_seg) {
         sp.mode = b->d_mode; sp.given_wterm = b->d_given_w; sp.given_b = b->d_given_b;
         sp.coef = b->d_coef; sp.intercept = b->d_intercept; sp.intercept_l1 = b->d_b1; sp.stability = b->d_stab; sp.sw = b->d_sw;
         sp.wterm = b->d_wterm; sp.n_active = b->d_nact; sp.all_zero = b->d_allzero; sp.iters = b->d_iters;
+        sp.part = part; sp.nparts = nparts;
+        auto mine = [&](size_t n) { return (unsigned)((n > (size_t)part) ? (n - part + nparts - 1) / nparts : 0); };
         const size_t smem = sizeof(double) * (size_t)c->geom.n_windows * KS;
-        if (!b->evals_gs8.empty()) {
+        if (mine(b->evals_gs8.size()) > 0) {
             sp.eval_list = b->d_lists + b->off_gs8;
-            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<8><<<(unsigned)b->evals_gs8.size(), SOLVE_THREADS, smem, c->stream>>>(sp); }
+            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<8><<<mine(b->evals_gs8.size()), SOLVE_THREADS, smem, c->stream>>>(sp); }
             CK(cudaGetLastError());
         }
-        if (!b->evals_gs16.empty()) {
+        if (mine(b->evals_gs16.size()) > 0) {
             sp.eval_list = b->d_lists + b->off_gs16;
-            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<16><<<(unsigned)b->evals_gs16.size(), SOLVE_THREADS, smem, c->stream>>>(sp); }
+            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<16><<<mine(b->evals_gs16.size()), SOLVE_THREADS, smem, c->stream>>>(sp); }
             CK(cudaGetLastError());
         }
-        if (!b->evals_gs32.empty()) {
+        if (mine(b->evals_gs32.size()) > 0) {
             sp.eval_list = b->d_lists + b->off_gs32;
-            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<32><<<(unsigned)b->evals_gs32.size(), SOLVE_THREADS, smem, c->stream>>>(sp); }
+            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<32><<<mine(b->evals_gs32.size()), SOLVE_THREADS, smem, c->stream>>>(sp); }
             CK(cudaGetLastError());
         }
     }
+    b->solved = true;
+    return 0;
+}
+
+int epde_batch_solve(epde_batch* b, const double* dev_seg) {
+    if (!b || !b->ctx) return fail("null batch");
+    return solve_impl(b, dev_seg, 0, 1);
+}
+
+int epde_batch_solution_size(epde_batch* b, int with_sw, int64_t* n) {
+    if (!b || !n) return fail("null argument");
+    *n = (int64_t)((b->sol_bytes + (with_sw ? b->sw_bytes : 0)) / sizeof(double));
+    return 0;
+}
+
+int epde_batch_solve_part(epde_batch* b, const double* dev_seg, int part, int nparts, int with_sw, double* dev_solution) {
+    if (!b || !b->ctx || !dev_solution) return fail("epde_batch_solve_part: null argument");
+    if (nparts < 1 || part < 0 || part >= nparts) return fail("epde_batch_solve_part: part %d of %d", part, nparts);
+    epde_ctx* c = b->ctx;
+    CK(cudaSetDevice(c->device));
+    // evals of the other parts contribute zeros to the sum that merges the parts
+    CK(cudaMemsetAsync(c->d_out.ptr, 0, b->sol_bytes, c->stream));
+    if (with_sw) CK(cudaMemsetAsync(b->d_sw, 0, b->sw_bytes, c->stream));
+    if (solve_impl(b, dev_seg, part, nparts)) return 1;
+    CK(cudaMemcpyAsync(dev_solution, c->d_out.ptr, b->sol_bytes, cudaMemcpyDeviceToDevice, c->stream));
+    if (with_sw)
+        CK(cudaMemcpyAsync((char*)dev_solution + b->sol_bytes, b->d_sw, b->sw_bytes, cudaMemcpyDeviceToDevice, c->stream));
+    return 0;
+}
+
+int epde_batch_set_solution(epde_batch* b, const double* dev_solution, int with_sw) {
+    if (!b || !b->ctx || !dev_solution) return fail("epde_batch_set_solution: null argument");
+    epde_ctx* c = b->ctx;
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(c->d_out.ptr, dev_solution, b->sol_bytes, cudaMemcpyDeviceToDevice, c->stream));
+    if (with_sw)
+        CK(cudaMemcpyAsync(b->d_sw, (const char*)dev_solution + b->sol_bytes, b->sw_bytes, cudaMemcpyDeviceToDevice, c->stream));
     b->solved = true;
     return 0;
 }
@@ -2708,9 +2855,12 @@ int epde_batch_fetch(epde_batch* b, const double* dev_sums, double* coef, double
     if (intercept) memcpy(intercept, hp(b->d_intercept), sizeof(double) * ne);
     if (stability) memcpy(stability, hp(b->d_stab), sizeof(double) * ne);
     if (sw_weights) memcpy(sw_weights, h + b->out_bytes, sw_bytes);
-    if (n_active) memcpy(n_active, hp(b->d_nact), sizeof(int) * ne);
-    if (all_zero) memcpy(all_zero, hp(b->d_allzero), sizeof(int) * ne);
-    if (iters) memcpy(iters, hp(b->d_iters), sizeof(int) * ne);
+    const double* hn = (const double*)hp(b->d_nact), *hz = (const double*)hp(b->d_allzero), *hi = (const double*)hp(b->d_iters);
+    for (int v = 0; v < ne; ++v) {
+        if (n_active) n_active[v] = (int32_t)hn[v];
+        if (all_zero) all_zero[v] = (int32_t)hz[v];
+        if (iters) iters[v] = (int32_t)hi[v];
+    }
     const double* sums = (const double*)hp(b->d_sums);
     for (int v = 0; v < ne; ++v) {
         if (fitness_l1) fitness_l1[v] = sums[3 * v] / sums[3 * v + 1];

@@ -320,6 +320,19 @@ class Batch:
     def solve(self, dev_seg=None):
         _lib.check(self._lib.epde_batch_solve(self._h, C.c_void_p(dev_seg) if dev_seg else None))
 
+    def solution_size(self, with_sw=False):
+        r = C.c_int64(0)
+        _lib.check(self._lib.epde_batch_solution_size(self._h, int(bool(with_sw)), C.byref(r)))
+        return int(r.value)
+
+    def solve_part(self, dev_seg, part, nparts, dev_solution, with_sw=False):
+        """solve 1 / nparts of the evals, zeros elsewhere; solution block -> dev_solution (to be sum-reduced over the ranks)"""
+        _lib.check(self._lib.epde_batch_solve_part(self._h, C.c_void_p(dev_seg) if dev_seg else None, int(part), int(nparts),
+                                                   int(bool(with_sw)), C.c_void_p(dev_solution)))
+
+    def set_solution(self, dev_solution, with_sw=False):
+        _lib.check(self._lib.epde_batch_set_solution(self._h, C.c_void_p(dev_solution), int(bool(with_sw))))
+
     def residual(self, dev_sums=None):
         _lib.check(self._lib.epde_batch_residual(self._h, C.c_void_p(dev_sums) if dev_sums else None))
 

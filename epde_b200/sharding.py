@@ -72,18 +72,24 @@ def grid_slab(shape, rank: int, world: int):
 # ------------------------------------------------------------------------------------------
 # grid-point sharding: the staged path with its two all-reduces
 # ------------------------------------------------------------------------------------------
-def evaluate_grid_sharded(engine, enc, seg, sums, group=None, want_sw=True, want_l2=True):
+def evaluate_grid_sharded(engine, enc, seg, sums, group=None, want_sw=True, want_l2=True, sol=None):
     """One evaluation of `enc` on an engine that holds a slab of the grid.
 
     seg, sums: float64 tensors of ``batch.gram_size`` / ``batch.residual_size`` elements on the
-    engine's device (scratch; reusable across calls).  Returns the BatchResult (identical on every
-    rank)."""
+    engine's device (scratch; reusable across calls); sol: optional scratch of ``batch.solution_size(want_sw)``
+    elements.  Returns the BatchResult (identical on every rank).
+
+    Collectives: all-reduce of the segment tables (pass A), all-reduce of the solution block (every rank solves
+    1 / world of the evals -- the window solves and the LASSO do not shrink with the slab, so solving all of them on
+    every rank would be the part of the step that does not scale), all-reduce of the residual sums (pass B)."""
     import torch.distributed as dist
     if seg.is_cuda and hasattr(engine, 'set_stream'):
         # the collectives order against torch's CURRENT stream: run the kernels on that stream too, otherwise the
         # all-reduce could start before pass A / pass B have finished (or the solve before the all-reduce)
         import torch
         engine.set_stream(torch.cuda.current_stream(seg.device).cuda_stream)
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
     with engine.batch(enc) as b:
         if seg.numel() < b.gram_size or sums.numel() < b.residual_size:
             raise ValueError(f'scratch too small: seg {seg.numel()} < {b.gram_size} or '
@@ -93,7 +99,16 @@ def evaluate_grid_sharded(engine, enc, seg, sums, group=None, want_sw=True, want
             b.set_norms(want_l2=False)
         b.gram(seg_v.data_ptr())
         dist.all_reduce(seg_v, op=dist.ReduceOp.SUM, group=group)
-        b.solve(seg_v.data_ptr())
+        if world > 1 and hasattr(b, 'solve_part'):
+            n_sol = b.solution_size(want_sw)
+            if sol is None or sol.numel() < n_sol:
+                sol = seg.new_empty(n_sol)
+            sol_v = sol[:n_sol]
+            b.solve_part(seg_v.data_ptr(), rank, world, sol_v.data_ptr(), with_sw=want_sw)
+            dist.all_reduce(sol_v, op=dist.ReduceOp.SUM, group=group)
+            b.set_solution(sol_v.data_ptr(), with_sw=want_sw)
+        else:
+            b.solve(seg_v.data_ptr())
         b.residual(sums_v.data_ptr())
         dist.all_reduce(sums_v, op=dist.ReduceOp.SUM, group=group)
         return b.fetch(sums_v.data_ptr(), want_sw=want_sw)

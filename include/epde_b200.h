@@ -162,6 +162,14 @@ int epde_batch_residual_size(epde_batch* b, int64_t* n_doubles);
 int epde_batch_gram(epde_batch* b, double* dev_seg);
 int epde_batch_solve(epde_batch* b, const double* dev_seg);
 int epde_batch_residual(epde_batch* b, double* dev_sums);
+/* Grid-sharded runs need not solve every eval on every rank: epde_batch_solve_part solves the evals at positions
+ * part, part + nparts, ... of the batch's solve lists and leaves zeros for the others, then copies the solution block
+ * (coefficients, intercepts, stability, ... : epde_batch_solution_size doubles; with_sw = 1 appends the sliding-window
+ * weights) to dev_solution.  The caller all-reduces (sum, float64) that buffer over the ranks and hands it back with
+ * epde_batch_set_solution before epde_batch_residual. */
+int epde_batch_solution_size(epde_batch* b, int with_sw, int64_t* n_doubles);
+int epde_batch_solve_part(epde_batch* b, const double* dev_seg, int part, int nparts, int with_sw, double* dev_solution);
+int epde_batch_set_solution(epde_batch* b, const double* dev_solution, int with_sw);
 int epde_batch_fetch(epde_batch* b, const double* dev_sums,
                      double* coef, double* intercept, double* fitness_l1, double* fitness_l2,
                      double* stability, double* sw_weights, int32_t* n_active,

@@ -413,9 +413,19 @@ def test_grid_sharding_single_gpu():
         segs.append(s)
     torch.cuda.synchronize()
     tot = segs[0] + segs[1]
+    # every shard solves half of the evals (epde_batch_solve_part); the solution blocks are merged by a sum, exactly
+    # what evaluate_grid_sharded does with NCCL
+    sols = []
     for r in range(2):
         segs[r].copy_(tot)
-        batches[r].solve(segs[r].data_ptr())
+        sol = torch.zeros(batches[r].solution_size(True), dtype=torch.float64, device='cuda')
+        batches[r].solve_part(segs[r].data_ptr(), r, 2, sol.data_ptr(), with_sw=True)
+        sols.append(sol)
+    torch.cuda.synchronize()
+    assert float((sols[0][:enc.n_eval * epde_b200.MAX_TERMS].abs() > 0).sum()) > 0
+    merged = sols[0] + sols[1]
+    for r in range(2):
+        batches[r].set_solution(merged.data_ptr(), with_sw=True)
         s = torch.zeros(batches[r].residual_size, dtype=torch.float64, device='cuda')
         batches[r].residual(s.data_ptr())
         sums.append(s)
@@ -426,8 +436,9 @@ def test_grid_sharding_single_gpu():
         b.close()
     for e in engines:
         e.close()
-    for k in ('coef', 'n_active', 'iters'):
+    for k in ('coef', 'n_active', 'iters', 'sw_weights'):
         assert np.array_equal(getattr(outs[0], k), getattr(outs[1], k)), k
+    assert outs[0].n_active.max() > 0 and outs[0].iters.max() > 0
     assert np.array_equal(outs[0].coef != 0, full.coef != 0)
     # the slabs sum their cells in another order than the whole grid: the contract tolerance (1e-6 relative)
     # applies, random equations of this population reach ~1e-8 through their conditioning
