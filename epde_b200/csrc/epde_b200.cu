@@ -2596,7 +2596,6 @@ static int launch_gram(epde_ctx* c, epde_batch* b, const LaunchGroup& g, double*
     p.cells = cells; p.n_ent = g.n_ent;
     p.box_a = c->box_a; p.box_b = c->box_b; p.box_c = c->box_c;
     p.use_tma = (c->geom.aligned16 && tensor_map_encoder() && c->box_a <= 256 && c->box_b <= 256) ? 1 : 0;
-    if (getenv("EPDE_DEBUG_NO_TMA")) p.use_tma = 0;   // DEBUG ONLY
     if (p.use_tma)
         for (int u = 0; u < p.U; ++u)
             if (make_token_map(c, p.tok[u], &p.tmap[u])) return 1;

@@ -148,28 +148,51 @@ def data_checksum(token, xp=np):
     return float(token[::4099].sum())
 
 
+def _term_pools(n_tokens, max_power):
+    """every product of 1-3 distinct tokens with powers 1..max_power, split into (admissible targets, others)."""
+    from itertools import combinations, product
+    adm, other = [], []
+    for nf in (1, 2, 3):
+        for toks in combinations(range(n_tokens), nf):
+            for pw in product(range(1, max_power + 1), repeat=nf):
+                term = [(int(t), float(q), 0, 0.0) for t, q in zip(toks, pw)]
+                (adm if sum(1 for f in term if f[0] != 0) == 1 else other).append(term)
+    return adm, other
+
+
 def make_population_distinct(n_tokens, pop, seed=0, t_range=(3, 7), max_power=3):
     """stress population with NO sharing: every term of every equation is distinct (products of 1-3 factors with
-    powers <= max_power), so the column dictionary de-duplicates nothing (report it beside the default)."""
+    powers <= max_power), so the column dictionary de-duplicates nothing (report it beside the default).
+
+    Terms are dealt without replacement from the enumerated pools (bounded work: no rejection loop).  Every equation
+    gets at least one admissible target; there are only 6 * max_power * (1 + max_power) of those for 7 tokens, so
+    max_power is raised until the pool holds one per equation (pop 128 with 7 tokens: powers up to 5), and the
+    targets left over after that go round the population up to three per equation."""
     rng = np.random.default_rng(seed)
-    seen, eqs = set(), []
-    while len(eqs) < pop:
-        T = int(rng.integers(t_range[0], t_range[1] + 1))
-        terms = []
-        while len(terms) < T:
-            nf = int(rng.integers(1, 4))
-            chosen = rng.choice(n_tokens, size=nf, replace=False)
-            term = [(int(c), float(rng.integers(1, max_power + 1)), 0, 0.0) for c in chosen]
-            key = frozenset(term)
-            if key in seen:
-                continue
-            seen.add(key)
-            terms.append(term)
-        if admissible_targets(terms):
-            eqs.append(terms)
-        else:
-            for t in terms:
-                seen.discard(frozenset(t))
+    adm, other = _term_pools(n_tokens, max_power)
+    while len(adm) < pop:
+        max_power += 1
+        if max_power > 8:
+            raise ValueError(f'no distinct population of {pop} equations over {n_tokens} tokens')
+        adm, other = _term_pools(n_tokens, max_power)
+    adm = [adm[i] for i in rng.permutation(len(adm))]
+    other = [other[i] for i in rng.permutation(len(other))]
+    T = rng.integers(t_range[0], t_range[1] + 1, size=pop)
+    n_adm = np.ones(pop, dtype=np.int64)
+    spare = len(adm) - pop
+    for _ in range(2):
+        for e in range(pop):
+            if spare > 0 and n_adm[e] < T[e] - 1:
+                n_adm[e] += 1
+                spare -= 1
+    if int(np.sum(T - n_adm)) > len(other):
+        raise ValueError(f'no distinct population of {pop} equations over {n_tokens} tokens')
+    eqs, ia, io = [], 0, 0
+    for e in range(pop):
+        terms = adm[ia:ia + n_adm[e]] + other[io:io + T[e] - n_adm[e]]
+        ia += int(n_adm[e])
+        io += int(T[e] - n_adm[e])
+        eqs.append([terms[i] for i in rng.permutation(len(terms))])
     return eqs
 
 
