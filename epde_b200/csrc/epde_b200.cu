@@ -102,7 +102,7 @@ static int fail(const char* fmt, ...) {
 // ------------------------------------------------------------------------------------------
 struct FactorDesc {          // 32 bytes; factors of the generic (non-fast) columns of a launch group
     int slot;                // token slot inside the launch group's tile
-    int ipow;                // integer power if power is 1, 2 or 3, else 0
+    int ipow;                // the power if it is an integer in 1..64 (multiplications, no pow()), else 0
     int kind;                // 0 pow, 1 sin, 2 cos, 3 inverse
     int pad;
     double power;
@@ -216,6 +216,14 @@ __device__ __forceinline__ double apply_factor(const FactorDesc& f, double x) {
     if (f.ipow == 2) return x * x;
     if (f.ipow == 3) return x * x * x;
     return pow(x, f.power);
+    if (f.ipow > 3) {                        // integer power by squaring (uniform per warp: a column is one warp's job)
+        double r = (f.ipow & 1) ? x : 1.0, sq = x;
+        for (int e = f.ipow >> 1; e; e >>= 1) {
+            sq *= sq;
+            if (e & 1) r *= sq;
+        }
+        return r;
+    }
 }
 
 // Phase 1 of both passes: the value of every column of the launch group's dictionary at the points of the
@@ -627,45 +635,53 @@ __global__ void __launch_bounds__(128) marginal_final_kernel(MargParams p) {
 }
 
 // Grids with two leading slots (3-D): every cell belongs to one segment row of EACH axis, so the kernel above reads the
-// cell table three times.  Two steps read it once: step 1, one CTA per (slot-A cell index a, 128 entries), walks the
-// contiguous slab [a][all b][all pieces] and leaves  tot[a], byB[a][b], byP[a][piece]  (byP accumulates in shared
-// memory, one column per thread); step 2 sums those over the ranges of each segment row, in index order.
+// cell table three times.  Two steps read it once: step 1, one CTA per (slot-A cell index a, 128 entries, chunk z of the
+// slot-B range), walks the contiguous slab [a][b in chunk z][all pieces] and leaves  tot[a][z], byB[a][b], byP[a][z][piece]
+// (byP accumulates in shared memory, one column per thread); step 2 sums those over the ranges of each segment row, in
+// index order.  The chunks exist to put enough CTAs (and loads) in flight when nA x entry blocks alone is a small grid.
+#define MARG_NBC 4
 struct MargSlabParams {
     Geom g;
     const double* cells;
-    double* part;            // [nA][1 + nB + npieces][n_ent]
+    double* part;            // [nA][MARG_NBC + nB + MARG_NBC * npieces][n_ent]
     double* seg;
     int n_ent;
 };
 
-// grid = (nA, ceil(n_ent / 128)); dynamic shared memory: npieces * 128 doubles
+// grid = (nA, ceil(n_ent / 128), MARG_NBC); dynamic shared memory: npieces * 128 doubles
 __global__ void __launch_bounds__(128) marginal_slab_kernel(MargSlabParams p) {
     extern __shared__ double s_pp[];               // [npieces][128]
-    const int a = blockIdx.x, tid = threadIdx.x;
+    const int a = blockIdx.x, tid = threadIdx.x, z = blockIdx.z;
     const int ent = blockIdx.y * 128 + tid;
     const int nB = p.g.nB, np = p.g.npieces;
     for (int q = 0; q < np; ++q) s_pp[q * 128 + tid] = 0.0;
     if (ent >= p.n_ent) return;
-    const double* C = p.cells + (long long)a * nB * np * p.n_ent + ent;
-    double* out = p.part + (long long)a * (1 + nB + np) * p.n_ent + ent;
+    const long long ne = p.n_ent;
+    const int per = (nB + MARG_NBC - 1) / MARG_NBC;
+    const int b_lo = z * per, b_hi = min(nB, b_lo + per);
+    const double* C = p.cells + (long long)a * nB * np * ne + ent;
+    double* out = p.part + (long long)a * (MARG_NBC + nB + MARG_NBC * np) * ne + ent;
     double tot = 0.0;
-    for (int b = 0; b < nB; ++b) {
-        const double* Cb = C + (long long)b * np * p.n_ent;
+    for (int b = b_lo; b < b_hi; ++b) {
+        const double* Cb = C + (long long)b * np * ne;
         double v0 = 0.0, v1 = 0.0;
         int q = 0;
-        for (; q + 3 < np; q += 4) {
-            const double x0 = __ldcs(Cb + (long long)q * p.n_ent), x1 = __ldcs(Cb + (long long)(q + 1) * p.n_ent),
-                         x2 = __ldcs(Cb + (long long)(q + 2) * p.n_ent), x3 = __ldcs(Cb + (long long)(q + 3) * p.n_ent);
-            s_pp[q * 128 + tid] += x0; s_pp[(q + 1) * 128 + tid] += x1; s_pp[(q + 2) * 128 + tid] += x2; s_pp[(q + 3) * 128 + tid] += x3;
-            v0 += x0 + x1; v1 += x2 + x3;
+        for (; q + 7 < np; q += 8) {
+            double x[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) x[k] = __ldcs(Cb + (long long)(q + k) * ne);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s_pp[(q + k) * 128 + tid] += x[k];
+            v0 += (x[0] + x[1]) + (x[2] + x[3]);
+            v1 += (x[4] + x[5]) + (x[6] + x[7]);
         }
-        for (; q < np; ++q) { const double x = __ldcs(Cb + (long long)q * p.n_ent); s_pp[q * 128 + tid] += x; v0 += x; }
+        for (; q < np; ++q) { const double x = __ldcs(Cb + (long long)q * ne); s_pp[q * 128 + tid] += x; v0 += x; }
         const double vb = v0 + v1;
-        out[(long long)(1 + b) * p.n_ent] = vb;
+        out[(long long)(MARG_NBC + b) * ne] = vb;
         tot += vb;
     }
-    out[0] = tot;
-    for (int q = 0; q < np; ++q) out[(long long)(1 + nB + q) * p.n_ent] = s_pp[q * 128 + tid];
+    out[(long long)z * ne] = tot;
+    for (int q = 0; q < np; ++q) out[(long long)(MARG_NBC + nB + z * np + q) * ne] = s_pp[q * 128 + tid];
 }
 
 // grid = (n_rows, ceil(n_ent / 128))
@@ -673,28 +689,44 @@ __global__ void __launch_bounds__(128) marginal_rows_kernel(MargSlabParams p) {
     const int ent = blockIdx.y * 128 + threadIdx.x;
     if (ent >= p.n_ent) return;
     const MargDesc m = p.g.marg[blockIdx.x];
-    const long long rowlen = (long long)(1 + p.g.nB + p.g.npieces) * p.n_ent;
+    const int nB = p.g.nB, np = p.g.npieces;
+    const long long ne = p.n_ent;
+    const long long rowlen = (long long)(MARG_NBC + nB + MARG_NBC * np) * ne;
     const double* P = p.part + ent;
     double s = 0.0;
     if (m.kind == 0) {
-        for (int a = m.a_lo; a < m.a_hi; ++a) s += P[a * rowlen];
-    } else {
-        const int lo = (m.kind == 1) ? 1 + m.b_lo : 1 + p.g.nB + m.p_lo;
-        const int n = (m.kind == 1) ? m.b_hi - m.b_lo : m.p_hi - m.p_lo;
-        for (int q = 0; q < n; ++q) {
+        for (int a = m.a_lo; a < m.a_hi; ++a) {
+            double t = 0.0;
+#pragma unroll
+            for (int z = 0; z < MARG_NBC; ++z) t += P[a * rowlen + z * ne];
+            s += t;
+        }
+    } else if (m.kind == 1) {
+        for (int b = m.b_lo; b < m.b_hi; ++b) {
             double t0 = 0.0, t1 = 0.0;
             int a = 0;
             for (; a + 1 < p.g.nA; a += 2) {
-                t0 += P[a * rowlen + (long long)(lo + q) * p.n_ent];
-                t1 += P[(a + 1) * rowlen + (long long)(lo + q) * p.n_ent];
+                t0 += P[a * rowlen + (long long)(MARG_NBC + b) * ne];
+                t1 += P[(a + 1) * rowlen + (long long)(MARG_NBC + b) * ne];
             }
-            if (a < p.g.nA) t0 += P[a * rowlen + (long long)(lo + q) * p.n_ent];
+            if (a < p.g.nA) t0 += P[a * rowlen + (long long)(MARG_NBC + b) * ne];
+            s += t0 + t1;
+        }
+    } else {
+        for (int q = m.p_lo; q < m.p_hi; ++q) {
+            double t0 = 0.0, t1 = 0.0;
+            for (int a = 0; a < p.g.nA; ++a) {
+                const double* Pa = P + a * rowlen + (long long)(MARG_NBC + nB + q) * ne;
+                t0 += Pa[0] + Pa[(long long)np * ne];
+                t1 += Pa[(long long)2 * np * ne] + Pa[(long long)3 * np * ne];
+            }
             s += t0 + t1;
         }
     }
     p.seg[(long long)m.row * p.n_ent + ent] = s;
 }
 
+static_assert(MARG_NBC == 4, "marginal_rows_kernel sums four slot-B chunks explicitly");
 // window row = direct sum of the segment rows of the window; row W = every point (all rows of axis 0).
 // grid = (W + 1, ceil(n_ent / 128))
 struct WindowParams {
@@ -2350,7 +2382,7 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
                     d.power = fac_power[f];
                     d.kind = fac_kind ? fac_kind[f] : 0;
                     d.param = fac_param ? fac_param[f] : 0.0;
-                    d.ipow = (d.power == 1.0) ? 1 : (d.power == 2.0) ? 2 : (d.power == 3.0) ? 3 : 0;
+                    d.ipow = (d.power >= 1.0 && d.power <= 64.0 && d.power == (double)(int)d.power) ? (int)d.power : 0;
                     gfac.push_back(d);
                 }
             }
@@ -2651,10 +2683,11 @@ int epde_batch_gram(epde_batch* b, double* dev_seg) {
         if (c->ndim == 3 && c->geom.nA >= 4 && slab_smem <= 100 * 1024) {
             MargSlabParams sp;
             sp.g = c->geom; sp.cells = cells; sp.seg = seg; sp.n_ent = g.n_ent;
-            if (c->d_marg.ensure(sizeof(double) * (size_t)c->geom.nA * (1 + c->geom.nB + c->geom.npieces) * g.n_ent)) return 1;
+            if (c->d_marg.ensure(sizeof(double) * (size_t)c->geom.nA * (MARG_NBC + c->geom.nB + MARG_NBC * c->geom.npieces) * g.n_ent))
+                return 1;
             sp.part = (double*)c->d_marg.ptr;
             KernelSpan ks(c, EPDE_KERNEL_MARGINAL);
-            marginal_slab_kernel<<<dim3(c->geom.nA, ey), 128, slab_smem, c->stream>>>(sp);
+            marginal_slab_kernel<<<dim3(c->geom.nA, ey, MARG_NBC), 128, slab_smem, c->stream>>>(sp);
             marginal_rows_kernel<<<dim3(c->geom.n_rows, ey), 128, 0, c->stream>>>(sp);
             c->launches++;
         } else {

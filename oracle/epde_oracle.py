@@ -253,8 +253,9 @@ def window_grams(seg_grams, plan: WindowPlan):
     """(W, K, K): Gram of every sliding window, axes stacked in order (supplementary.py:471)."""
     res = []
     for seg, ax in zip(seg_grams, plan.axes):
-        csum = np.concatenate([np.zeros((1,) + seg.shape[1:]), np.cumsum(seg, axis=0)], axis=0)
-        res.append(csum[ax.seg_hi] - csum[ax.seg_lo])
+        # direct sums over the segments of each window: differences of running sums cancel digits when a column is
+        # heavy-tailed along the axis (products of cubed noisy derivatives: 1e-6 relative on a window weight)
+        res.append(np.stack([seg[int(lo):int(hi)].sum(axis=0) for lo, hi in zip(ax.seg_lo, ax.seg_hi)], axis=0))
     return np.concatenate(res, axis=0)
 
 

@@ -300,6 +300,24 @@ def test_factor_kinds_vs_oracle():
     check_against_oracle(res, toks, shape, eqs, evals, 'kinds', min_checked=3)
 
 
+def test_high_integer_powers_vs_oracle():
+    """integer powers above 3 (multiplications by squaring in the kernel, numpy's pow in the oracle), alone and inside
+    products, negative bases included; the distinct stress population of the bench uses powers up to 5."""
+    shape = (36, 30, 12)
+    rng = np.random.default_rng(9)
+    axes = np.meshgrid(*[np.linspace(0.0, 1.0 + d, n) for d, n in enumerate(shape)], indexing='ij')
+    toks = [(np.sin(2 * axes[0] + k) * np.cos(axes[1] - k) + 0.4 * axes[2] - 0.3 + 0.05 * rng.standard_normal(shape)).reshape(-1)
+            for k in range(4)]
+    eqs = [[[(0, 1)], [(1, 4)], [(2, 5)], [(3, 1)]],
+           [[(1, 1)], [(0, 4), (2, 1)], [(3, 7)], [(2, 6), (0, 2)]],
+           [[(2, 1)], [(3, 5), (1, 4), (0, 3)], [(0, 8)]]]
+    eqs = [[[(t, float(p), 0, 0.0) for t, p in term] for term in eq] for eq in eqs]
+    evals = [(0, 0), (0, 3), (1, 0), (2, 0)]
+    with make_engine(shape, toks) as eng:
+        res = eng.evaluate(epde_b200.encode(eqs, evals))
+    check_against_oracle(res, toks, shape, eqs, evals, 'high powers', min_checked=3)
+
+
 def test_staged_equals_oneshot_and_is_deterministic():
     shape, _, kind = syn.CONFIGS['wave61']
     tokens = syn.make_tokens(shape, kind, seed=4)
@@ -386,26 +404,13 @@ def test_cache_api():
         assert 3 not in eng and eng.consumed_memory == 0
 
 
-def test_grid_sharding_single_gpu():
-    """two shard contexts on one device + a manual sum of their segment Grams / residual sums
-    == the unsharded evaluation; the NCCL variant only replaces the sum."""
+def two_shards_vs_whole(shape, cuts, enc, whole_engine, shard_engines):
+    """two shard contexts on one device + a manual sum of their segment Grams / solution blocks / residual sums
+    (exactly what evaluate_grid_sharded does with NCCL all-reduces) against the unsharded evaluation."""
     import torch
-    shape, _, kind = syn.CONFIGS['heat64']
-    shape = (40, 24, 28)
-    tokens = syn.make_tokens(shape, kind, seed=8)
-    eqs = syn.make_population(len(tokens), 8, seed=8)
-    enc = epde_b200.encode(eqs, syn.make_evals(eqs))
-    with make_engine(shape, tokens) as eng:
-        full = eng.evaluate(enc)
-    cuts = [0, 13, 40]
-    row = shape[1] * shape[2]
-    engines, batches, segs, sums = [], [], [], []
-    for r in range(2):
-        lo, hi = cuts[r], cuts[r + 1]
-        e = epde_b200.Engine((hi - lo,) + shape[1:], shard=(lo, shape[0]))
-        for i, t in enumerate(tokens):
-            e.upload(i, t[lo * row:hi * row])
-        engines.append(e)
+    full = whole_engine.evaluate(enc)
+    batches, segs, sums = [], [], []
+    for e in shard_engines:
         b = e.batch(enc)
         batches.append(b)
         s = torch.zeros(b.gram_size, dtype=torch.float64, device='cuda')
@@ -413,8 +418,7 @@ def test_grid_sharding_single_gpu():
         segs.append(s)
     torch.cuda.synchronize()
     tot = segs[0] + segs[1]
-    # every shard solves half of the evals (epde_batch_solve_part); the solution blocks are merged by a sum, exactly
-    # what evaluate_grid_sharded does with NCCL
+    # every shard solves half of the evals (epde_batch_solve_part); the solution blocks are merged by a sum
     sols = []
     for r in range(2):
         segs[r].copy_(tot)
@@ -434,17 +438,92 @@ def test_grid_sharding_single_gpu():
     outs = [batches[r].fetch(tots.data_ptr()) for r in range(2)]
     for b in batches:
         b.close()
-    for e in engines:
-        e.close()
     for k in ('coef', 'n_active', 'iters', 'sw_weights'):
         assert np.array_equal(getattr(outs[0], k), getattr(outs[1], k)), k
     assert outs[0].n_active.max() > 0 and outs[0].iters.max() > 0
     assert np.array_equal(outs[0].coef != 0, full.coef != 0)
     # the slabs sum their cells in another order than the whole grid: the contract tolerance (1e-6 relative)
-    # applies, random equations of this population reach ~1e-8 through their conditioning
+    # applies, random equations of these populations reach ~1e-8 through their conditioning
     assert_rel(outs[0].coef, full.coef, 'sharded coef', rtol=1e-6, atol=1e-14)
     assert_rel(outs[0].fitness_l1, full.fitness_l1, 'sharded fitness', rtol=1e-6, atol=1e-10)
     assert_rel(outs[0].stability, full.stability, 'sharded stability', rtol=1e-6, atol=1e-14)
+    return full
+
+
+def test_grid_sharding_single_gpu():
+    """uneven cut of a small grid; the NCCL variant only replaces the sums."""
+    shape = (40, 24, 28)
+    tokens = syn.make_tokens(shape, 'heat', seed=8)
+    eqs = syn.make_population(len(tokens), 8, seed=8)
+    enc = epde_b200.encode(eqs, syn.make_evals(eqs))
+    cuts = [0, 13, 40]
+    row = shape[1] * shape[2]
+    shards = []
+    for r in range(2):
+        lo, hi = cuts[r], cuts[r + 1]
+        e = epde_b200.Engine((hi - lo,) + shape[1:], shard=(lo, shape[0]))
+        for i, t in enumerate(tokens):
+            e.upload(i, t[lo * row:hi * row])
+        shards.append(e)
+    with make_engine(shape, tokens) as eng:
+        two_shards_vs_whole(shape, cuts, enc, eng, shards)
+    for e in shards:
+        e.close()
+
+
+def device_engine(shape, kind, seed, axis0_range=None, global_rows=None):
+    """engine whose tokens are generated on the device (counter-based noise: a slab holds the rows of the whole grid)."""
+    import torch
+    lo, hi = axis0_range if axis0_range else (0, shape[0])
+    kw = dict(shard=(lo, global_rows)) if axis0_range else {}
+    eng = epde_b200.Engine((hi - lo,) + tuple(shape[1:]), device=0, **kw)
+    for i in range(len(syn.token_labels(kind))):
+        tk = syn.make_tokens(shape, kind, xp=torch, device=torch.device('cuda', 0), seed=seed, axis0_range=(lo, hi), only=[i])[i]
+        torch.cuda.synchronize()
+        eng.upload_device(i, tk.data_ptr(), tk.numel())
+        eng.synchronize()
+        del tk
+    return eng
+
+
+def test_slab_sharding_at_size_512x256x256():
+    """a 2-shard slab run of a 512 x 256 x 256 grid (population 16, every admissible target) against
+    the unsharded run of the same grid: identical selected sets, coefficients / fitness / stability at 1e-6."""
+    shape, kind = (512, 256, 256), 'heat'
+    eqs = syn.make_population(len(syn.token_labels(kind)), 16, seed=12)
+    enc = epde_b200.encode(eqs, syn.make_evals(eqs))
+    cuts = [0, 256, 512]
+    whole = device_engine(shape, kind, 12)
+    shards = [device_engine(shape, kind, 12, axis0_range=(cuts[r], cuts[r + 1]), global_rows=shape[0]) for r in range(2)]
+    try:
+        full = two_shards_vs_whole(shape, cuts, enc, whole, shards)
+        assert full.coef.shape[0] == enc.n_eval >= 16
+    finally:
+        for e in [whole] + shards:
+            e.close()
+
+
+def test_heat256_population_vs_streamed_oracle():
+    """parity at a size the bench quotes -- heat 256^3, population 16 evaluated as one batch; every
+    eval of the first 4 equations against the streamed oracle (oracle.evaluate_equation_streamed)."""
+    shape, kind = (256, 256, 256), 'heat'
+    tokens = syn.make_tokens(shape, kind, seed=6)
+    eqs = syn.make_population(len(tokens), 16, seed=6)
+    evals = syn.make_evals(eqs)
+    with make_engine(shape, tokens) as eng:
+        res = eng.evaluate(epde_b200.encode(eqs, evals))
+    checked = 0
+    for e in range(4):
+        sel = [v for v, (ee, _) in enumerate(evals) if ee == e]
+        outs = orc.evaluate_equation_streamed(tokens, shape, eqs[e], targets=[evals[v][1] for v in sel])
+        for v, o in zip(sel, outs):
+            if not np.isfinite(o.cond) or o.cond > COND_MAX:
+                continue
+            ref = dict(coef=o.coef, intercept=o.intercept, sw=o.sw_weights, fitness=o.fitness, fitness_l2=o.fitness_l2,
+                       stability=o.stability, scales=eval_scales(tokens, eqs[e], evals[v][1]))
+            compare_eval(res, v, ref, len(eqs[e]), 3, f'heat256 eq {e} eval {v}')
+            checked += 1
+    assert checked >= 4, checked
 
 
 def test_large_grid_properties():
