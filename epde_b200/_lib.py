@@ -51,6 +51,7 @@ SIGNATURES = {
     'epde_fd_gradient': (C.c_int, [vp, vp, vp, C.c_int, c_i64p, C.c_int, c_f64p]),
     'epde_cache_upload_interior': (C.c_int, [vp, C.c_int, vp, C.c_int, c_i64p, c_i64p]),
     'epde_poly_derivative': (C.c_int, [vp, vp, vp, C.c_int, c_i64p, C.c_int, C.c_int, C.c_int, c_f64p, c_f64p]),
+    'epde_poly_derivative_noalloc': (C.c_int, [vp, vp, vp, C.c_int, c_i64p, C.c_int, C.c_int, C.c_int, c_f64p, c_f64p]),
     'epde_measure_fp64_peak': (C.c_int, [C.c_int, C.c_double, c_f64p, c_f64p]),
     'epde_ctx_launch_count': (C.c_int, [vp, c_i64p]),
     'epde_ctx_set_timing': (C.c_int, [vp, C.c_int]),

@@ -51,6 +51,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <set>
 #include <string>
 #include <vector>
@@ -215,7 +216,6 @@ __device__ __forceinline__ double apply_factor(const FactorDesc& f, double x) {
     if (f.ipow == 1) return x;
     if (f.ipow == 2) return x * x;
     if (f.ipow == 3) return x * x * x;
-    return pow(x, f.power);
     if (f.ipow > 3) {                        // integer power by squaring (uniform per warp: a column is one warp's job)
         double r = (f.ipow & 1) ? x : 1.0, sq = x;
         for (int e = f.ipow >> 1; e; e >>= 1) {
@@ -224,6 +224,7 @@ __device__ __forceinline__ double apply_factor(const FactorDesc& f, double x) {
         }
         return r;
     }
+    return pow(x, f.power);
 }
 
 // Phase 1 of both passes: the value of every column of the launch group's dictionary at the points of the
@@ -725,8 +726,8 @@ __global__ void __launch_bounds__(128) marginal_rows_kernel(MargSlabParams p) {
     }
     p.seg[(long long)m.row * p.n_ent + ent] = s;
 }
-
 static_assert(MARG_NBC == 4, "marginal_rows_kernel sums four slot-B chunks explicitly");
+
 // window row = direct sum of the segment rows of the window; row W = every point (all rows of axis 0).
 // grid = (W + 1, ceil(n_ent / 128))
 struct WindowParams {
@@ -2990,6 +2991,69 @@ int epde_poly_derivative(epde_ctx* c, const double* dev_in, double* dev_out, int
     CK(cudaMemcpyAsync((char*)c->d_fd.ptr + wbytes, coords, xbytes, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));               // pageable host sources
     p.w = (const double*)c->d_fd.ptr; p.x = (const double*)((char*)c->d_fd.ptr + wbytes);
+    const int grid = (int)std::min<long long>((p.total + 255) / 256, (long long)c->sm_count * 16);
+    c->launches++;
+    poly_derivative_kernel<<<grid, 256, 0, c->stream>>>(p);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"
+
+// Scratch of the allocation-free entry point below: one fixed array per GPU that loads the library (held until
+// exit).  In host code `g_noalloc_scratch` is only a stand-in for the symbol: its DEVICE address is looked up with
+// cudaGetSymbolAddress, once per device with that device current, and that pointer is what the kernel is given.
+static __device__ __align__(256) double g_noalloc_scratch[EPDE_NOALLOC_MAX_DOUBLES];
+static std::mutex g_noalloc_mutex;
+static double* g_noalloc_ptr[64] = {nullptr};
+
+static int noalloc_scratch(int device, double** out) {          // the caller has made `device` current
+    if (device < 0 || device >= 64) return fail("epde_poly_derivative_noalloc: device %d out of range", device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        void* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr)
+            return fail("epde_poly_derivative_noalloc: cudaGetSymbolAddress failed on device %d: %s", device, cudaGetErrorString(e));
+        g_noalloc_ptr[device] = (double*)ptr;
+    }
+    *out = g_noalloc_ptr[device];
+    return 0;
+}
+
+extern "C" {
+
+int epde_poly_derivative_noalloc(epde_ctx* c, const double* dev_in, double* dev_out, int ndim, const int64_t* shape,
+                                 int axis, int order, int window, const double* weights, const double* coords) {
+    if (!c || !dev_in || !dev_out || !shape || !weights || !coords) return fail("epde_poly_derivative_noalloc: null argument");
+    if (ndim < 1 || ndim > EPDE_MAX_NDIM || axis < 0 || axis >= ndim) return fail("epde_poly_derivative_noalloc: bad ndim / axis");
+    if (dev_in == dev_out) return fail("epde_poly_derivative_noalloc: in-place differentiation is not supported");
+    if (order < 1 || order > 3) return fail("epde_poly_derivative_noalloc: derivative order %d not in 1..3 (fin_der.py:33)", order);
+    if (window < 3 || !(window & 1)) return fail("epde_poly_derivative_noalloc: window %d must be odd and >= 3", window);
+    if (shape[axis] < 1 || shape[axis] > EPDE_NOALLOC_MAX_DOUBLES)
+        return fail("epde_poly_derivative_noalloc: axis %d has %lld points; the fixed scratch holds %d doubles", axis,
+                    (long long)shape[axis], EPDE_NOALLOC_MAX_DOUBLES);
+    const int n = (int)shape[axis];
+    const int bound = window / 2 + 1;                   // deriv_calculators.py:117
+    if (n < 2 * bound + 1 || n < 6) return fail("epde_poly_derivative_noalloc: axis %d has %d points, too few for window %d", axis, n, window);
+    const long long need = (long long)n * window + n;   // weights [n][window] + coordinates [n]
+    if (need > EPDE_NOALLOC_MAX_DOUBLES)
+        return fail("epde_poly_derivative_noalloc: %d points x (window %d + 1) = %lld doubles of scratch; the fixed scratch holds "
+                    "%d (use epde_poly_derivative)", n, window, need, EPDE_NOALLOC_MAX_DOUBLES);
+    CK(cudaSetDevice(c->device));
+    double* scratch = nullptr;
+    if (noalloc_scratch(c->device, &scratch)) return 1;
+    PolyParams p;
+    memset(&p, 0, sizeof p);
+    p.in = dev_in; p.out = dev_out; p.n = n; p.window = window; p.bound = bound; p.order = order;
+    p.total = 1; p.stride = 1;
+    for (int d = 0; d < ndim; ++d) { p.total *= shape[d]; if (d > axis) p.stride *= shape[d]; }
+    const size_t wbytes = sizeof(double) * (size_t)n * window, xbytes = sizeof(double) * (size_t)n;
+    // every scratch value the kernel reads is overwritten here, so nothing of the previous call survives into this one
+    CK(cudaMemcpyAsync(scratch, weights, wbytes, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(scratch + (size_t)n * window, coords, xbytes, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));               // pageable host sources
+    p.w = scratch; p.x = scratch + (size_t)n * window;
     const int grid = (int)std::min<long long>((p.total + 255) / 256, (long long)c->sm_count * 16);
     c->launches++;
     poly_derivative_kernel<<<grid, 256, 0, c->stream>>>(p);

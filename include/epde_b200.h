@@ -199,6 +199,23 @@ int epde_cache_upload_interior(epde_ctx* ctx, int token_id, const double* dev_fu
 int epde_poly_derivative(epde_ctx* ctx, const double* dev_in, double* dev_out, int ndim, const int64_t* shape,
                          int axis, int order, int window, const double* weights, const double* coords);
 
+/* epde_poly_derivative_noalloc: NO COUNTERPART IN THE REFERENCE; added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, checks and result as epde_poly_derivative, but the per-call device scratch (the weight table
+ * [shape[axis]][window] and the coordinate vector, which epde_poly_derivative keeps in a cudaMalloc'ed buffer that
+ * grows on demand) lives in a fixed file-scope __device__ array of EPDE_NOALLOC_MAX_DOUBLES doubles (512 KiB, held by
+ * every GPU that loads the library until the process exits).  The call allocates nothing: no cudaMalloc / cudaFree /
+ * allocating library routine.  Limit: shape[axis] * (window + 1) <= EPDE_NOALLOC_MAX_DOUBLES, otherwise the call fails
+ * with a message naming the limit (use epde_poly_derivative).  The array is shared by every call on the device and
+ * keeps the last call's contents; this call overwrites every value its kernel reads before launching it, so nothing
+ * has to be cleared, but two calls whose device work overlaps (different streams / contexts / host threads on one
+ * GPU) RACE on it: serialise them.  The first call on a device resolves the array's device address
+ * (cudaGetSymbolAddress); like epde_poly_derivative the call copies from pageable host memory and waits for the
+ * context stream before it launches. */
+#define EPDE_NOALLOC_MAX_DOUBLES 65536
+int epde_poly_derivative_noalloc(epde_ctx* ctx, const double* dev_in, double* dev_out, int ndim, const int64_t* shape,
+                                 int axis, int order, int window, const double* weights, const double* coords);
+
 /* Measurement aid (no reference counterpart): sustained FP64 rate of `device` in TFLOP/s through plain FMA
  * chains (SASS DFMA) and through the FP64 tensor-core instruction pass A uses (mma.sync m8n8k4 f64, SASS
  * DMMA.8x8x4), each run for about seconds / 2.  The roofline of the streaming passes is FP64 issue, not HBM. */
