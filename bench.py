@@ -547,7 +547,7 @@ def run_b200(args):
             bound, peak, src = peak_of[kind]
             ach = flops[kind]['executed'] / (ms * 1e-3) / 1e12 if ms > 0 else 0.0
             useful = flops[kind]['useful'] / (ms * 1e-3) / 1e12 if ms > 0 else 0.0
-            traffic = measured_traffic(args.workload, kind, world, args.pop)
+            traffic = measured_traffic(args.workload, kind, world, args.pop or args.population != 'default' or args.norms != 'l1')
             hbm = {'peak_gbs': hbm_peak, 'peak_source': hbm_src,
                    'algorithmic_bytes_per_step': int(alg[kind]),
                    'algorithmic_gbs': alg[kind] / (ms * 1e-3) / 1e9 if ms > 0 else 0.0,
