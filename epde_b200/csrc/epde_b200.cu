@@ -1076,88 +1076,161 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
 // (fitness.py:135-142 and 70-83).  Persistent CTAs (one per SM) walk over chunks of PT_B consecutive points
 // (token rows of the chunk fetched with one bulk async copy per token, two stages).  Phase 1 builds the column tile
 // of the launch group's dictionary once per chunk; phase 2: warps take jobs from a shared counter:
-//   equation job  up to EQJ evals of ONE equation (its admissible targets: they all read the same T columns).  Lane <->
-//                 8 points; the job walks the columns some eval of it needs, loads a column's 8 values ONCE and adds
-//                 a[j] * column to the residual of every eval j with a non-zero a[j] (a = 1 for the eval's target, -w for
-//                 a surviving feature): the kernel is bound by shared-memory bandwidth, and a column value now feeds up
-//                 to EQJ FMAs instead of one.  The EQJ per-eval sums are reduced over the warp together
-//                 (reduce-scatter butterfly);
-//   target job    sum|t| of one distinct target column.
+//   octet job   8 consecutive evals of the group's list (sorted by target column): lane <-> 4 points per 128-point
+//               sweep; a residual is the sparse dot of the eval's target and surviving columns read from the column
+//               tile (the target column stays in registers while consecutive evals share it); the 8 per-eval sums are
+//               reduced over the warp together (reduce-scatter butterfly: 9 shuffle steps instead of 40);
+//   target job  sum|t| of one distinct target column.
 // Chunk sums go to a per-CTA shared table in chunk order, written once per CTA and reduced over CTAs in CTA order by
 // residual_final_kernel: fixed summation order, no atomics on data.
 // ------------------------------------------------------------------------------------------
-#define EQJ 4                // evals per equation job
+#define OCT 8                // evals per octet job
 
-struct EqJobStatic {         // 16 bytes, built on the host at batch creation
-    int eq;                  // equation
-    int slot0;               // first sum slot; the evals of the job are slots [slot0, slot0 + nev)
-    int nev;                 // 1..EQJ
-    int ent_off;             // first column entry of the job (capacity: T entries)
-};
-
-struct EqJobHdr {            // 96 bytes, built on the device from the solve outputs
-    int ncols;               // columns some eval of the job needs
-    int nev;
-    int ent_off;
-    int slot0;
-    int pad[4];
-    double b1[EQJ];          // offset of the L1 residual
-    double delta[EQJ];       // r2 = r + delta (b1 - intercept: non-zero only when no feature survives)
-};
-
-struct ColEnt {              // 48 bytes: one column of an equation job
-    int col;                 // byte offset of the column's row in the column tile
-    int pad[3];
-    double a[EQJ];           // residual of eval j += a[j] * column
+struct EvalJob {             // 32 bytes, built on the device from the solve outputs
+    int tcol, nnz, pad0, pad1;   // target column (byte offset of its row in the column tile), surviving features
+    double b1;               // offset of the L1 residual
+    double delta;            // r2 = r + delta (b1 - intercept: non-zero only when no feature survives)
 };
 
 struct ResidProgParams {
     const EqDesc* eqs;
+    const int* eval_eq;
     const int* eval_tgt;
-    const int* slot_ev;      // [n_slots] eval id of every sum slot (job order)
-    const EqJobStatic* jobs; // [n_jobs]
+    const int* slot_ev;      // [n_slots] eval id of every sum slot (sorted by target column)
     const double* wterm;     // [n_eval][TMAX]
     const double* intercept;
     const double* intercept_l1;
-    EqJobHdr* hdr;           // [n_jobs]
-    ColEnt* ent;             // [sum of T over the jobs]
-    int n_jobs;
+    EvalJob* jobs;           // [n_slots rounded up to OCT]
+    int* job_col;            // [n_slots][TMAX] byte offsets of the surviving columns' rows in the column tile
+    double* job_w;           // [n_slots][TMAX]
+    int n_slots;
 };
 
 __global__ void residual_prog_kernel(ResidProgParams p) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= p.n_jobs) return;
-    const EqJobStatic js = p.jobs[j];
-    const EqDesc& eq = p.eqs[js.eq];
-    EqJobHdr h;
-    h.nev = js.nev; h.ent_off = js.ent_off; h.slot0 = js.slot0;
-    h.pad[0] = h.pad[1] = h.pad[2] = h.pad[3] = 0;
-    int ev[EQJ], tgt[EQJ];
-#pragma unroll
-    for (int v = 0; v < EQJ; ++v) {
-        ev[v] = v < js.nev ? p.slot_ev[js.slot0 + v] : -1;
-        tgt[v] = v < js.nev ? p.eval_tgt[ev[v]] : -1;
-        h.b1[v] = v < js.nev ? p.intercept_l1[ev[v]] : 0.0;
-        h.delta[v] = v < js.nev ? p.intercept_l1[ev[v]] - p.intercept[ev[v]] : 0.0;
-    }
-    int n = 0;
-    for (int t = 0; t < eq.T; ++t) {
-        ColEnt e;
-        e.col = (int)eq.col[t] * (PP_B * 8);
-        e.pad[0] = e.pad[1] = e.pad[2] = 0;
-        bool any = false;
-#pragma unroll
-        for (int v = 0; v < EQJ; ++v) {
-            double a = 0.0;
-            if (v < js.nev) a = (t == tgt[v]) ? 1.0 : -p.wterm[(long long)ev[v] * TMAX + t];
-            if (a == 0.0) a = 0.0;          // -0.0 -> +0.0
-            e.a[v] = a;
-            any = any || a != 0.0;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n_pad = (p.n_slots + OCT - 1) / OCT * OCT;
+    if (s >= n_pad) return;
+    EvalJob j;
+    j.tcol = 0; j.nnz = 0; j.pad0 = j.pad1 = 0; j.b1 = 0.0; j.delta = 0.0;
+    if (s < p.n_slots) {
+        const int ev = p.slot_ev[s];
+        const EqDesc& eq = p.eqs[p.eval_eq[ev]];
+        const int tgt = p.eval_tgt[ev];
+        int nnz = 0;
+        for (int t = 0; t < eq.T; ++t) {
+            const double w = p.wterm[(long long)ev * TMAX + t];
+            if (t != tgt && w != 0.0) {
+                p.job_col[(long long)s * TMAX + nnz] = (int)eq.col[t] * (PP_B * 8);
+                p.job_w[(long long)s * TMAX + nnz] = w;
+                ++nnz;
+            }
         }
-        if (any) p.ent[js.ent_off + n++] = e;
+        j.tcol = (int)eq.col[tgt] * (PP_B * 8); j.nnz = nnz;
+        j.b1 = p.intercept_l1[ev];
+        j.delta = p.intercept_l1[ev] - p.intercept[ev];
     }
-    h.ncols = n;
-    p.hdr[j] = h;
+    p.jobs[s] = j;
+}
+
+// Pass B walks the evals of a launch group sorted by (target column, first surviving column), so that consecutive
+// evals of an octet reuse the registers that hold those two columns, and reads their descriptors from a COMPACT
+// table (32-byte headers in that order + CSR lists of (column, weight) entries) small enough to sit in shared memory.
+// The surviving sets only exist after the solve, so ordering and packing run on the device: one CTA, bitonic sort of
+// 64-bit keys (column, column, slot), then a prefix sum of the entry counts.  More than SORT_MAX evals: slot order.
+#define SORT_MAX 8192
+struct EvalHdr {             // 32 bytes
+    int tcol;                // byte offset of the target column's row in the column tile
+    int nnz;                 // surviving features
+    int off;                 // first entry in the CSR arrays
+    int slot;                // sum slot (-1: padding)
+    double b1, delta;
+};
+
+struct ResidPackParams {
+    const EvalJob* jobs;     // [n_slots] in slot order
+    const int* job_col;      // [n_slots][TMAX]
+    const double* job_w;     // [n_slots][TMAX]
+    EvalHdr* hdr;            // [n_slots rounded up to OCT] in walking order
+    int* ent_col;            // [sum nnz]
+    double* ent_w;           // [sum nnz]
+    int* meta;               // [0] = sum nnz
+    int n_slots;
+};
+
+__global__ void __launch_bounds__(1024) residual_pack_kernel(ResidPackParams p) {
+    extern __shared__ unsigned long long s_key[];          // n2 keys, then n2 ints (scan)
+    const int n_pad = (p.n_slots + OCT - 1) / OCT * OCT;
+    int n2 = 1;
+    while (n2 < p.n_slots) n2 <<= 1;
+    if (n2 > SORT_MAX) {                                    // too many evals for the shared-memory sort: slot order, serial scan
+        if (threadIdx.x == 0) {
+            int off = 0;
+            for (int q = 0; q < n_pad; ++q) {
+                EvalHdr h;
+                h.tcol = 0; h.nnz = 0; h.off = off; h.slot = -1; h.b1 = 0.0; h.delta = 0.0;
+                if (q < p.n_slots) {
+                    const EvalJob j = p.jobs[q];
+                    h.tcol = j.tcol; h.nnz = j.nnz; h.slot = q; h.b1 = j.b1; h.delta = j.delta;
+                    for (int z = 0; z < j.nnz; ++z) { p.ent_col[off + z] = p.job_col[(long long)q * TMAX + z]; p.ent_w[off + z] = p.job_w[(long long)q * TMAX + z]; }
+                    off += j.nnz;
+                }
+                p.hdr[q] = h;
+            }
+            p.meta[0] = off;
+        }
+        return;
+    }
+    int* s_scan = (int*)(s_key + n2);
+    for (int q = threadIdx.x; q < n2; q += blockDim.x) {
+        unsigned long long k = ~0ull;
+        if (q < p.n_slots) {
+            const EvalJob j = p.jobs[q];
+            const unsigned long long c0 = j.nnz > 0 ? (unsigned long long)(p.job_col[(long long)q * TMAX] / (PP_B * 8)) : 0xffffull;
+            k = ((unsigned long long)(j.tcol / (PP_B * 8)) << 44) | (c0 << 24) | (unsigned long long)q;
+        }
+        s_key[q] = k;
+    }
+    __syncthreads();
+    for (int k = 2; k <= n2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int q = threadIdx.x; q < n2; q += blockDim.x) {
+                const int x = q ^ j;
+                if (x > q) {
+                    const unsigned long long a = s_key[q], b = s_key[x];
+                    const bool up = (q & k) == 0;
+                    if ((a > b) == up) { s_key[q] = b; s_key[x] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    // inclusive scan of the entry counts in walking order (Hillis-Steele, n2 <= 8192)
+    for (int q = threadIdx.x; q < n2; q += blockDim.x)
+        s_scan[q] = q < p.n_slots ? p.jobs[(int)(s_key[q] & 0xffffffull)].nnz : 0;
+    __syncthreads();
+    for (int d = 1; d < n2; d <<= 1) {
+        int add[SORT_MAX / 1024];
+        int m = 0;
+        for (int q = threadIdx.x; q < n2; q += blockDim.x) add[m++] = q >= d ? s_scan[q - d] : 0;
+        __syncthreads();
+        m = 0;
+        for (int q = threadIdx.x; q < n2; q += blockDim.x) s_scan[q] += add[m++];
+        __syncthreads();
+    }
+    for (int q = threadIdx.x; q < n_pad; q += blockDim.x) {
+        EvalHdr h;
+        h.tcol = 0; h.nnz = 0; h.off = 0; h.slot = -1; h.b1 = 0.0; h.delta = 0.0;
+        if (q < p.n_slots) {
+            const int slot = (int)(s_key[q] & 0xffffffull);
+            const EvalJob j = p.jobs[slot];
+            h.tcol = j.tcol; h.nnz = j.nnz; h.off = s_scan[q] - j.nnz; h.slot = slot; h.b1 = j.b1; h.delta = j.delta;
+            for (int z = 0; z < j.nnz; ++z) {
+                p.ent_col[h.off + z] = p.job_col[(long long)slot * TMAX + z];
+                p.ent_w[h.off + z] = p.job_w[(long long)slot * TMAX + z];
+            }
+        }
+        p.hdr[q] = h;
+    }
+    if (threadIdx.x == 0) p.meta[0] = p.n_slots > 0 ? s_scan[p.n_slots - 1] : 0;
 }
 
 struct ResidParams {
@@ -1167,9 +1240,10 @@ struct ResidParams {
     const ColDesc* cols;
     const FactorDesc* gfac;
     int nbuild;              // columns of the tile (cp)
-    const EqJobHdr* hdr;     // [n_jobs] (residual_prog_kernel)
-    const ColEnt* ent;       // [n_ent_cap] column entries of the jobs
-    int n_jobs, n_ent_cap;
+    const EvalHdr* hdr;      // [n_slots rounded up to OCT] in walking order (residual_pack_kernel)
+    const int* ent_col;      // CSR entries: byte offsets of the surviving columns' rows in the column tile
+    const double* ent_w;
+    const int* meta;         // [0] = number of entries
     int wcol;                // weighted mode: row of the column tile that holds the sample weights g (L2Fitness multiplies
                              // its residual by g, fitness.py:81-82), else -1
     int desc_smem;           // bytes of shared memory available for a copy of the descriptors (0: read them from global)
@@ -1190,20 +1264,24 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-// sums of EQJ = 4 per-lane values over the warp, all at once: after the two exchange steps lane l holds value
-// ((l >> 4) & 1) * 2 + ((l >> 3) & 1) summed over the 4 lanes that share its low three bits; three more butterfly steps
-// finish it.  Returns that value's warp total (the same in the 8 lanes of a group).
-__device__ __forceinline__ double warp_sum4(const double (&a)[EQJ], int lane) {
-    double b[2];
-    const bool h16 = lane & 16, h8 = lane & 8;
+// sums of 8 per-lane values over the warp, all at once: after the three exchange steps lane l holds value
+// ((l >> 4) & 1) * 4 + ((l >> 3) & 1) * 2 + ((l >> 2) & 1) summed over the 8 lanes that share its low two bits; two more
+// butterfly steps finish it.  Returns that value's warp total (the same in the 4 lanes of a group).
+__device__ __forceinline__ double warp_sum8(const double (&a)[OCT], int lane) {
+    double b[4], c[2];
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const double keep = h16 ? a[i + 2] : a[i], give = h16 ? a[i] : a[i + 2];
+    for (int i = 0; i < 4; ++i) {
+        const double keep = h16 ? a[i + 4] : a[i], give = h16 ? a[i] : a[i + 4];
         b[i] = keep + __shfl_xor_sync(0xffffffffu, give, 16);
     }
-    const double keep = h8 ? b[1] : b[0], give = h8 ? b[0] : b[1];
-    double d = keep + __shfl_xor_sync(0xffffffffu, give, 8);
-    d += __shfl_xor_sync(0xffffffffu, d, 4);
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const double keep = h8 ? b[i + 2] : b[i], give = h8 ? b[i] : b[i + 2];
+        c[i] = keep + __shfl_xor_sync(0xffffffffu, give, 8);
+    }
+    const double keep = h4 ? c[1] : c[0], give = h4 ? c[0] : c[1];
+    double d = keep + __shfl_xor_sync(0xffffffffu, give, 4);
     d += __shfl_xor_sync(0xffffffffu, d, 2);
     d += __shfl_xor_sync(0xffffffffu, d, 1);
     return d;
@@ -1242,17 +1320,21 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
     const int nsum = 2 * p.n_slots + p.n_tcols;
     load_cols_to_smem(s_cols, p.cols, p.nbuild, PT_B * 8, tid, nthreads);
     for (int q = tid; q < nsum; q += nthreads) s_sum[q] = 0.0;
-    // descriptors of the jobs: a shared-memory copy when it fits (generic pointers: the loops below do not care)
-    const EqJobHdr* hdr = p.hdr;
-    const ColEnt* ent = p.ent;
+    // descriptors of the evals: a shared-memory copy when it fits (generic pointers: the loops below do not care)
+    const int n_oct = (p.n_slots + OCT - 1) / OCT;
+    const EvalHdr* hdr = p.hdr;
+    const int* ent_col = p.ent_col;
+    const double* ent_w = p.ent_w;
     {
-        const size_t need = sizeof(EqJobHdr) * (size_t)p.n_jobs + sizeof(ColEnt) * (size_t)p.n_ent_cap + 16;
+        const int n_ent = p.meta[0];
+        const size_t need = sizeof(EvalHdr) * (size_t)n_oct * OCT + (sizeof(double) + sizeof(int)) * (size_t)n_ent + 16;
         if (need <= (size_t)p.desc_smem) {
-            EqJobHdr* sh = (EqJobHdr*)(s_sum + ((nsum + 1) & ~1));
-            ColEnt* se = (ColEnt*)(sh + p.n_jobs);
-            for (int q = tid; q < p.n_jobs * (int)(sizeof(EqJobHdr) / 16); q += nthreads) ((double2*)sh)[q] = ((const double2*)p.hdr)[q];
-            for (int q = tid; q < p.n_ent_cap * (int)(sizeof(ColEnt) / 16); q += nthreads) ((double2*)se)[q] = ((const double2*)p.ent)[q];
-            hdr = sh; ent = se;
+            EvalHdr* sh = (EvalHdr*)(s_sum + ((nsum + 1) & ~1));
+            double* sw = (double*)(sh + (size_t)n_oct * OCT);
+            int* sc = (int*)(sw + n_ent);
+            for (int q = tid; q < n_oct * OCT * 2; q += nthreads) ((double2*)sh)[q] = ((const double2*)p.hdr)[q];
+            for (int q = tid; q < n_ent; q += nthreads) { sw[q] = p.ent_w[q]; sc[q] = p.ent_col[q]; }
+            hdr = sh; ent_col = sc; ent_w = sw;
         }
     }
     if (tid == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); }
@@ -1264,7 +1346,7 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
     unsigned phase[2] = {0, 0};
     int it = 0;
     if (p.nstages == 2 && (long long)blockIdx.x < p.n_chunks) resid_stage_issue(p, blockIdx.x, tiles, &s_bar[0], tid, nthreads);
-    const int njobs_all = p.n_jobs + p.n_tcols;
+    const int njobs_all = n_oct + p.n_tcols;
     for (long long ci = blockIdx.x; ci < p.n_chunks; ci += gridDim.x, ++it) {
         const int st = (p.nstages == 2) ? (it & 1) : 0;
         double* tile = tiles + (size_t)st * p.U * PT_B;
@@ -1295,95 +1377,96 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
         __syncthreads();
 
         const unsigned cl = ct + lane * 8;
-        const bool full = npts == PT_B;
         for (;;) {
             int jj = 0;
             if (lane == 0) jj = atomicAdd(&s_next, 1);
             jj = __shfl_sync(0xffffffffu, jj, 0);
             if (jj >= njobs_all) break;
-            if (jj < p.n_jobs) {
-                // ---------------- equation job
-                const EqJobHdr* h = hdr + jj;
-                const int4 h0 = *(const int4*)h;                  // ncols, nev, ent_off, slot0
-                const double2 b01 = *(const double2*)&h->b1[0], b23 = *(const double2*)&h->b1[2];
-                double r[EQJ][RES_NPL];
+            if (jj < n_oct) {
+                // ---------------- octet job: evals [8 jj, 8 jj + 8) of the list (padding evals: nnz 0, sums discarded)
+                // descriptors are fetched up front, spread over the lanes (lane v: header of eval v; lane z: entry z of
+                // each eval), and broadcast by shuffles inside the loops: no global load on the critical path
+                const EvalHdr mine = hdr[(size_t)jj * OCT + (lane & 7)];
+                const int my_slot = mine.slot;
+                const bool full = npts == PT_B;
+                double a1[OCT], a2[OCT];
+                int cur_t = -1, cur_c = -1;
+                double t[RES_NPL], c1[RES_NPL];
 #pragma unroll
-                for (int k = 0; k < RES_NPL; ++k) { r[0][k] = -b01.x; r[1][k] = -b01.y; r[2][k] = -b23.x; r[3][k] = -b23.y; }
-                const ColEnt* e = ent + h0.z;
-                // entry z + 1 is fetched while entry z is being used (the table has a spare entry behind the last job)
-                int co_n = *(const int*)e;
-                double2 a01_n = *(const double2*)&e->a[0], a23_n = *(const double2*)&e->a[2];
+                for (int v = 0; v < OCT; ++v) {
+                    // every shuffle sits at the top level of the unrolled loop (none inside a conditional)
+                    const int nz = __shfl_sync(0xffffffffu, mine.nnz, v);
+                    const int tco = __shfl_sync(0xffffffffu, mine.tcol, v);
+                    const double b1 = __shfl_sync(0xffffffffu, mine.b1, v);
+                    // entry z of the eval in lane z (one coalesced fetch), broadcast by shuffle when used
+                    const int eo = __shfl_sync(0xffffffffu, mine.off, v) + lane;
+                    const int e_col = (lane < nz) ? ent_col[eo] : 0;
+                    const double e_w = (lane < nz) ? ent_w[eo] : 0.0;
+                    const int co0 = __shfl_sync(0xffffffffu, e_col, 0), co1 = __shfl_sync(0xffffffffu, e_col, 1);
+                    const double w0 = __shfl_sync(0xffffffffu, e_w, 0), w1 = __shfl_sync(0xffffffffu, e_w, 1);
+                    if (tco != cur_t) {
+                        cur_t = tco;
+#pragma unroll
+                        for (int k = 0; k < RES_NPL; ++k) t[k] = lds_f64_e(cl + tco + k * 256, jj);
+                    }
+                    double r[RES_NPL];
+#pragma unroll
+                    for (int k = 0; k < RES_NPL; ++k) r[k] = t[k] - b1;
+                    if (nz > 0) {
+                        // first surviving column: kept in registers while consecutive evals use the same one
+                        if (co0 != cur_c) {
+                            cur_c = co0;
+#pragma unroll
+                            for (int k = 0; k < RES_NPL; ++k) c1[k] = lds_f64_e(cl + co0 + k * 256, jj);
+                        }
+#pragma unroll
+                        for (int k = 0; k < RES_NPL; ++k) r[k] = fma(-w0, c1[k], r[k]);
+                    }
+                    if (nz > 1) {
+#pragma unroll
+                        for (int k = 0; k < RES_NPL; ++k) r[k] = fma(-w1, lds_f64_e(cl + co1 + k * 256, jj), r[k]);
+                    }
+                    if (nz > 2) {
 #pragma unroll 1
-                for (int z = 0; z < h0.x; ++z) {
-                    const int co = co_n;
-                    const double2 a01 = a01_n, a23 = a23_n;
-                    ++e;
-                    co_n = *(const int*)e;
-                    a01_n = *(const double2*)&e->a[0]; a23_n = *(const double2*)&e->a[2];
-                    double c[RES_NPL];
+                        for (int z = 2; z < nz; ++z) {
+                            const unsigned ca = cl + (unsigned)__shfl_sync(0xffffffffu, e_col, z);
+                            const double w = __shfl_sync(0xffffffffu, e_w, z);
 #pragma unroll
-                    for (int k = 0; k < RES_NPL; ++k) c[k] = lds_f64_e(cl + co + k * 256, jj);
-                    if (a01.x != 0.0) {
-#pragma unroll
-                        for (int k = 0; k < RES_NPL; ++k) r[0][k] = fma(a01.x, c[k], r[0][k]);
+                            for (int k = 0; k < RES_NPL; ++k) r[k] = fma(-w, lds_f64_e(ca + k * 256, jj), r[k]);
+                        }
                     }
-                    if (a01.y != 0.0) {
-#pragma unroll
-                        for (int k = 0; k < RES_NPL; ++k) r[1][k] = fma(a01.y, c[k], r[1][k]);
-                    }
-                    if (a23.x != 0.0) {
-#pragma unroll
-                        for (int k = 0; k < RES_NPL; ++k) r[2][k] = fma(a23.x, c[k], r[2][k]);
-                    }
-                    if (a23.y != 0.0) {
-#pragma unroll
-                        for (int k = 0; k < RES_NPL; ++k) r[3][k] = fma(a23.y, c[k], r[3][k]);
-                    }
-                }
-                double a1[EQJ], a2[EQJ];
-                if (L2) {
-                    const double2 d01 = *(const double2*)&h->delta[0], d23 = *(const double2*)&h->delta[2];
-                    const double dl[EQJ] = {d01.x, d01.y, d23.x, d23.y};
-                    double g[RES_NPL];
-#pragma unroll
-                    for (int k = 0; k < RES_NPL; ++k) g[k] = (p.wcol >= 0) ? lds_f64_e(cl + p.wcol * (PP_B * 8) + k * 256, jj) : 1.0;
-#pragma unroll
-                    for (int v = 0; v < EQJ; ++v) {
-                        double s1 = 0.0, s2 = 0.0;
+                    double s1 = 0.0, s2 = 0.0;
+                    if (L2) {
+                        const double dl = __shfl_sync(0xffffffffu, mine.delta, v);
 #pragma unroll
                         for (int k = 0; k < RES_NPL; ++k) {
-                            const bool ok = full || lane + 32 * k < npts;
-                            const double r2 = (r[v][k] + dl[v]) * g[k];
-                            s1 += ok ? fabs(r[v][k]) : 0.0;
-                            s2 = ok ? fma(r2, r2, s2) : s2;
+                            double r2 = r[k] + dl;
+                            if (p.wcol >= 0) r2 *= lds_f64_e(cl + p.wcol * (PP_B * 8) + k * 256, jj);
+                            r[k] = (full || lane + 32 * k < npts) ? r[k] : 0.0;
+                            s2 = (full || lane + 32 * k < npts) ? fma(r2, r2, s2) : s2;
                         }
-                        a1[v] = s1; a2[v] = s2;
+#pragma unroll
+                        for (int k = 0; k < RES_NPL; ++k) s1 += fabs(r[k]);
+                    } else if (full) {
+#pragma unroll
+                        for (int k = 0; k < RES_NPL; ++k) s1 += fabs(r[k]);
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < RES_NPL; ++k) if (lane + 32 * k < npts) s1 += fabs(r[k]);
                     }
-                } else {
-#pragma unroll
-                    for (int v = 0; v < EQJ; ++v) {
-                        double s1 = 0.0;
-                        if (full) {
-#pragma unroll
-                            for (int k = 0; k < RES_NPL; ++k) s1 += fabs(r[v][k]);
-                        } else {
-#pragma unroll
-                            for (int k = 0; k < RES_NPL; ++k) if (lane + 32 * k < npts) s1 += fabs(r[v][k]);
-                        }
-                        a1[v] = s1; a2[v] = 0.0;
-                    }
+                    a1[v] = s1; a2[v] = s2;
                 }
-                const int vi = ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1);
-                const bool writer = (lane & 7) == 0 && vi < h0.y;
-                const double t1 = warp_sum4(a1, lane);
-                if (writer) s_sum[h0.w + vi] += t1;
+                const int vi = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+                const int slot = __shfl_sync(0xffffffffu, my_slot, vi);
+                const double t1 = warp_sum8(a1, lane);
+                if ((lane & 3) == 0 && slot >= 0) s_sum[slot] += t1;
                 if (L2) {
-                    const double t2 = warp_sum4(a2, lane);
-                    if (writer) s_sum[p.n_slots + h0.w + vi] += t2;
+                    const double t2 = warp_sum8(a2, lane);
+                    if ((lane & 3) == 0 && slot >= 0) s_sum[p.n_slots + slot] += t2;
                 }
             } else {
                 // ---------------- target job: sum|t| of one target column (padding points hold 0)
-                const int tc = jj - p.n_jobs;
+                const int tc = jj - n_oct;
                 const int c = p.tcols[tc];
                 double a = 0.0;
 #pragma unroll
@@ -1718,9 +1801,7 @@ struct LaunchGroup {             // equations evaluated together over ONE dictio
     std::vector<int> col_term;   // column -> global distinct-term id (the ones column is appended after these)
     int ncols = 0, cp = 0, n_ent = 0;
     int ntasks = 0, ksplit = 1, n_block_pairs = 0;
-    int n_slots = 0, n_tcols = 0;   // pass-B sums: evals (sum slots), distinct target columns
-    int n_jobs = 0, n_ent_cap = 0;  // pass-B equation jobs and the capacity of their column-entry table
-    EqJobStatic* d_jobs = nullptr;
+    int n_slots = 0, n_tcols = 0;   // pass-B jobs: evals (sum slots), distinct target columns
     int n_gfac = 0;
     long long seg_off = 0, win_off = 0, pe_off = 0;     // doubles / doubles / ints into the batch-wide tables
     // device pointers into ctx->d_enc
@@ -1990,6 +2071,7 @@ int epde_ctx_create(int device, int ndim, const int64_t* inner_shape, epde_ctx**
         for (const void* fn : resid) if (set_dyn_smem(fn, c->max_smem, &c->smem_resid)) { delete c; return 1; }
         for (const void* fn : solve) if (set_dyn_smem(fn, c->max_smem, &c->smem_solve)) { delete c; return 1; }
         int unused = c->max_smem;
+        if (set_dyn_smem((const void*)residual_pack_kernel, c->max_smem, &unused)) { delete c; return 1; }
         if (set_dyn_smem((const void*)marginal_slab_kernel, c->max_smem, &unused)) { delete c; return 1; }
     }
     c->N = 1;
@@ -2257,7 +2339,7 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
     auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
     std::vector<char> img;
     auto put = [&](const void* src, size_t bytes) { const size_t o = align(img.size()); img.resize(o + std::max<size_t>(bytes, 1)); if (bytes) memcpy(img.data() + o, src, bytes); return o; };
-    struct GOff { size_t cols, gfac, tasks, flush, slot_ev, slot_tci, tcols, jobs; };
+    struct GOff { size_t cols, gfac, tasks, flush, slot_ev, slot_tci, tcols; };
     std::vector<GOff> goff(b->groups.size());
     std::vector<int> pairent_all;
     long long seg_off = 0, win_off = 0;
@@ -2353,42 +2435,18 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
                         if (ci <= cj) flush[((size_t)(t * TASK_PAIRS + m) * 32 + l) * 2 + h] = pairent[(size_t)ci * g.cp + cj];
                     }
             }
-        // pass-B jobs: the evals of an equation in chunks of <= EQJ (near-equal sizes), the expensive jobs first (the
-        // warps of a CTA take them from a counter); sum slots follow the job order; distinct target columns for sum|t|
-        std::vector<int> tcols;
+        // pass-B jobs.  Sum slots = the evals of the group sorted by target column (consecutive evals then share the
+        // target registers); distinct target columns for sum|t|
+        std::vector<std::pair<int, int>> byt;      // (target column, eval)
         for (int e : g.eqs)
-            for (int v : eq_evals[e]) tcols.push_back((int)b->eqs[e].col[eval_target[v]]);
-        std::sort(tcols.begin(), tcols.end());
-        tcols.erase(std::unique(tcols.begin(), tcols.end()), tcols.end());
-        struct JobTmp { int eq, first, nev, cost; };
-        std::vector<JobTmp> jt;
-        for (int e : g.eqs) {
-            const int n = (int)eq_evals[e].size();
-            const int parts = (n + EQJ - 1) / EQJ;
-            for (int q = 0, first = 0; q < parts; ++q) {
-                const int nev = n / parts + (q < n % parts ? 1 : 0);
-                jt.push_back({e, first, nev, b->eqs[e].T * (nev + 1)});
-                first += nev;
-            }
+            for (int v : eq_evals[e]) byt.push_back({(int)b->eqs[e].col[eval_target[v]], v});
+        std::stable_sort(byt.begin(), byt.end());
+        std::vector<int> slot_ev, slot_tci, tcols;
+        for (auto& q : byt) {
+            if (tcols.empty() || tcols.back() != q.first) tcols.push_back(q.first);
+            slot_ev.push_back(q.second);
+            slot_tci.push_back((int)tcols.size() - 1);
         }
-        std::stable_sort(jt.begin(), jt.end(), [](const JobTmp& x, const JobTmp& y) { return x.cost > y.cost; });
-        std::vector<int> slot_ev, slot_tci;
-        std::vector<EqJobStatic> jobs_static;
-        int ent_cap = 0;
-        for (auto& j : jt) {
-            EqJobStatic js;
-            js.eq = j.eq; js.slot0 = (int)slot_ev.size(); js.nev = j.nev; js.ent_off = ent_cap;
-            ent_cap += b->eqs[j.eq].T;
-            for (int q = 0; q < j.nev; ++q) {
-                const int v = eq_evals[j.eq][j.first + q];
-                slot_ev.push_back(v);
-                const int tc = (int)b->eqs[j.eq].col[eval_target[v]];
-                slot_tci.push_back((int)(std::lower_bound(tcols.begin(), tcols.end(), tc) - tcols.begin()));
-            }
-            jobs_static.push_back(js);
-        }
-        g.n_jobs = (int)jobs_static.size();
-        g.n_ent_cap = ent_cap + 1;                 // one spare entry: pass B prefetches one entry past a job's last
         g.n_slots = (int)slot_ev.size();
         g.n_tcols = (int)tcols.size();
         // tables
@@ -2407,7 +2465,6 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
         goff[gi].slot_ev = put(slot_ev.data(), slot_ev.size() * sizeof(int));
         goff[gi].slot_tci = put(slot_tci.data(), slot_tci.size() * sizeof(int));
         goff[gi].tcols = put(tcols.data(), tcols.size() * sizeof(int));
-        goff[gi].jobs = put(jobs_static.data(), jobs_static.size() * sizeof(EqJobStatic));
     }
     b->seg_doubles = seg_off;
     b->win_doubles = win_off;
@@ -2438,7 +2495,6 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
         g.d_cols = (ColDesc*)(d + goff[gi].cols); g.d_gfac = (FactorDesc*)(d + goff[gi].gfac);
         g.d_tasks = (TaskDesc*)(d + goff[gi].tasks); g.d_flush = (int*)(d + goff[gi].flush);
         g.d_slot_ev = (int*)(d + goff[gi].slot_ev); g.d_slot_tci = (int*)(d + goff[gi].slot_tci); g.d_tcols = (int*)(d + goff[gi].tcols);
-        g.d_jobs = (EqJobStatic*)(d + goff[gi].jobs);
     }
     // outputs
     const size_t ne = (size_t)std::max(1, n_eval);
@@ -2746,16 +2802,28 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
     auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
     for (auto& g : b->groups) {
         if (g.n_slots == 0) continue;
-        const size_t o_ent = align(sizeof(EqJobHdr) * (size_t)g.n_jobs), tot = align(o_ent + sizeof(ColEnt) * (size_t)g.n_ent_cap + 64);
+        const size_t n_pad = ((size_t)g.n_slots + OCT - 1) / OCT * OCT;
+        const size_t o_col = align(sizeof(EvalJob) * n_pad), o_w = align(o_col + sizeof(int) * n_pad * TMAX),
+                     o_hdr = align(o_w + sizeof(double) * n_pad * TMAX), o_ec = align(o_hdr + sizeof(EvalHdr) * n_pad),
+                     o_ew = align(o_ec + sizeof(int) * n_pad * TMAX), o_meta = align(o_ew + sizeof(double) * n_pad * TMAX),
+                     tot = align(o_meta + 64);
         if (c->d_jobs.ensure(tot)) return 1;
         char* jb = (char*)c->d_jobs.ptr;
         ResidProgParams pp;
-        pp.eqs = b->d_eqs; pp.eval_tgt = b->d_eval_tgt; pp.slot_ev = g.d_slot_ev; pp.jobs = g.d_jobs;
+        pp.eqs = b->d_eqs; pp.eval_eq = b->d_eval_eq; pp.eval_tgt = b->d_eval_tgt; pp.slot_ev = g.d_slot_ev;
         pp.wterm = b->d_wterm; pp.intercept = b->d_intercept; pp.intercept_l1 = b->d_b1;
-        pp.hdr = (EqJobHdr*)jb; pp.ent = (ColEnt*)(jb + o_ent); pp.n_jobs = g.n_jobs;
-        // (entries past a job's ncols are never read by the jobs; the staging copy of pass B reads the whole table)
-        CK(cudaMemsetAsync(jb + o_ent, 0, sizeof(ColEnt) * (size_t)g.n_ent_cap, c->stream));
-        { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_prog_kernel<<<(unsigned)((g.n_jobs + 63) / 64), 64, 0, c->stream>>>(pp); }
+        pp.jobs = (EvalJob*)jb; pp.job_col = (int*)(jb + o_col); pp.job_w = (double*)(jb + o_w); pp.n_slots = g.n_slots;
+        { KernelSpan ks(c, EPDE_KERNEL_RESIDUAL); residual_prog_kernel<<<(unsigned)((n_pad + 63) / 64), 64, 0, c->stream>>>(pp); }
+        CK(cudaGetLastError());
+        ResidPackParams sp;
+        sp.jobs = pp.jobs; sp.job_col = pp.job_col; sp.job_w = pp.job_w; sp.n_slots = g.n_slots;
+        sp.hdr = (EvalHdr*)(jb + o_hdr); sp.ent_col = (int*)(jb + o_ec); sp.ent_w = (double*)(jb + o_ew); sp.meta = (int*)(jb + o_meta);
+        {
+            int n2 = 1;
+            while (n2 < g.n_slots) n2 <<= 1;
+            KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
+            residual_pack_kernel<<<1, 1024, n2 <= SORT_MAX ? (sizeof(unsigned long long) + sizeof(int)) * n2 : 0, c->stream>>>(sp);
+        }
         CK(cudaGetLastError());
         ResidParams p;
         memset(&p, 0, sizeof p);
@@ -2763,7 +2831,7 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
         for (int u = 0; u < p.U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
         p.cols = g.d_cols; p.gfac = g.d_gfac; p.nbuild = g.cp; p.wcol = -1;
         if (b->weighted && b->want_l2) { p.tok[p.U++] = c->weights; p.nbuild = g.cp + 1; p.wcol = g.cp; }
-        p.hdr = pp.hdr; p.ent = pp.ent; p.n_jobs = g.n_jobs; p.n_ent_cap = g.n_ent_cap;
+        p.hdr = sp.hdr; p.ent_col = sp.ent_col; p.ent_w = sp.ent_w; p.meta = sp.meta;
         p.n_slots = g.n_slots; p.tcols = g.d_tcols; p.n_tcols = g.n_tcols;
         p.n_chunks = (int)n_chunks; p.aligned = 1;
         const int nsum = 2 * g.n_slots + g.n_tcols;
@@ -2774,10 +2842,9 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
         p.nstages = (2 * tile_bytes + rest <= (size_t)c->smem_resid) ? 2 : 1;
         size_t smem = p.nstages * tile_bytes + rest + 16;
         if (smem > (size_t)c->smem_resid) return fail("pass B needs %zu bytes of shared memory (> %d)", smem, c->smem_resid);
-        // whatever is left holds a copy of the job descriptors (96 bytes per job + 48 per column entry); the kernel falls
-        // back to global reads when they do not fit
-        p.desc_smem = (int)std::min<size_t>((size_t)c->smem_resid - smem,
-                                            sizeof(EqJobHdr) * (size_t)g.n_jobs + sizeof(ColEnt) * (size_t)g.n_ent_cap + 64);
+        // whatever is left holds a copy of the eval descriptors (headers + an entry per surviving coefficient: at most
+        // 32 + 12 * TMAX bytes per eval, typically ~50); the kernel falls back to global reads when they do not fit
+        p.desc_smem = (int)std::min<size_t>((size_t)c->smem_resid - smem, n_pad * (sizeof(EvalHdr) + 12 * (size_t)TMAX) + 64);
         smem += (size_t)p.desc_smem;
         {
             KernelSpan ks(c, EPDE_KERNEL_RESIDUAL);
