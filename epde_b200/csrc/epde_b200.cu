@@ -810,9 +810,15 @@ struct SolveParams {
     double* all_zero;        // grid sharding (epde_batch_solve_part)
     double* iters;
     int part, nparts;        // this launch solves the evals at list positions part, part + nparts, ...
+    int stage;               // GS = 8: keep a shared-memory copy of the equation's window Grams (dynamic smem sized for it)
 };
 
 #define SOLVE_THREADS 128
+// threads per CTA of lasso_solve_kernel<GS>: systems of <= 8 unknowns (equations of <= 7 terms, the common case) get 256
+// threads = 32 window systems in flight and a shared-memory copy of the window Grams of their equation
+__host__ __device__ constexpr int solve_threads(int gs) { return gs == 8 ? 256 : SOLVE_THREADS; }
+#define SOLVE_STAGE_DIM 9              // GS = 8: T <= 8 terms + the ones column
+#define SOLVE_STAGE_DOUBLES (SOLVE_STAGE_DIM * SOLVE_STAGE_DIM)
 
 __device__ __forceinline__ double nan_to_num(double x) {
     if (isnan(x)) return 0.0;
@@ -821,8 +827,9 @@ __device__ __forceinline__ double nan_to_num(double x) {
 }
 
 template <int GS>
-__global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams p) {
-    constexpr int NG = SOLVE_THREADS / GS;
+__global__ void __launch_bounds__(solve_threads(GS)) lasso_solve_kernel(SolveParams p) {
+    constexpr int NT = solve_threads(GS);
+    constexpr int NG = NT / GS;
     __shared__ double Gt[KS * KS];             // total Gram of all points, symmetric K x K
     __shared__ double M[NG][GS][GS + 1];       // augmented systems
     __shared__ int s_ent[KS * KS];             // (term | ones, term | ones) -> entry of the group's pair table
@@ -843,7 +850,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
     const double* P = p.win + eq.w_off;
     const int* pe = p.pairent + eq.pe_off;
 
-    for (int q = tid; q < (T + 1) * (T + 1); q += SOLVE_THREADS) {
+    for (int q = tid; q < (T + 1) * (T + 1); q += NT) {
         const int i = q / (T + 1), j = q % (T + 1);
         const int en = pe[(int)eq.col[i] * eq.cp + (int)eq.col[j]];
         s_ent[i * KS + j] = en;
@@ -862,6 +869,17 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
     }
     __syncthreads();
 
+    // GS = 8: the (T + 1) x (T + 1) Gram of every window, copied once (every refit solves all W systems again)
+    double* s_win = s_sw + (size_t)W * KS;     // [W][9][9]
+    const bool staged = GS == 8 && p.stage;
+    if (staged) {
+        for (int q = tid; q < W * SOLVE_STAGE_DOUBLES; q += NT) {
+            const int w = q / SOLVE_STAGE_DOUBLES, r = q - w * SOLVE_STAGE_DOUBLES;
+            const int i = r / SOLVE_STAGE_DIM, j = r - i * SOLVE_STAGE_DIM;
+            s_win[q] = (i <= T && j <= T) ? P[(long long)w * NE + s_ent[i * KS + j]] : 0.0;
+        }
+        __syncthreads();
+    }
     const int grp = tid / GS, lr = tid % GS;
     // feature j (0..F-1) <-> term index
     auto feat_term = [&](int j) { return j < tgt ? j : j + 1; };
@@ -879,12 +897,22 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
             double (*Mg)[GS + 1] = M[grp];
             if (lr < n) {
                 const int i = cols[lr];
-                for (int c = 0; c < n; ++c) {
-                    double v = Phi[s_ent[i * KS + cols[c]]];
-                    if (c == lr) v += RIDGE;
-                    Mg[lr][c] = v;
+                if (staged) {
+                    const double* Sw = s_win + (size_t)w * SOLVE_STAGE_DOUBLES + i * SOLVE_STAGE_DIM;
+                    for (int c = 0; c < n; ++c) {
+                        double v = Sw[cols[c]];
+                        if (c == lr) v += RIDGE;
+                        Mg[lr][c] = v;
+                    }
+                    Mg[lr][n] = Sw[tgt];
+                } else {
+                    for (int c = 0; c < n; ++c) {
+                        double v = Phi[s_ent[i * KS + cols[c]]];
+                        if (c == lr) v += RIDGE;
+                        Mg[lr][c] = v;
+                    }
+                    Mg[lr][n] = Phi[s_ent[i * KS + tgt]];
                 }
-                Mg[lr][n] = Phi[s_ent[i * KS + tgt]];
             }
             __syncwarp();
             for (int k = 0; k < n; ++k) {
@@ -920,17 +948,22 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
         }
         __syncthreads();
         // ---------------- column statistics: mean, var(ddof=1), CV (sparsity.py:29-40) ----------
-        if (tid < n) {
+        // one warp per column, lanes stride over the windows, butterfly sums (fixed order)
+        for (int c = tid >> 5; c < n; c += NT / 32) {
+            const int lane = tid & 31;
             double s = 0.0;
-            for (int w = 0; w < W; ++w) s += s_sw[w * KS + tid];
+            for (int w = lane; w < W; w += 32) s += s_sw[w * KS + c];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
             const double mu = s / W;
             double q = 0.0;
-            for (int w = 0; w < W; ++w) { const double dlt = s_sw[w * KS + tid] - mu; q = fma(dlt, dlt, q); }
+            for (int w = lane; w < W; w += 32) { const double dlt = s_sw[w * KS + c] - mu; q = fma(dlt, dlt, q); }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) q += __shfl_xor_sync(0xffffffffu, q, off);
             const double var = q / (W - 1);     // std(ddof=1)**2 ; W == 1 -> nan like numpy
             double cv = var / (mu * mu);
             if (mu == 0.0) cv = 0.0;
-            s_mu[tid] = mu;
-            s_cvraw[tid] = cv;
+            if (lane == 0) { s_mu[c] = mu; s_cvraw[c] = cv; }
         }
         __syncthreads();
         // ---------------- coordinate descent (thread 0) ----------------
@@ -953,35 +986,43 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
             // after a refit the reference finishes the interrupted sweep's bookkeeping:
             // max_change = inf fails criterion 1, then iteration += 1  (sparsity.py:96-150)
             if (first_pass_after_refit) iteration = 1;
-            auto all_zero = [&]() { for (int j = 0; j < F; ++j) if (s_coef[j] != 0.0) return false; return true; };
+            // Within one fit the intercept, the CVs and the SET of non-zero coefficients are fixed (a coefficient that
+            // reaches zero ends the fit at once), so everything that depends only on them is computed once per fit:
+            // the visiting order argsort(cv)[::-1] (descending CV, ties -> higher index first) restricted to the
+            // non-zero coefficients, y_sq_sum and the thresholds.  Skipped zero coefficients contribute exact zeros
+            // to every sum of the reference, so the values are unchanged.
+            int act[TMAX], na = 0;
+            for (int j = 0; j < F; ++j)
+                if (s_coef[j] != 0.0) act[na++] = j;
+            for (int a = 1; a < na; ++a) {
+                const int oj = act[a];
+                const double cvj = s_cv[oj];
+                int b2 = a - 1;
+                while (b2 >= 0 && (s_cv[act[b2]] < cvj || (s_cv[act[b2]] == cvj && act[b2] < oj))) {
+                    act[b2 + 1] = act[b2];
+                    --b2;
+                }
+                act[b2 + 1] = oj;
+            }
+            const double y_sq_sum = yy - 2.0 * s_b * sy + Npts * s_b * s_b;
             auto xt_res = [&](int j) {
                 const int tj = feat_term(j);
                 double s = Gt[tj * KS + tgt];
-                for (int k2 = 0; k2 < F; ++k2) s = fma(-Gt[tj * KS + feat_term(k2)], s_coef[k2], s);
+                // ascending feature index, as the reference's dot product runs
+                for (int k2 = 0; k2 < F; ++k2) {
+                    const double ck = s_coef[k2];
+                    if (ck != 0.0) s = fma(-Gt[tj * KS + feat_term(k2)], ck, s);
+                }
                 return fma(-s_b, Gt[tj * KS + T], s);
             };
-            while (iteration < LASSO_MAX_ITER && !all_zero()) {
+            while (iteration < LASSO_MAX_ITER && na > 0) {
                 ++s_sweeps;
                 double max_change = 0.0;
-                // order = argsort(cv)[::-1]: descending CV, ties -> higher index first
-                int order[TMAX];
-                for (int j = 0; j < F; ++j) order[j] = j;
-                for (int a = 1; a < F; ++a) {
-                    const int oj = order[a];
-                    int b2 = a - 1;
-                    while (b2 >= 0 && (s_cv[order[b2]] < s_cv[oj] || (s_cv[order[b2]] == s_cv[oj] && order[b2] < oj))) {
-                        order[b2 + 1] = order[b2];
-                        --b2;
-                    }
-                    order[b2 + 1] = oj;
-                }
-                for (int q = 0; q < F; ++q) {
-                    const int j = order[q];
+                for (int q = 0; q < na; ++q) {
+                    const int j = act[q];
                     const double old_coef = s_coef[j];
-                    if (old_coef == 0.0) continue;
                     const int tj = feat_term(j);
                     const double norm_sq = Gt[tj * KS + tj];
-                    const double y_sq_sum = yy - 2.0 * s_b * sy + Npts * s_b * s_b;
                     const double rho = xt_res(j) + old_coef * norm_sq;
                     const double thr = s_cv[j] * y_sq_sum;
                     const double mag = fmax(fabs(rho) - thr, 0.0);
@@ -994,9 +1035,8 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
                 }
                 if (refit) break;
                 double max_abs = 0.0;
-                for (int j = 0; j < F; ++j) max_abs = fmax(max_abs, fabs(s_coef[j]));
+                for (int q = 0; q < na; ++q) max_abs = fmax(max_abs, fabs(s_coef[act[q]]));
                 if (max_change <= LASSO_TOL * max_abs) {
-                    const double y_sq_sum = yy - 2.0 * s_b * sy + Npts * s_b * s_b;
                     double dual_norm = 0.0;
                     for (int j = 0; j < F; ++j)
                         if (s_cv[j] * y_sq_sum > 0.0)
@@ -1046,7 +1086,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) lasso_solve_kernel(SolveParams 
     }
     __syncthreads();
     const int n = (mode == 2) ? 0 : s_n;
-    for (int q = tid; q < W * KS; q += SOLVE_THREADS) {
+    for (int q = tid; q < W * KS; q += NT) {
         const int c = q % KS;
         p.sw[(long long)ev * W * KS + q] = (c < n) ? s_sw[q] : 0.0;
     }
@@ -1907,10 +1947,13 @@ struct FdParams {
     double dx_first, dx_last;    // end spacings
 };
 
+// I = unsigned when the tensor has fewer than 2^31 elements: the per-element index arithmetic (two divisions) is what
+// these elementwise kernels spend their instructions on, and 64-bit division costs ~5x the 32-bit one
+template <typename I>
 __global__ void __launch_bounds__(256) fd_gradient_kernel(FdParams p) {
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < p.total;
-         idx += (long long)gridDim.x * blockDim.x) {
-        const int i = (int)((idx / p.stride) % p.n);
+    const I total = (I)p.total, stride = (I)p.stride, n = (I)p.n, step = (I)gridDim.x * (I)blockDim.x;
+    for (I idx = (I)blockIdx.x * (I)blockDim.x + (I)threadIdx.x; idx < total; idx += step) {
+        const int i = (int)((idx / stride) % n);
         double v;
         if (i == 0) {
             v = __ddiv_rn(__dsub_rn(p.in[idx + p.stride], p.in[idx]), p.dx_first);
@@ -1936,14 +1979,16 @@ struct CropParams {
     long long inner[EPDE_MAX_NDIM], full_stride[EPDE_MAX_NDIM], off[EPDE_MAX_NDIM];
 };
 
+template <typename I>
 __global__ void __launch_bounds__(256) crop_interior_kernel(CropParams p) {
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < p.n_inner;
-         idx += (long long)gridDim.x * blockDim.x) {
-        long long rem = idx, src = 0;
+    const I total = (I)p.n_inner, step = (I)gridDim.x * (I)blockDim.x;
+    for (I idx = (I)blockIdx.x * (I)blockDim.x + (I)threadIdx.x; idx < total; idx += step) {
+        I rem = idx, src = 0;
         for (int d = p.ndim - 1; d >= 0; --d) {
-            const long long q = rem % p.inner[d];
-            rem /= p.inner[d];
-            src += (q + p.off[d]) * p.full_stride[d];
+            const I in_d = (I)p.inner[d];
+            const I q = rem % in_d;
+            rem /= in_d;
+            src += (q + (I)p.off[d]) * (I)p.full_stride[d];
         }
         p.out[idx] = p.in[src];
     }
@@ -1967,9 +2012,11 @@ struct PolyParams {
     int n, window, bound, order;
 };
 
+template <typename I>
 __global__ void __launch_bounds__(256) poly_derivative_kernel(PolyParams p) {
-    for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < p.total; q += (long long)gridDim.x * blockDim.x) {
-        const int i = (int)((q / p.stride) % p.n);
+    const I total = (I)p.total, stride = (I)p.stride, np_ = (I)p.n, step = (I)gridDim.x * (I)blockDim.x;
+    for (I q = (I)blockIdx.x * (I)blockDim.x + (I)threadIdx.x; q < total; q += step) {
+        const int i = (int)((q / stride) % np_);
         const double* c = p.in + q;
         double v;
         if (i >= p.bound && i <= p.n - p.bound) {
@@ -2728,12 +2775,17 @@ static int solve_impl(epde_batch* b, const double* dev_seg, int part, int nparts
         sp.mode = b->d_mode; sp.given_wterm = b->d_given_w; sp.given_b = b->d_given_b;
         sp.coef = b->d_coef; sp.intercept = b->d_intercept; sp.intercept_l1 = b->d_b1; sp.stability = b->d_stab; sp.sw = b->d_sw;
         sp.wterm = b->d_wterm; sp.n_active = b->d_nact; sp.all_zero = b->d_allzero; sp.iters = b->d_iters;
-        sp.part = part; sp.nparts = nparts;
+        sp.part = part; sp.nparts = nparts; sp.stage = 0;
         auto mine = [&](size_t n) { return (unsigned)((n > (size_t)part) ? (n - part + nparts - 1) / nparts : 0); };
         const size_t smem = sizeof(double) * (size_t)c->geom.n_windows * KS;
         if (mine(b->evals_gs8.size()) > 0) {
             sp.eval_list = b->d_lists + b->off_gs8;
-            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<8><<<mine(b->evals_gs8.size()), SOLVE_THREADS, smem, c->stream>>>(sp); }
+            // the staged copy of the window Grams pays when the launch is latency-bound (few CTAs) or when it still
+            // leaves room for three CTAs per SM; a large batch on a 3-D grid (W ~ 100) prefers the occupancy
+            const size_t stage_bytes = sizeof(double) * (size_t)c->geom.n_windows * SOLVE_STAGE_DOUBLES;
+            sp.stage = (mine(b->evals_gs8.size()) <= 2u * (unsigned)c->sm_count || smem + stage_bytes <= 40 * 1024) ? 1 : 0;
+            { KernelSpan ks(c, EPDE_KERNEL_SOLVE); lasso_solve_kernel<8><<<mine(b->evals_gs8.size()), solve_threads(8), smem + (sp.stage ? stage_bytes : 0), c->stream>>>(sp); }
+            sp.stage = 0;
             CK(cudaGetLastError());
         }
         if (mine(b->evals_gs16.size()) > 0) {
@@ -2964,7 +3016,8 @@ int epde_fd_gradient(epde_ctx* c, const double* dev_in, double* dev_out, int ndi
     }
     const int grid = (int)std::min<long long>((p.total + 255) / 256, (long long)c->sm_count * 16);
     c->launches++;
-    fd_gradient_kernel<<<grid, 256, 0, c->stream>>>(p);
+    if (p.total < (1ll << 31)) fd_gradient_kernel<unsigned><<<grid, 256, 0, c->stream>>>(p);
+    else fd_gradient_kernel<long long><<<grid, 256, 0, c->stream>>>(p);
     CK(cudaGetLastError());
     return 0;
 }
@@ -2993,7 +3046,8 @@ int epde_poly_derivative(epde_ctx* c, const double* dev_in, double* dev_out, int
     p.w = (const double*)c->d_fd.ptr; p.x = (const double*)((char*)c->d_fd.ptr + wbytes);
     const int grid = (int)std::min<long long>((p.total + 255) / 256, (long long)c->sm_count * 16);
     c->launches++;
-    poly_derivative_kernel<<<grid, 256, 0, c->stream>>>(p);
+    if (p.total < (1ll << 31)) poly_derivative_kernel<unsigned><<<grid, 256, 0, c->stream>>>(p);
+    else poly_derivative_kernel<long long><<<grid, 256, 0, c->stream>>>(p);
     CK(cudaGetLastError());
     return 0;
 }
@@ -3056,7 +3110,8 @@ int epde_poly_derivative_noalloc(epde_ctx* c, const double* dev_in, double* dev_
     p.w = scratch; p.x = scratch + (size_t)n * window;
     const int grid = (int)std::min<long long>((p.total + 255) / 256, (long long)c->sm_count * 16);
     c->launches++;
-    poly_derivative_kernel<<<grid, 256, 0, c->stream>>>(p);
+    if (p.total < (1ll << 31)) poly_derivative_kernel<unsigned><<<grid, 256, 0, c->stream>>>(p);
+    else poly_derivative_kernel<long long><<<grid, 256, 0, c->stream>>>(p);
     CK(cudaGetLastError());
     return 0;
 }
@@ -3083,7 +3138,8 @@ int epde_cache_upload_interior(epde_ctx* c, int id, const double* dev_full, int 
     p.out = tok;
     const int grid = (int)std::min<long long>((c->N + 255) / 256, (long long)c->sm_count * 16);
     c->launches++;
-    crop_interior_kernel<<<grid, 256, 0, c->stream>>>(p);
+    if (stride < (1ll << 31)) crop_interior_kernel<unsigned><<<grid, 256, 0, c->stream>>>(p);      // stride = full-grid size here
+    else crop_interior_kernel<long long><<<grid, 256, 0, c->stream>>>(p);
     CK(cudaGetLastError());
     return 0;
 }

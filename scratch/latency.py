@@ -17,6 +17,7 @@ for cfg, neq in [('wave61', 1), ('wave61', 8), ('burgers156', 1), ('burgers156',
             eng.evaluate(enc)
         dt = (time.perf_counter() - t0) / 50
         eng.set_timing(True)
-        eng.evaluate(enc)
+        res = eng.evaluate(enc)
         kt = eng.kernel_times()
+    print(f'{cfg} {neq} eq / {len(evals)} evals: sweeps {np.asarray(res.iters).tolist()[:8]} active {np.asarray(res.n_active).tolist()[:8]}')
     print(f'{cfg} {neq} eq / {len(evals)} evals: {dt * 1e6:.0f} us per call; kernels {dict((k, round(v[0] * 1e3)) for k, v in kt.items())} us')

@@ -47,3 +47,16 @@ def test_slab_tokens_equal_rows_of_the_whole_grid():
     part = syn.make_tokens(shape, 'heat', seed=5, axis0_range=(7, 24))
     for f, p in zip(full, part):
         assert np.array_equal(f[7 * row:], p)
+
+
+def test_distinct_population_is_bounded_and_shares_nothing():
+    """the all-distinct stress population (bench --population distinct): generation is a bounded deal from the
+    enumerated term pools (the round-1 rejection loop never ended for 128 equations over 7 tokens), no term appears
+    twice, every equation has an admissible target."""
+    from epde_b200 import synthetic as syn
+    for n_tokens, pop, seed in ((7, 128, 5), (7, 48, 2), (5, 96, 1)):
+        eqs = syn.make_population_distinct(n_tokens, pop, seed=seed)
+        terms = [frozenset(t) for eq in eqs for t in eq]
+        assert len(eqs) == pop and len(set(terms)) == len(terms)
+        assert all(3 <= len(eq) <= 7 and syn.admissible_targets(eq) for eq in eqs)
+        assert eqs == syn.make_population_distinct(n_tokens, pop, seed=seed)
