@@ -204,6 +204,16 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
                  : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
+// x / d for 0 <= x < 2^24, d >= 1, through a float reciprocal and one correction step (the producers of pass A locate
+// 4 points per lane and chunk: two runtime integer divisions each were 14 % of the kernel's instructions)
+__device__ __forceinline__ int small_div(int x, int d, float inv_d) {
+    int q = __float2int_rz((float)x * inv_d);
+    const int rem = x - q * d;
+    q += (rem >= d) ? 1 : 0;
+    q -= (rem < 0) ? 1 : 0;
+    return q;
+}
+
 // ------------------------------------------------------------------------------------------
 // factor / term evaluation (factor.py:218-269, evaluators.py:92-151)
 // ------------------------------------------------------------------------------------------
@@ -486,6 +496,7 @@ __global__ void __launch_bounds__(GRAM_MAX_THREADS, 1) gram_dmma_kernel(const __
             unsigned tile_a = smem_addr(tiles + (size_t)st * p.U * tstride);
             asm volatile("mov.u32 %0, %0;" : "+r"(tile_a) :: "memory");
             const int wb = u.b_hi - u.b_lo;
+            const float inv_wb = 1.0f / (float)wb;
             const int nrows = (u.a_hi - u.a_lo) * wb;
             const int shift = u.col_lo & 1;
             for (int q = 0; q < u.npieces; ++q) {
@@ -493,6 +504,7 @@ __global__ void __launch_bounds__(GRAM_MAX_THREADS, 1) gram_dmma_kernel(const __
                 const int pw = p.g.piece_start[u.piece_lo + q + 1] - ps;
                 const int c_lo = ps - u.col_lo + shift;
                 const int npts = nrows * pw;
+                const float inv_pw = 1.0f / (float)pw;
                 for (int c0 = 0; c0 < npts; c0 += PT_A, ++chunk) {
                     const int bf = chunk & 1;
                     int toffb[PT_A / 32];
@@ -501,8 +513,8 @@ __global__ void __launch_bounds__(GRAM_MAX_THREADS, 1) gram_dmma_kernel(const __
                     for (int k = 0; k < PT_A / 32; ++k) {
                         const int pi = c0 + lane + 32 * k;
                         valid[k] = pi < npts;
-                        const int r = pi / pw;
-                        const int ra = r / wb;
+                        const int r = small_div(pi, pw, inv_pw);
+                        const int ra = small_div(r, wb, inv_wb);
                         toffb[k] = valid[k] ? (((ra * p.box_b + (r - ra * wb)) * p.box_c + c_lo + (pi - r * pw)) * 8) : 0;
                     }
                     bar_sync(BAR_EMPTY + bf, nthreads);                  // consumers are done with this buffer
@@ -1417,11 +1429,13 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
         __syncthreads();
 
         const unsigned cl = ct + lane * 8;
+        // the next job number is drawn while the current job runs (lane 0 holds it; broadcast at the top of the loop)
+        int jj_next = 0;
+        if (lane == 0) jj_next = atomicAdd(&s_next, 1);
         for (;;) {
-            int jj = 0;
-            if (lane == 0) jj = atomicAdd(&s_next, 1);
-            jj = __shfl_sync(0xffffffffu, jj, 0);
+            const int jj = __shfl_sync(0xffffffffu, jj_next, 0);
             if (jj >= njobs_all) break;
+            if (lane == 0) jj_next = atomicAdd(&s_next, 1);
             if (jj < n_oct) {
                 // ---------------- octet job: evals [8 jj, 8 jj + 8) of the list (padding evals: nnz 0, sums discarded)
                 // descriptors are fetched up front, spread over the lanes (lane v: header of eval v; lane z: entry z of

@@ -112,13 +112,16 @@ def chebyshev_window_weights(coords, order, window=9, n_der=None, poly_order=Non
     for i in range(bound, n - bound + 1):
         xr = x[i - h:i + h + 1]
         key = tuple(np.round((xr - xr[0]) / (xr[-1] - xr[0]), 14))     # equal relative spacing -> same fit up to scale
+        span = float(xr[-1] - xr[0])
         ref = cache.get(key)
-        if ref is not None and ref[1] == (float(xr[0]), float(xr[-1])):
-            W[i] = ref[0]
+        if ref is not None:
+            # Chebyshev.fit works on the window mapped to [-1, 1]: windows with the same relative spacing have the same
+            # fit, and the order-th derivative scales with (1 / span) ** order (a uniform axis needs ONE fit, not n)
+            W[i] = ref[0] if ref[1] == span else ref[0] * (ref[1] / span) ** int(order)
             continue
         row = np.array([Chebyshev.fit(xr, eye[j], deg).deriv(m=int(order))(xr[int(xr.size / 2.)]) for j in range(window)])
         W[i] = row
-        cache[key] = (row, (float(xr[0]), float(xr[-1])))
+        cache[key] = (row, span)
     return W
 
 
