@@ -172,6 +172,32 @@ def measured_traffic(workload, kernel, world, pop_override):
         return None
 
 
+def single_call_latency(device, calls=50):
+    """wall time of ONE small Engine.evaluate call -- what a per-equation operator call (EqRightPartSelector.apply on
+    one equation: its D admissible targets as one batch) pays on a config-1 sized grid (61 x 61), host encodings in,
+    host results out; median of `calls` after a warm-up."""
+    import epde_b200
+    from epde_b200 import synthetic as syn
+    shape, _, kind = syn.CONFIGS['wave61']
+    tokens = syn.make_tokens(shape, kind, seed=1)
+    eqs = syn.make_population(len(tokens), 1, seed=1, t_fresh=(6, 6), pruned_fraction=0.0)
+    evals = syn.make_evals(eqs)
+    enc = epde_b200.encode(eqs, evals)
+    with epde_b200.Engine(shape, device=device) as eng:
+        for i, t in enumerate(tokens):
+            eng.upload(i, t)
+        for _ in range(5):
+            eng.evaluate(enc)
+        ts = []
+        for _ in range(calls):
+            t0 = time.perf_counter()
+            eng.evaluate(enc)
+            ts.append(time.perf_counter() - t0)
+    return {'single_equation_call_us': float(np.median(ts) * 1e6), 'grid': 'x'.join(str(n) for n in shape),
+            'terms': len(eqs[0]), 'evals': len(evals), 'calls': calls,
+            'note': 'Engine.evaluate of one 6-term equation (all admissible targets), median wall time per call'}
+
+
 # ------------------------------------------------------------------------------------------
 # CPU side: the oracle port (numpy, all host cores through BLAS) -- ONLY the cpu_baseline leg and
 # the --impl reference arm may execute oracle/.
@@ -558,11 +584,18 @@ def run_b200(args):
                            '(+ the cell table) and HBM is far from binding'}
             if hbm['dram_gbs_measured']:
                 hbm['dram_frac'] = hbm['dram_gbs_measured'] / hbm_peak
-            return {'bound': bound, 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak if peak else None,
-                    'traffic': traffic, 'kernel': names[kind], 'peak_source': src, 'launches_per_step': int(n),
-                    'kernel_ms_per_step': ms, 'flop_per_step_executed': flops[kind]['executed'],
-                    'flop_per_step_useful': flops[kind]['useful'], 'useful_tflops': useful,
-                    'useful_frac': useful / peak if peak else None, 'hbm': hbm}
+            out = {'bound': bound, 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak if peak else None,
+                   'traffic': traffic, 'kernel': names[kind], 'peak_source': src, 'launches_per_step': int(n),
+                   'kernel_ms_per_step': ms, 'flop_per_step_executed': flops[kind]['executed'],
+                   'flop_per_step_useful': flops[kind]['useful'], 'useful_tflops': useful,
+                   'useful_frac': useful / peak if peak else None, 'hbm': hbm}
+            # pipe utilisations of the committed ncu --set full capture of this configuration (NOT measured in this
+            # run): which on-chip resource binds the kernel
+            ncu = measured_traffic(args.workload, kind + ':ncu', world,
+                                   args.pop or args.population != 'default' or args.norms != 'l1')
+            if ncu:
+                out['ncu_capture'] = ncu
+            return out
 
         dominant = 'residual' if ktimes['residual'][0] >= ktimes['gram'][0] else 'gram'
         other = 'gram' if dominant == 'residual' else 'residual'
@@ -587,6 +620,8 @@ def run_b200(args):
             'kernel_ms_per_step': {k: v[0] for k, v in ktimes.items()},
             'kernel_ms_per_step_by_rank': rank_ms,
         }
+        if world == 1:
+            line['latency'] = single_call_latency(local_rank)
         if world == 1 and not args.no_cpu_baseline:
             host_tokens = [eng.download(i) for i in range(n_tok)]
             # the host upload path an EPDE run would use (epde_cache_upload: pageable host memory -> HBM), timed once
