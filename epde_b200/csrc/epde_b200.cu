@@ -114,8 +114,8 @@ struct ColDesc {             // 32 bytes; one distinct term of a launch group = 
     int off[MAXSF];          // fast column: token slots of the expanded factors (u^2 * v -> u, u, v), -1 = none; the
                              // kernels scale them to byte offsets of the slot inside a token tile when staging
     short nf;                // number of expanded factors (fast) / factors (generic)
-    short kind;              // 0 fast, 1 generic, 2 ones column, 3 padding (all zero)
-    int gfac_off;            // generic: first factor in the group's factor array
+    short kind;              // 0 fast, 1 generic, 2 ones column, 3 padding (all zero), 4 product of <= 4 integer powers
+    int gfac_off;            // generic: first factor in the group's factor array; kind 4: the powers, 8 bits each
 };
 static_assert(sizeof(ColDesc) == 32, "ColDesc is copied as int4 pairs");
 
@@ -309,6 +309,30 @@ __device__ __forceinline__ void build_columns(unsigned ct, int ppb, unsigned col
                 const FactorDesc fd = gfac[q1.w + f];
 #pragma unroll
                 for (int k = 0; k < NPL; ++k) v[k] *= apply_factor(fd, lds_f64_e(tile + fd.slot * tstride_b + toffb[k], epoch));
+            }
+        } else if (kind == 4) {
+            // product of up to 4 token values raised to integer powers that do not fit the expanded form (u^5 * v^4):
+            // slots in off[0..3], powers in gfac_off; powers by squaring, everything warp-uniform, no global loads
+#pragma unroll
+            for (int k = 0; k < NPL; ++k) v[k] = 1.0;
+            for (int f = 0; f < nf; ++f) {
+                const int o = (f == 0) ? q0.x : (f == 1) ? q0.y : (f == 2) ? q0.z : q0.w;
+                const int pw = (q1.w >> (8 * f)) & 0xff;
+                double x[NPL];
+#pragma unroll
+                for (int k = 0; k < NPL; ++k) x[k] = lds_f64_e(tile + o + toffb[k], epoch);
+                if (pw & 1) {
+#pragma unroll
+                    for (int k = 0; k < NPL; ++k) v[k] *= x[k];
+                }
+                for (int e = pw >> 1; e; e >>= 1) {
+#pragma unroll
+                    for (int k = 0; k < NPL; ++k) x[k] *= x[k];
+                    if (e & 1) {
+#pragma unroll
+                        for (int k = 0; k < NPL; ++k) v[k] *= x[k];
+                    }
+                }
             }
         } else {
 #pragma unroll
@@ -2434,7 +2458,21 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
                 for (int q = 0; q < ip; ++q) { if (nsf < MAXSF) cd.off[nsf] = slot[fac_token[f]]; ++nsf; }
             }
             if (nsf > MAXSF) fast = false;
+            // plain integer powers that do not fit the expanded form: (slot, power) pairs, all in the descriptor
+            bool powprod = !fast && (fac_off[t + 1] - fac_off[t]) <= 4;
+            for (int f = fac_off[t]; powprod && f < fac_off[t + 1]; ++f) {
+                const double pw = fac_power[f];
+                if ((fac_kind ? fac_kind[f] : 0) != 0 || !(pw >= 1.0 && pw <= 255.0 && pw == (double)(int)pw)) powprod = false;
+            }
             if (fast) { cd.kind = 0; cd.nf = (short)nsf; }
+            else if (powprod) {
+                cd.kind = 4; cd.nf = (short)(fac_off[t + 1] - fac_off[t]); cd.gfac_off = 0;
+                for (int q = 0; q < MAXSF; ++q) cd.off[q] = -1;
+                for (int f = fac_off[t], q = 0; f < fac_off[t + 1]; ++f, ++q) {
+                    cd.off[q] = slot[fac_token[f]];
+                    cd.gfac_off |= (int)fac_power[f] << (8 * q);
+                }
+            }
             else {
                 cd.kind = 1; cd.nf = (short)(fac_off[t + 1] - fac_off[t]); cd.gfac_off = (int)gfac.size();
                 for (int f = fac_off[t]; f < fac_off[t + 1]; ++f) {
