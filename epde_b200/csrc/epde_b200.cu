@@ -271,11 +271,16 @@ __device__ __forceinline__ void load_cols_to_smem(ColDesc* s_cols, const ColDesc
     }
 }
 
-template <int NPL>
+template <int NPL, bool LISTED = false>
 __device__ __forceinline__ void build_columns(unsigned ct, int ppb, unsigned cols, int nbuild, const FactorDesc* gfac,
                                               unsigned tile, int tstride_b, const int (&toffb)[NPL],
-                                              const bool (&valid)[NPL], int warp, int nwarps, int lane, int epoch) {
-    for (int c = warp; c < nbuild; c += nwarps) {
+                                              const bool (&valid)[NPL], int warp, int nwarps, int lane, int epoch,
+                                              unsigned list = 0) {
+    // LISTED: `list` = shared-memory address of the nbuild column numbers to build (pass B builds only the columns
+    // some eval reads); otherwise all columns 0 .. nbuild - 1
+    for (int ci = warp; ci < nbuild; ci += nwarps) {
+        int c = ci;
+        if (LISTED) asm volatile("ld.shared.s32 %0, [%1];" : "=r"(c) : "r"(list + ci * 4));
         const int4 q0 = lds_v4(cols + c * 32), q1 = lds_v4(cols + c * 32 + 16);
         const int nf = q1.z & 0xffff, kind = q1.z >> 16;
         double v[NPL];
@@ -1229,12 +1234,31 @@ struct ResidPackParams {
     EvalHdr* hdr;            // [n_slots rounded up to OCT] in walking order
     int* ent_col;            // [sum nnz]
     double* ent_w;           // [sum nnz]
-    int* meta;               // [0] = sum nnz
+    int* meta;               // [0] = sum nnz, [1] = number of columns in blist
+    int* blist;              // [nbuild] columns of the dictionary that some eval reads (targets, surviving terms, weights)
+    int nbuild, wcol;
     int n_slots;
 };
 
 __global__ void __launch_bounds__(1024) residual_pack_kernel(ResidPackParams p) {
     extern __shared__ unsigned long long s_key[];          // n2 keys, then n2 ints (scan)
+    // columns pass B has to build: after the LASSO most columns of the dictionary survive in no eval
+    __shared__ int s_need[CMAX + 8];
+    for (int q = threadIdx.x; q < p.nbuild; q += blockDim.x) s_need[q] = 0;
+    __syncthreads();
+    for (int q = threadIdx.x; q < p.n_slots; q += blockDim.x) {
+        const EvalJob j = p.jobs[q];
+        s_need[j.tcol / (PP_B * 8)] = 1;
+        for (int z = 0; z < j.nnz; ++z) s_need[p.job_col[(long long)q * TMAX + z] / (PP_B * 8)] = 1;
+    }
+    if (threadIdx.x == 0 && p.wcol >= 0) s_need[p.wcol] = 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int nb = 0;
+        for (int c = 0; c < p.nbuild; ++c)
+            if (s_need[c]) p.blist[nb++] = c;
+        p.meta[1] = nb;
+    }
     const int n_pad = (p.n_slots + OCT - 1) / OCT * OCT;
     int n2 = 1;
     while (n2 < p.n_slots) n2 <<= 1;
@@ -1319,7 +1343,8 @@ struct ResidParams {
     const EvalHdr* hdr;      // [n_slots rounded up to OCT] in walking order (residual_pack_kernel)
     const int* ent_col;      // CSR entries: byte offsets of the surviving columns' rows in the column tile
     const double* ent_w;
-    const int* meta;         // [0] = number of entries
+    const int* meta;         // [0] = number of entries, [1] = number of columns to build
+    const int* blist;        // columns to build (residual_pack_kernel)
     int wcol;                // weighted mode: row of the column tile that holds the sample weights g (L2Fitness multiplies
                              // its residual by g, fitness.py:81-82), else -1
     int desc_smem;           // bytes of shared memory available for a copy of the descriptors (0: read them from global)
@@ -1387,8 +1412,11 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ uint64_t s_bar[2];
     __shared__ int s_next;
+    __shared__ int s_blist[CMAX + 8];
     const int tid = threadIdx.x, nthreads = blockDim.x;
     const int warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
+    const int n_blist = p.meta[1];
+    for (int q = tid; q < n_blist; q += nthreads) s_blist[q] = p.blist[q];
     double* tiles = (double*)smem_raw;                                        // [nstages][U][PT_B]
     double* ctp = tiles + (size_t)p.nstages * p.U * PT_B;                     // [nbuild][PP_B]
     ColDesc* s_cols = (ColDesc*)(ctp + (size_t)p.nbuild * PP_B);              // [nbuild]
@@ -1447,7 +1475,8 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 1) residual_cols_kernel(ResidP
             for (int k = 0; k < RES_NPL; ++k) { valid[k] = lane + 32 * k < npts; toffb[k] = valid[k] ? (lane + 32 * k) * 8 : 0; }
             unsigned tile_a = smem_addr(tile);
             asm volatile("mov.u32 %0, %0;" : "+r"(tile_a) :: "memory");     // defined after the wait: see gram_dmma_kernel
-            build_columns<RES_NPL>(ct, PP_B * 8, cols_a, p.nbuild, p.gfac, tile_a, PT_B * 8, toffb, valid, warp, nwarps, lane, (int)ci);
+            build_columns<RES_NPL, true>(ct, PP_B * 8, cols_a, n_blist, p.gfac, tile_a, PT_B * 8, toffb, valid, warp, nwarps, lane, (int)ci,
+                                         smem_addr(s_blist));
         }
         if (tid == 0) s_next = 0;
         __syncthreads();
@@ -2910,7 +2939,7 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
         const size_t o_col = align(sizeof(EvalJob) * n_pad), o_w = align(o_col + sizeof(int) * n_pad * TMAX),
                      o_hdr = align(o_w + sizeof(double) * n_pad * TMAX), o_ec = align(o_hdr + sizeof(EvalHdr) * n_pad),
                      o_ew = align(o_ec + sizeof(int) * n_pad * TMAX), o_meta = align(o_ew + sizeof(double) * n_pad * TMAX),
-                     tot = align(o_meta + 64);
+                     o_bl = o_meta + 64, tot = align(o_bl + sizeof(int) * (CMAX + 8));
         if (c->d_jobs.ensure(tot)) return 1;
         char* jb = (char*)c->d_jobs.ptr;
         ResidProgParams pp;
@@ -2922,6 +2951,9 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
         ResidPackParams sp;
         sp.jobs = pp.jobs; sp.job_col = pp.job_col; sp.job_w = pp.job_w; sp.n_slots = g.n_slots;
         sp.hdr = (EvalHdr*)(jb + o_hdr); sp.ent_col = (int*)(jb + o_ec); sp.ent_w = (double*)(jb + o_ew); sp.meta = (int*)(jb + o_meta);
+        sp.blist = (int*)(jb + o_bl);
+        sp.wcol = (b->weighted && b->want_l2) ? g.cp : -1;
+        sp.nbuild = g.cp + (sp.wcol >= 0 ? 1 : 0);
         {
             int n2 = 1;
             while (n2 < g.n_slots) n2 <<= 1;
@@ -2935,7 +2967,7 @@ int epde_batch_residual(epde_batch* b, double* dev_sums) {
         for (int u = 0; u < p.U; ++u) p.tok[u] = c->tokens[g.token_ids[u]];
         p.cols = g.d_cols; p.gfac = g.d_gfac; p.nbuild = g.cp; p.wcol = -1;
         if (b->weighted && b->want_l2) { p.tok[p.U++] = c->weights; p.nbuild = g.cp + 1; p.wcol = g.cp; }
-        p.hdr = sp.hdr; p.ent_col = sp.ent_col; p.ent_w = sp.ent_w; p.meta = sp.meta;
+        p.hdr = sp.hdr; p.ent_col = sp.ent_col; p.ent_w = sp.ent_w; p.meta = sp.meta; p.blist = sp.blist;
         p.n_slots = g.n_slots; p.tcols = g.d_tcols; p.n_tcols = g.n_tcols;
         p.n_chunks = (int)n_chunks; p.aligned = 1;
         const int nsum = 2 * g.n_slots + g.n_tcols;
