@@ -73,7 +73,9 @@
 #define TASK_A 2               // a pass-A task covers TASK_A x TASK_B block pairs
 #define TASK_B 3
 #define GRAM_MAX_WARPS 12     // consumer (tensor-core) warps of pass A
+#ifndef GRAM_PROD_WARPS
 #define GRAM_PROD_WARPS 10     // producer (term assembly) warps of pass A (fewer when the consumers need the slots)
+#endif
 #define GRAM_MAX_THREADS 704
 #define PT_B 256               // points per pass-B chunk
 #define PP_B (PT_B + 4)
