@@ -2465,6 +2465,50 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
         g.token_ids.assign(g_tok[gi].begin(), g_tok[gi].end());
         std::map<int, int> slot;
         for (size_t u = 0; u < g.token_ids.size(); ++u) slot[g.token_ids[u]] = (int)u;
+        // Column order: pass A computes whole 8 x 8 blocks of column pairs, and a block pair is needed as soon as one
+        // equation has a column in each block, so columns that occur together should share a block.  Greedy fill: a
+        // block is seeded with the unplaced column that co-occurs most with the other unplaced ones and takes, 7 times,
+        // the unplaced column that shares the most equations with it (~10 % fewer block pairs than first-appearance
+        // order on the bench populations; a 20 000-step local search finds 25 % but costs tens of ms on the host).
+        if (g.col_term.size() > 8) {
+            const int n = (int)g.col_term.size();
+            std::map<int, int> idx;
+            for (int k = 0; k < n; ++k) idx[g.col_term[k]] = k;
+            std::vector<int> co((size_t)n * n, 0);
+            for (int e : g.eqs) {
+                std::vector<int> cs;
+                for (int t = term_off[e]; t < term_off[e + 1]; ++t) cs.push_back(idx[term_of[t]]);
+                for (int a : cs) for (int bb : cs) if (a != bb) co[(size_t)a * n + bb]++;
+            }
+            std::vector<char> placed(n, 0);
+            std::vector<int> order_c;
+            while ((int)order_c.size() < n) {
+                int seed = -1; long best = -1;
+                for (int cidx = 0; cidx < n; ++cidx) {
+                    if (placed[cidx]) continue;
+                    long sc = 0;
+                    for (int u = 0; u < n; ++u) if (!placed[u]) sc += co[(size_t)cidx * n + u];
+                    if (sc > best) { best = sc; seed = cidx; }
+                }
+                std::vector<int> blk{seed};
+                placed[seed] = 1;
+                while (blk.size() < 8 && (int)(order_c.size() + blk.size()) < n) {
+                    int nxt = -1; long bsc = -1;
+                    for (int cidx = 0; cidx < n; ++cidx) {
+                        if (placed[cidx]) continue;
+                        long sc = 0;
+                        for (int q : blk) sc += co[(size_t)cidx * n + q];
+                        if (sc > bsc) { bsc = sc; nxt = cidx; }
+                    }
+                    blk.push_back(nxt);
+                    placed[nxt] = 1;
+                }
+                order_c.insert(order_c.end(), blk.begin(), blk.end());
+            }
+            std::vector<int> re(n);
+            for (int k = 0; k < n; ++k) re[k] = g.col_term[order_c[k]];
+            g.col_term.swap(re);
+        }
         std::map<int, int> col_of;
         for (size_t k = 0; k < g.col_term.size(); ++k) col_of[g.col_term[k]] = (int)k;
         const int ones = (int)g.col_term.size();

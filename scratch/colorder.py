@@ -103,3 +103,28 @@ for kind in sys.argv[1:] or ['default']:
         for iters in (500, 2000, 5000):
             print('  local search', iters, local_search(ncols, cliques, iters=iters, seed=seed)[0], end=';')
         print()
+
+def local_search_from(perm, ncols, cliques, iters, seed=0):
+    rng = random.Random(seed)
+    perm = list(perm)
+    best = block_pairs(perm, ncols, cliques)
+    for it in range(iters):
+        a, b = rng.randrange(ncols), rng.randrange(ncols)
+        if perm[a] // 8 == perm[b] // 8:
+            continue
+        perm[a], perm[b] = perm[b], perm[a]
+        cur = block_pairs(perm, ncols, cliques)
+        if cur <= best:
+            best = cur
+        else:
+            perm[a], perm[b] = perm[b], perm[a]
+    return best
+
+print('--- greedy + short local search')
+for kind in sys.argv[1:] or ['default']:
+    for seed in (5, 6, 7, 8):
+        eqs = population(kind, seed=seed)
+        ncols, cliques = columns(eqs)
+        g = greedy_blocks(ncols, cliques)
+        print(kind, 'pop seed', seed, 'cols', ncols, 'shipped', block_pairs(list(range(ncols)), ncols, cliques), 'greedy', block_pairs(g, ncols, cliques),
+              '+300', local_search_from(g, ncols, cliques, 300), '+1000', local_search_from(g, ncols, cliques, 1000))
