@@ -2505,9 +2505,27 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
                 }
                 order_c.insert(order_c.end(), blk.begin(), blk.end());
             }
-            std::vector<int> re(n);
-            for (int k = 0; k < n; ++k) re[k] = g.col_term[order_c[k]];
-            g.col_term.swap(re);
+            // keep the clustered order only if it needs fewer block pairs than the order of first appearance (which is
+            // already the best one when equations share nothing: each equation's columns sit next to each other)
+            auto block_pairs_of = [&](const std::vector<int>& pos /* column index -> position */) {
+                const int nb = (n + 1 + 7) / 8, ones_blk = n / 8;
+                std::vector<char> need((size_t)nb * nb, 0);
+                for (int e : g.eqs) {
+                    std::vector<int> bl{ones_blk};
+                    for (int t = term_off[e]; t < term_off[e + 1]; ++t) bl.push_back(pos[idx[term_of[t]]] / 8);
+                    for (int a : bl) for (int bb : bl) need[(size_t)std::min(a, bb) * nb + std::max(a, bb)] = 1;
+                }
+                int cnt = 0;
+                for (char v : need) cnt += v;
+                return cnt;
+            };
+            std::vector<int> pos_first(n), pos_greedy(n);
+            for (int k = 0; k < n; ++k) { pos_first[k] = k; pos_greedy[order_c[k]] = k; }
+            if (block_pairs_of(pos_greedy) < block_pairs_of(pos_first)) {
+                std::vector<int> re(n);
+                for (int k = 0; k < n; ++k) re[k] = g.col_term[order_c[k]];
+                g.col_term.swap(re);
+            }
         }
         std::map<int, int> col_of;
         for (size_t k = 0; k < g.col_term.size(); ++k) col_of[g.col_term[k]] = (int)k;
