@@ -403,6 +403,8 @@ def wave_cases(ref):
                 [[('d^2u/dx1^2', 1), ('du/dx0', 1)], [('d^2u/dx0^2', 1), ('du/dx0', 1)]]]
     run_case('wave_b5', coords, d, 5, (2, 2), n_random=14, seed=1, extra_eqs=wave_eqs)
     run_case('wave_b10', coords, d, 10, (2, 2), n_random=10, seed=2, extra_eqs=wave_eqs)
+    # round 2: a third wave fixture so that the wave data carries >= 50 reference-evaluated equations
+    run_case('wave_b8', coords, d, 8, (2, 2), n_random=26, seed=7, extra_eqs=wave_eqs)
 
 
 def burgers_case(ref):
