@@ -76,7 +76,7 @@ def term_key(term):
 
 
 def run_case(name, coords, data, boundary, max_deriv_order, n_random, seed, extra_eqs=(),
-             derivs=None, preproc='FD', preproc_kwargs=None, extra_arrays=None):
+             derivs=None, preproc='FD', preproc_kwargs=None, extra_arrays=None, t_range=(3, 6)):
     rl.load_reference()
     import epde.globals as gv
     search = rl.make_search(coords, data, boundary, max_deriv_order, derivs=derivs, preproc=preproc,
@@ -92,7 +92,7 @@ def run_case(name, coords, data, boundary, max_deriv_order, n_random, seed, extr
     assert np.all(g == 1.0)
 
     rng = np.random.default_rng(seed)
-    eqs = list(extra_eqs) + random_equations(rng, labels, deriv_labels, n_random)
+    eqs = list(extra_eqs) + random_equations(rng, labels, deriv_labels, n_random, t_range=t_range)
 
     term_off, fac_off, fac_tok, fac_pow = [0], [0], [], []
     ev_eq, ev_tgt, ev_coef, ev_b, ev_fit, ev_fit_l2, ev_stab, ev_sw, ev_nact = [], [], [], [], [], [], [], [], []
@@ -391,6 +391,8 @@ def main():
         burgers_poly_case(ref)
     if 'heat' in which:
         heat_case()
+    if 'heat2' in which:
+        heat_case2()
 
 
 def wave_cases(ref):
@@ -436,6 +438,17 @@ def burgers_poly_case(ref):
              preproc_kwargs={'use_smoothing': False, 'mp_poolsize': 4, 'polynomial_window': 9, 'poly_order': None},
              extra_arrays={'data_full': noisy, 'axis0': tb, 'axis1': xb, 'boundary': np.int64(50),
                            'polynomial_window': np.int64(9)})
+
+
+def heat_case2():
+    # (round 2) second 3-D fixture: 36^3, boundary 3 -> 30^3, equations of 4..7 terms
+    n = 36
+    tt = np.linspace(0, 1, n); xx = np.linspace(0, np.pi, n); yy = np.linspace(0, np.pi, n)
+    T3, X3, Y3 = np.meshgrid(tt, xx, yy, indexing='ij')
+    u3 = (np.exp(-T3) * np.sin(X3) * np.sin(Y3) + 0.4 * np.exp(-2.5 * T3) * np.sin(2 * X3) * np.sin(Y3)
+          + 0.2 * np.exp(-4 * T3) * np.sin(X3) * np.sin(3 * Y3))
+    u3 = u3 + 1e-3 * np.random.default_rng(8).standard_normal(u3.shape)
+    run_case('heat3d_b3', (T3, X3, Y3), u3, 3, (1, 2, 2), n_random=8, seed=10, t_range=(4, 7))
 
 
 def heat_case():

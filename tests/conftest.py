@@ -9,7 +9,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 GOLDEN = os.path.join(ROOT, 'tests', 'golden')
-EQ_FIXTURES = ['wave_b5', 'wave_b10', 'wave_b8', 'burgers_b50', 'heat3d_b4', 'burgers_poly_b50']
+EQ_FIXTURES = ['wave_b5', 'wave_b10', 'wave_b8', 'burgers_b50', 'heat3d_b4', 'burgers_poly_b50', 'heat3d_b3']
 
 
 def pytest_configure(config):
