@@ -2563,7 +2563,7 @@ int epde_batch_create(epde_ctx* c, int n_eq, const int32_t* term_off, const int3
                 for (int q = 0; q < MAXSF; ++q) cd.off[q] = -1;
                 for (int f = fac_off[t], q = 0; f < fac_off[t + 1]; ++f, ++q) {
                     cd.off[q] = slot[fac_token[f]];
-                    cd.gfac_off |= (int)fac_power[f] << (8 * q);
+                    cd.gfac_off = (int)((unsigned)cd.gfac_off | ((unsigned)(int)fac_power[f] << (8 * q)));
                 }
             }
             else {
